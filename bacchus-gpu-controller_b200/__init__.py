@@ -1,0 +1,285 @@
+"""bacchus-gpu-controller_b200 — batched admission / quota evaluation on B200 (sm_100a).
+
+Python face of libbgc.so (include/bgc.h): a thin ctypes binding plus a host-side mirror of the
+reference's handler interface (reference src/admission.rs:184-431).  All compute happens in the
+hand-written CUDA kernels of csrc/; there is NO CPU fallback — importing this package without the
+built library, or creating an Engine without a CUDA device, raises.
+
+The directory name carries the reference's hyphens, so import it with
+``importlib.import_module("bacchus-gpu-controller_b200")`` (see tests/conftest.py).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbgc.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "or `make -C bacchus-gpu-controller_b200/csrc`. There is no CPU fallback."
+    )
+
+lib = C.CDLL(LIB_PATH)
+
+OK, E_BADARG, E_CUDA, E_OOM, E_STATE = 0, -1, -2, -3, -4
+MAX_R = 4
+UNIT_COUNT, UNIT_MILLI, UNIT_BYTES = 0, 1, 2
+REDUCE_GROUPED, REDUCE_ACCUMULATE = 1, 2
+K1_AUTO, K1_GLOBAL, K1_SMEM_DIRECT, K1_SMEM_HASH = 0, 1, 2, 3
+VERDICT_BAD_NS = 0xFF
+ALLOW, ALLOW_PATCH, DENY, INVALID = 0, 1, 2, 3
+GEN_GPU, GEN_CPU_MILLI, GEN_MEM_BYTES, GEN_MIG = 0, 1, 2, 3
+DIST_UNIFORM, DIST_ZIPF_CDF = 0, 1
+
+# every symbol include/*.h declares (tests check the library exports all of them)
+EXPORTS = [
+    "bgc_ctx_create", "bgc_ctx_destroy", "bgc_last_error", "bgc_ctx_set_stream", "bgc_ctx_sync",
+    "bgc_timings_get", "bgc_policy_eval", "bgc_policy_eval_dev", "bgc_quota_table_set",
+    "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_quota_eval",
+    "bgc_quota_eval_dev", "bgc_ctx_set_k1_variant", "bgc_last_k1_variant", "bgc_version",
+    "bgc_synth_pods_dev", "bgc_synth_policy_dev", "bgc_checksum_u8_dev", "bgc_histogram_u8_dev",
+    "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
+    "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
+    "bgc_nsmap_intern", "bgc_nsmap_lookup", "bgc_nsmap_size", "bgc_nsmap_name", "bgc_flatten_pods",
+    "bgc_hard_from_sheet_row",
+]
+
+
+class Timings(C.Structure):
+    _fields_ = [("h2d_ns", C.c_uint64), ("kernel_ns", C.c_uint64), ("d2h_ns", C.c_uint64), ("launches", C.c_uint64)]
+
+
+class SynthParams(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("set", C.c_uint32), ("ns_count", C.c_uint32), ("dist", C.c_uint32),
+                ("grouped", C.c_uint32), ("n_total", C.c_uint64), ("scramble_a", C.c_uint64),
+                ("scramble_b", C.c_uint64), ("d_cdf", C.c_void_p), ("R", C.c_uint32), ("kind", C.c_uint32 * MAX_R)]
+
+
+lib.bgc_last_error.restype = C.c_char_p
+lib.bgc_last_error.argtypes = [C.c_void_p]
+lib.bgc_last_k1_variant.restype = C.c_char_p
+lib.bgc_last_k1_variant.argtypes = [C.c_void_p]
+lib.bgc_version.restype = C.c_char_p
+lib.bgc_reason_message.restype = C.c_char_p
+lib.bgc_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+lib.bgc_ctx_destroy.argtypes = [C.c_void_p]
+lib.bgc_ctx_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+lib.bgc_ctx_sync.argtypes = [C.c_void_p]
+lib.bgc_timings_get.argtypes = [C.c_void_p, C.POINTER(Timings)]
+lib.bgc_ctx_set_k1_variant.argtypes = [C.c_void_p, C.c_int]
+_P, _Z = C.c_void_p, C.c_size_t
+lib.bgc_policy_eval.argtypes = [_P, _P, _P, _Z, _P, _P]
+lib.bgc_policy_eval_dev.argtypes = [_P, _P, _P, _Z, _P, _P]
+lib.bgc_quota_table_set.argtypes = [_P, C.c_uint32, C.c_uint32, _P, _P, _P]
+lib.bgc_usage_reduce.argtypes = [_P, _P, _P, _Z, C.c_uint, _P]
+lib.bgc_usage_reduce_dev.argtypes = [_P, _P, _P, _Z, C.c_uint, _P]
+lib.bgc_usage_get.argtypes = [_P, _P]
+lib.bgc_usage_set.argtypes = [_P, _P]
+lib.bgc_quota_eval.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_quota_eval_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_synth_pods_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64, _Z, _P, _P, _P]
+lib.bgc_synth_policy_dev.argtypes = [_P, C.c_uint64, C.c_uint64, _Z, _P, _P]
+lib.bgc_checksum_u8_dev.argtypes = [_P, _P, C.c_uint64, _Z, C.POINTER(C.c_uint64)]
+lib.bgc_histogram_u8_dev.argtypes = [_P, _P, _Z, _P]
+
+
+class BgcError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"bgc error {code}: {msg}")
+        self.code = code
+
+
+def _np_ptr(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def _dev_ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _check_np(a, dtype, n=None, name="array"):
+    if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags["C_CONTIGUOUS"]:
+        raise TypeError(f"{name} must be a C-contiguous numpy array of {np.dtype(dtype).name}")
+    if n is not None and a.shape[0] != n:
+        raise ValueError(f"{name} has {a.shape[0]} rows, expected {n}")
+
+
+class Engine:
+    """One bgc_ctx bound to one CUDA device (replaces the reference's Arc<AppState>,
+    src/admission.rs:145-147).  Not thread-safe: use one Engine per thread."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        rc = lib.bgc_ctx_create(device, C.byref(h))
+        if rc != OK:
+            raise BgcError(rc, "bgc_ctx_create failed: no usable CUDA device (there is no CPU fallback)")
+        self._h = h
+        self.device = device
+        self.NS = 0
+        self.R = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.bgc_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != OK:
+            raise BgcError(rc, lib.bgc_last_error(self._h).decode())
+
+    # -- plumbing
+    def set_stream(self, cuda_stream_handle: int | None):
+        self._ck(lib.bgc_ctx_set_stream(self._h, C.c_void_p(cuda_stream_handle or 0)))
+
+    def use_torch_stream(self):
+        import torch
+        self.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def sync(self):
+        self._ck(lib.bgc_ctx_sync(self._h))
+
+    def timings(self) -> dict:
+        t = Timings()
+        self._ck(lib.bgc_timings_get(self._h, C.byref(t)))
+        return dict(h2d_ns=t.h2d_ns, kernel_ns=t.kernel_ns, d2h_ns=t.d2h_ns, launches=t.launches)
+
+    def set_k1_variant(self, v: int):
+        self._ck(lib.bgc_ctx_set_k1_variant(self._h, v))
+
+    def last_k1_variant(self) -> str:
+        return lib.bgc_last_k1_variant(self._h).decode()
+
+    # -- K0 (row A1)
+    def policy_eval(self, op: np.ndarray, flags: np.ndarray):
+        n = op.shape[0]
+        _check_np(op, np.uint8, name="op")
+        _check_np(flags, np.uint16, n, "flags")
+        code = np.empty(n, np.uint8)
+        pm = np.empty(n, np.uint8)
+        self._ck(lib.bgc_policy_eval(self._h, _np_ptr(op), _np_ptr(flags), n, _np_ptr(code), _np_ptr(pm)))
+        return code, pm
+
+    def policy_eval_dev(self, d_op, d_flags, d_code, d_pm):
+        self._ck(lib.bgc_policy_eval_dev(self._h, _dev_ptr(d_op), _dev_ptr(d_flags), d_op.numel(),
+                                         _dev_ptr(d_code), _dev_ptr(d_pm)))
+
+    # -- quota table
+    def quota_table_set(self, hard: np.ndarray, hard_mask: np.ndarray, unit):
+        hard = np.ascontiguousarray(hard, dtype=np.int64)
+        R, NS = hard.shape
+        _check_np(hard_mask, np.uint8, NS, "hard_mask")
+        u = np.asarray(unit, dtype=np.uint8)
+        if u.shape[0] != R:
+            raise ValueError("unit must have R entries")
+        self._ck(lib.bgc_quota_table_set(self._h, NS, R, _np_ptr(hard), _np_ptr(hard_mask), _np_ptr(u)))
+        self.NS, self.R = NS, R
+
+    def usage_get(self) -> np.ndarray:
+        out = np.empty((self.R, self.NS), np.int64)
+        self._ck(lib.bgc_usage_get(self._h, _np_ptr(out)))
+        return out
+
+    def usage_set(self, used: np.ndarray):
+        used = np.ascontiguousarray(used, dtype=np.int64)
+        if used.shape != (self.R, self.NS):
+            raise ValueError("used must be [R][NS]")
+        self._ck(lib.bgc_usage_set(self._h, _np_ptr(used)))
+
+    # -- K1 (row A3)
+    def usage_reduce(self, ns_id: np.ndarray, req: list, flags: int = 0, want_used: bool = True):
+        n = ns_id.shape[0]
+        _check_np(ns_id, np.uint32, name="ns_id")
+        for r, c in enumerate(req):
+            _check_np(c, np.int64, n, f"req[{r}]")
+        if len(req) != self.R:
+            raise ValueError(f"expected {self.R} request columns")
+        ptrs = (C.c_void_p * len(req))(*[c.ctypes.data for c in req])
+        out = np.empty((self.R, self.NS), np.int64) if want_used else None
+        self._ck(lib.bgc_usage_reduce(self._h, _np_ptr(ns_id), ptrs, n, flags, _np_ptr(out)))
+        return out
+
+    def usage_reduce_dev(self, d_ns_id, d_req: list, flags: int = 0, d_used_out=None, n: int | None = None):
+        if len(d_req) != self.R:
+            raise ValueError(f"expected {self.R} request columns")
+        ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
+        self._ck(lib.bgc_usage_reduce_dev(self._h, _dev_ptr(d_ns_id), ptrs, d_ns_id.numel() if n is None else n,
+                                          flags, _dev_ptr(d_used_out)))
+
+    # -- K2 (row A4)
+    def quota_eval(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None) -> np.ndarray:
+        n = ns_id.shape[0]
+        _check_np(ns_id, np.uint32, name="ns_id")
+        for r, c in enumerate(req):
+            _check_np(c, np.int64, n, f"req[{r}]")
+        if req_mask is not None:
+            _check_np(req_mask, np.uint8, n, "req_mask")
+        if len(req) != self.R:
+            raise ValueError(f"expected {self.R} request columns")
+        ptrs = (C.c_void_p * len(req))(*[c.ctypes.data for c in req])
+        verdict = np.empty(n, np.uint8)
+        self._ck(lib.bgc_quota_eval(self._h, _np_ptr(ns_id), ptrs, _np_ptr(req_mask), n, _np_ptr(verdict)))
+        return verdict
+
+    def quota_eval_dev(self, d_ns_id, d_req: list, d_req_mask, d_verdict, n: int | None = None):
+        ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
+        self._ck(lib.bgc_quota_eval_dev(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask),
+                                        d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
+
+    # -- raw-pointer variants (host pinned buffers, slices of larger allocations)
+    def usage_reduce_ptr(self, ns_ptr: int, req_ptrs: list, n: int, flags: int = 0, used_out_ptr: int = 0):
+        ptrs = (C.c_void_p * len(req_ptrs))(*req_ptrs)
+        self._ck(lib.bgc_usage_reduce(self._h, C.c_void_p(ns_ptr), ptrs, n, flags, C.c_void_p(used_out_ptr)))
+
+    def quota_eval_ptr(self, ns_ptr: int, req_ptrs: list, mask_ptr: int, n: int, verdict_ptr: int):
+        ptrs = (C.c_void_p * len(req_ptrs))(*req_ptrs)
+        self._ck(lib.bgc_quota_eval(self._h, C.c_void_p(ns_ptr), ptrs, C.c_void_p(mask_ptr), n, C.c_void_p(verdict_ptr)))
+
+    def policy_eval_ptr(self, op_ptr: int, flags_ptr: int, n: int, code_ptr: int, pm_ptr: int):
+        self._ck(lib.bgc_policy_eval(self._h, C.c_void_p(op_ptr), C.c_void_p(flags_ptr), n, C.c_void_p(code_ptr), C.c_void_p(pm_ptr)))
+
+    # -- synthetic inputs on the device (include/bgc_synth.h)
+    def synth_pods_dev(self, params: SynthParams, first: int, count: int, d_ns_id, d_req: list, d_req_mask=None):
+        ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
+        self._ck(lib.bgc_synth_pods_dev(self._h, C.byref(params), first, count, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask)))
+
+    def synth_policy_dev(self, seed: int, first: int, count: int, d_op, d_flags):
+        self._ck(lib.bgc_synth_policy_dev(self._h, seed, first, count, _dev_ptr(d_op), _dev_ptr(d_flags)))
+
+    def checksum_u8_dev(self, d_v, first: int = 0, count: int | None = None) -> int:
+        out = C.c_uint64()
+        self._ck(lib.bgc_checksum_u8_dev(self._h, _dev_ptr(d_v), first, d_v.numel() if count is None else count, C.byref(out)))
+        return out.value
+
+    def histogram_u8_dev(self, d_v, count: int | None = None) -> np.ndarray:
+        out = np.zeros(256, np.uint64)
+        self._ck(lib.bgc_histogram_u8_dev(self._h, _dev_ptr(d_v), d_v.numel() if count is None else count, _np_ptr(out)))
+        return out
+
+
+def synth_params(seed, set_, NS, dist, grouped, n_total, a, b, d_cdf, kinds) -> SynthParams:
+    p = SynthParams()
+    p.seed, p.set, p.ns_count, p.dist, p.grouped, p.n_total = seed, set_, NS, dist, int(grouped), n_total
+    p.scramble_a, p.scramble_b = a, b
+    p.d_cdf = d_cdf.data_ptr() if d_cdf is not None else None
+    p.R = len(kinds)
+    for i, k in enumerate(kinds):
+        p.kind[i] = k
+    return p
+
+
+def version() -> str:
+    return lib.bgc_version().decode()
+
+
+from . import admission, pods, shard  # noqa: E402,F401

@@ -1,0 +1,733 @@
+// bgc_api.cu — the C ABI of libbgc.so (include/bgc.h, include/bgc_synth.h).
+//
+// Host side of the boundary that sits behind the reference's `mutate` seam
+// (reference src/admission.rs:241-244): a context per caller thread, caller-owned POD buffers,
+// integer status codes, no exceptions across the boundary, no CPU fallback.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/bgc.h"
+#include "../../include/bgc_synth.h"
+#include "bgc_kernels.cuh"
+
+using namespace bgc;
+
+namespace {
+
+constexpr size_t kChunkPods = size_t(4) << 20;      // host-pointer calls move 4 Mi pods per stage
+constexpr size_t kSmemBudget = 200 * 1024;          // CTA-private K1 table budget (<= 227 KB opt-in)
+constexpr int kSlots = 2;
+
+struct Slot {
+  uint32_t* ns = nullptr;
+  long long* req[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  uint8_t* mask = nullptr;
+  uint8_t* out0 = nullptr;  // verdict / code
+  uint8_t* out1 = nullptr;  // patch_mask
+  uint16_t* flags = nullptr;
+  cudaEvent_t h2d_done = nullptr, k_done = nullptr, free_ev = nullptr;
+  bool used = false;
+};
+
+}  // namespace
+
+struct bgc_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t own_stream = nullptr, stream = nullptr, h2d_stream = nullptr, d2h_stream = nullptr;
+  std::string err;
+  // quota table
+  QuotaRow* rows = nullptr;
+  uint8_t* d_hard_mask = nullptr;
+  long long* d_table_tmp = nullptr;  // [R][NS] staging for import/export
+  uint32_t NS = 0;
+  int R = 0;
+  uint32_t compute_mask = 0;
+  // K1
+  int k1_forced = BGC_K1_AUTO;
+  const char* last_k1 = "none";
+  // staging for host-pointer calls
+  Slot slot[kSlots];
+  size_t slot_pods = 0;
+  int slot_R = 0;
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_next = 0;
+  unsigned long long* d_scratch = nullptr;  // 256 x u64
+  bgc_timings tm{};
+};
+
+namespace {
+
+int fail(bgc_ctx* c, int code, const char* fmt, ...) {
+  if (c) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    c->err = buf;
+  }
+  return code;
+}
+
+#define CU(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return fail(ctx, e_ == cudaErrorMemoryAllocation ? BGC_E_OOM : BGC_E_CUDA, "%s: %s",    \
+                  #call, cudaGetErrorString(e_));                                             \
+  } while (0)
+
+#define NEED(cond, msg)                                   \
+  do {                                                    \
+    if (!(cond)) return fail(ctx, BGC_E_BADARG, "%s", msg); \
+  } while (0)
+
+inline bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
+int grid_for(size_t work_items, int per_block, int max_blocks) {
+  size_t b = (work_items + per_block - 1) / per_block;
+  if (b < 1) b = 1;
+  if (b > (size_t)max_blocks) b = max_blocks;
+  return (int)b;
+}
+
+cudaEvent_t next_event(bgc_ctx* ctx) {
+  if (ctx->ev_next == ctx->ev_pool.size()) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+    ctx->ev_pool.push_back(e);
+  }
+  return ctx->ev_pool[ctx->ev_next++];
+}
+
+// ---- kernel launchers (device pointers, ctx->stream unless told otherwise) -------------------
+int launch_k0(bgc_ctx* ctx, cudaStream_t st, const uint8_t* op, const uint16_t* flags, size_t n,
+              uint8_t* code, uint8_t* pm) {
+  if (n == 0) return BGC_OK;
+  const int vec = aligned(op, 16) && aligned(flags, 16) && aligned(code, 16) && aligned(pm, 16);
+  const int grid = grid_for((n + kK0PerThread - 1) / kK0PerThread, kK0Threads, ctx->sm_count * 8);
+  k0_policy_eval<<<grid, kK0Threads, 0, st>>>(op, flags, n, code, pm, vec);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+template <int R, int SINK, bool VEC>
+int launch_k1_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
+                   size_t n, uint32_t cap) {
+  ReqCols<R> cols;
+  for (int r = 0; r < R; ++r) cols.p[r] = req[r];
+  auto kern = k1_usage_reduce<R, SINK, VEC>;
+  size_t smem = 0;
+  int threads = 512, blocks_per_sm = 1;
+  if (SINK == SINK_GLOBAL) {
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, threads, 0));
+    if (blocks_per_sm < 1) blocks_per_sm = 1;
+  } else {
+    threads = 1024;
+    smem = (size_t)2 * R * cap * 4 + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  const size_t tiles = (n + kK1Tile - 1) / kK1Tile;
+  int grid = ctx->sm_count * blocks_per_sm;
+  const size_t warps_per_block = threads / 32;
+  if ((size_t)grid * warps_per_block > tiles) grid = (int)((tiles + warps_per_block - 1) / warps_per_block);
+  if (grid < 1) grid = 1;
+  // a warp's chunk: long enough to amortise the carry flush, short enough to balance the grid
+  size_t chunk_tiles = tiles / ((size_t)grid * warps_per_block * 4);
+  if (chunk_tiles < 1) chunk_tiles = 1;
+  if (chunk_tiles > 32) chunk_tiles = 32;
+  kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->rows, ctx->NS, cap, (uint32_t)chunk_tiles);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+template <int R>
+int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
+                size_t n, unsigned flags) {
+  bool vec = aligned(ns, 16);
+  for (int r = 0; r < R; ++r) vec = vec && aligned(req[r], 32);
+  // variant choice
+  int variant = ctx->k1_forced;
+  const size_t direct_bytes = (size_t)ctx->NS * R * 8;
+  if (variant == BGC_K1_AUTO) {
+    if (flags & BGC_REDUCE_GROUPED) variant = BGC_K1_GLOBAL;
+    else if (direct_bytes <= kSmemBudget) variant = BGC_K1_SMEM_DIRECT;
+    else variant = BGC_K1_SMEM_HASH;
+  }
+  if (variant == BGC_K1_SMEM_DIRECT && direct_bytes > kSmemBudget) variant = BGC_K1_SMEM_HASH;
+  uint32_t cap = ctx->NS;
+  if (variant == BGC_K1_SMEM_HASH) {
+    cap = 1;
+    while ((size_t)cap * 2 * (8 * R + 4) <= kSmemBudget) cap *= 2;
+  }
+  switch (variant) {
+    case BGC_K1_GLOBAL:
+      ctx->last_k1 = "global_red";
+      return vec ? launch_k1_inst<R, SINK_GLOBAL, true>(ctx, st, ns, req, n, cap)
+                 : launch_k1_inst<R, SINK_GLOBAL, false>(ctx, st, ns, req, n, cap);
+    case BGC_K1_SMEM_DIRECT:
+      ctx->last_k1 = "smem_direct";
+      return vec ? launch_k1_inst<R, SINK_DIRECT, true>(ctx, st, ns, req, n, cap)
+                 : launch_k1_inst<R, SINK_DIRECT, false>(ctx, st, ns, req, n, cap);
+    default:
+      ctx->last_k1 = "smem_hash";
+      return vec ? launch_k1_inst<R, SINK_HASH, true>(ctx, st, ns, req, n, cap)
+                 : launch_k1_inst<R, SINK_HASH, false>(ctx, st, ns, req, n, cap);
+  }
+}
+
+int launch_k1(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
+              size_t n, unsigned flags) {
+  if (n == 0) return BGC_OK;
+  switch (ctx->R) {
+    case 1: return launch_k1_r<1>(ctx, st, ns, req, n, flags);
+    case 2: return launch_k1_r<2>(ctx, st, ns, req, n, flags);
+    case 3: return launch_k1_r<3>(ctx, st, ns, req, n, flags);
+    default: return launch_k1_r<4>(ctx, st, ns, req, n, flags);
+  }
+}
+
+template <int R, bool HAS_MASK>
+int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
+                   const uint8_t* mask, size_t n, uint8_t* verdict) {
+  ReqCols<R> cols;
+  bool vec = aligned(ns, 16) && aligned(verdict, 4) && (!HAS_MASK || aligned(mask, 4));
+  for (int r = 0; r < R; ++r) {
+    cols.p[r] = req[r];
+    vec = vec && aligned(req[r], 32);
+  }
+  const int grid = grid_for((n + 3) / 4, kK2Threads, ctx->sm_count * 8);
+  if (vec)
+    k2_quota_eval<R, HAS_MASK, true><<<grid, kK2Threads, 0, st>>>(
+        ns, cols, mask, n, ctx->rows, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+  else
+    k2_quota_eval<R, HAS_MASK, false><<<grid, kK2Threads, 0, st>>>(
+        ns, cols, mask, n, ctx->rows, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+int launch_k2(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
+              const uint8_t* mask, size_t n, uint8_t* verdict) {
+  if (n == 0) return BGC_OK;
+#define K2CASE(RR)                                                                   \
+  case RR:                                                                           \
+    return mask ? launch_k2_inst<RR, true>(ctx, st, ns, req, mask, n, verdict)       \
+                : launch_k2_inst<RR, false>(ctx, st, ns, req, mask, n, verdict);
+  switch (ctx->R) {
+    K2CASE(1)
+    K2CASE(2)
+    K2CASE(3)
+    default:
+      return mask ? launch_k2_inst<4, true>(ctx, st, ns, req, mask, n, verdict)
+                  : launch_k2_inst<4, false>(ctx, st, ns, req, mask, n, verdict);
+  }
+#undef K2CASE
+}
+
+int clear_used(bgc_ctx* ctx, cudaStream_t st) {
+  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
+  k_rows_clear_used<<<grid, 256, 0, st>>>(ctx->rows, ctx->NS, ctx->R);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+int export_used(bgc_ctx* ctx, cudaStream_t st, long long* d_out) {
+  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
+  k_rows_export_used<<<grid, 256, 0, st>>>(ctx->rows, d_out, ctx->NS, ctx->R);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+void free_slots(bgc_ctx* ctx) {
+  for (auto& s : ctx->slot) {
+    cudaFree(s.ns);
+    for (auto& p : s.req) { cudaFree(p); p = nullptr; }
+    cudaFree(s.mask);
+    cudaFree(s.out0);
+    cudaFree(s.out1);
+    cudaFree(s.flags);
+    s.ns = nullptr; s.mask = s.out0 = s.out1 = nullptr; s.flags = nullptr;
+  }
+  ctx->slot_pods = 0;
+  ctx->slot_R = 0;
+}
+
+// device staging for host-pointer calls, sized to the largest chunk seen so far
+int ensure_slots(bgc_ctx* ctx, size_t pods, int R) {
+  if (pods > kChunkPods) pods = kChunkPods;
+  pods = (pods + 127) & ~size_t(127);
+  if (pods <= ctx->slot_pods && R <= ctx->slot_R) return BGC_OK;
+  if (pods < ctx->slot_pods) pods = ctx->slot_pods;
+  if (R < ctx->slot_R) R = ctx->slot_R;
+  CU(cudaDeviceSynchronize());
+  free_slots(ctx);
+  for (auto& s : ctx->slot) {
+    CU(cudaMalloc(&s.ns, pods * 4));
+    for (int r = 0; r < R; ++r) CU(cudaMalloc(&s.req[r], pods * 8));
+    CU(cudaMalloc(&s.mask, pods));
+    CU(cudaMalloc(&s.out0, pods));
+    CU(cudaMalloc(&s.out1, pods));
+    CU(cudaMalloc(&s.flags, pods * 2));
+    if (!s.h2d_done) {
+      CU(cudaEventCreateWithFlags(&s.h2d_done, cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&s.k_done, cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&s.free_ev, cudaEventDisableTiming));
+    }
+    s.used = false;
+  }
+  ctx->slot_pods = pods;
+  ctx->slot_R = R;
+  return BGC_OK;
+}
+
+struct Spans {
+  std::vector<cudaEvent_t> h2d, k, d2h;  // start/stop pairs
+};
+
+int finish_timings(bgc_ctx* ctx, const Spans& sp) {
+  auto sum = [&](const std::vector<cudaEvent_t>& v, uint64_t* out) -> cudaError_t {
+    double total = 0;
+    for (size_t i = 0; i + 1 < v.size(); i += 2) {
+      float ms = 0;
+      cudaError_t e = cudaEventElapsedTime(&ms, v[i], v[i + 1]);
+      if (e != cudaSuccess) return e;
+      total += ms;
+    }
+    *out = (uint64_t)(total * 1e6);
+    return cudaSuccess;
+  };
+  CU(sum(sp.h2d, &ctx->tm.h2d_ns));
+  CU(sum(sp.k, &ctx->tm.kernel_ns));
+  CU(sum(sp.d2h, &ctx->tm.d2h_ns));
+  return BGC_OK;
+}
+
+}  // namespace
+
+// =============================================================================== C ABI
+extern "C" {
+
+const char* bgc_version(void) { return "bgc 0.1 (sm_100a)"; }
+
+int bgc_ctx_create(int device, bgc_ctx** out) {
+  if (!out) return BGC_E_BADARG;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return BGC_E_CUDA;
+  bgc_ctx* ctx = new (std::nothrow) bgc_ctx;
+  if (!ctx) return BGC_E_OOM;
+  ctx->device = device;
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMalloc(&ctx->d_scratch, 256 * sizeof(unsigned long long));
+  if (e != cudaSuccess) {
+    delete ctx;
+    return BGC_E_CUDA;
+  }
+  ctx->stream = ctx->own_stream;
+  *out = ctx;
+  return BGC_OK;
+}
+
+int bgc_ctx_destroy(bgc_ctx* ctx) {
+  if (!ctx) return BGC_E_BADARG;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  free_slots(ctx);
+  for (auto& s : ctx->slot) {
+    if (s.h2d_done) cudaEventDestroy(s.h2d_done);
+    if (s.k_done) cudaEventDestroy(s.k_done);
+    if (s.free_ev) cudaEventDestroy(s.free_ev);
+  }
+  for (auto e : ctx->ev_pool) cudaEventDestroy(e);
+  cudaFree(ctx->rows);
+  cudaFree(ctx->d_hard_mask);
+  cudaFree(ctx->d_table_tmp);
+  cudaFree(ctx->d_scratch);
+  cudaStreamDestroy(ctx->own_stream);
+  cudaStreamDestroy(ctx->h2d_stream);
+  cudaStreamDestroy(ctx->d2h_stream);
+  delete ctx;
+  return BGC_OK;
+}
+
+const char* bgc_last_error(const bgc_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int bgc_ctx_set_stream(bgc_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return BGC_E_BADARG;
+  ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  return BGC_OK;
+}
+
+int bgc_ctx_sync(bgc_ctx* ctx) {
+  if (!ctx) return BGC_E_BADARG;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaStreamSynchronize(ctx->h2d_stream));
+  CU(cudaStreamSynchronize(ctx->d2h_stream));
+  return BGC_OK;
+}
+
+int bgc_timings_get(bgc_ctx* ctx, bgc_timings* out) {
+  if (!ctx || !out) return BGC_E_BADARG;
+  *out = ctx->tm;
+  return BGC_OK;
+}
+
+int bgc_ctx_set_k1_variant(bgc_ctx* ctx, int variant) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(variant >= BGC_K1_AUTO && variant <= BGC_K1_SMEM_HASH, "unknown K1 variant");
+  ctx->k1_forced = variant;
+  return BGC_OK;
+}
+
+const char* bgc_last_k1_variant(const bgc_ctx* ctx) { return ctx ? ctx->last_k1 : "none"; }
+
+// ---------------------------------------------------------------- K0
+int bgc_policy_eval_dev(bgc_ctx* ctx, const uint8_t* d_op, const uint16_t* d_flags, size_t n,
+                        uint8_t* d_code, uint8_t* d_patch_mask) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(n == 0 || (d_op && d_flags && d_code && d_patch_mask), "null column pointer");
+  CU(cudaSetDevice(ctx->device));
+  return launch_k0(ctx, ctx->stream, d_op, d_flags, n, d_code, d_patch_mask);
+}
+
+int bgc_policy_eval(bgc_ctx* ctx, const uint8_t* op, const uint16_t* flags, size_t n, uint8_t* code,
+                    uint8_t* patch_mask) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(n == 0 || (op && flags && code && patch_mask), "null column pointer");
+  CU(cudaSetDevice(ctx->device));
+  ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
+  if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
+  if (n == 0) return BGC_OK;
+  int rc = ensure_slots(ctx, n, ctx->slot_R);
+  if (rc) return rc;
+  ctx->ev_next = 0;
+  Spans sp;
+  const size_t chunk = ctx->slot_pods;
+  size_t k = 0;
+  for (size_t off = 0; off < n; off += chunk, ++k) {
+    Slot& s = ctx->slot[k % kSlots];
+    const size_t m = (n - off < chunk) ? n - off : chunk;
+    cudaEvent_t a = next_event(ctx), b = next_event(ctx), c = next_event(ctx), d = next_event(ctx),
+                e = next_event(ctx), f = next_event(ctx);
+    if (!f) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
+    if (s.used) CU(cudaStreamWaitEvent(ctx->h2d_stream, s.free_ev, 0));
+    CU(cudaEventRecord(a, ctx->h2d_stream));
+    CU(cudaMemcpyAsync(s.mask, op + off, m, cudaMemcpyHostToDevice, ctx->h2d_stream));  // op column staged in `mask`
+    CU(cudaMemcpyAsync(s.flags, flags + off, m * 2, cudaMemcpyHostToDevice, ctx->h2d_stream));
+    CU(cudaEventRecord(b, ctx->h2d_stream));
+    CU(cudaEventRecord(s.h2d_done, ctx->h2d_stream));
+    CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+    CU(cudaEventRecord(c, ctx->own_stream));
+    rc = launch_k0(ctx, ctx->own_stream, s.mask, s.flags, m, s.out0, s.out1);
+    if (rc) return rc;
+    CU(cudaEventRecord(d, ctx->own_stream));
+    CU(cudaEventRecord(s.k_done, ctx->own_stream));
+    CU(cudaStreamWaitEvent(ctx->d2h_stream, s.k_done, 0));
+    CU(cudaEventRecord(e, ctx->d2h_stream));
+    CU(cudaMemcpyAsync(code + off, s.out0, m, cudaMemcpyDeviceToHost, ctx->d2h_stream));
+    CU(cudaMemcpyAsync(patch_mask + off, s.out1, m, cudaMemcpyDeviceToHost, ctx->d2h_stream));
+    CU(cudaEventRecord(f, ctx->d2h_stream));
+    CU(cudaEventRecord(s.free_ev, ctx->d2h_stream));
+    s.used = true;
+    sp.h2d.push_back(a); sp.h2d.push_back(b);
+    sp.k.push_back(c); sp.k.push_back(d);
+    sp.d2h.push_back(e); sp.d2h.push_back(f);
+  }
+  CU(cudaStreamSynchronize(ctx->d2h_stream));
+  return finish_timings(ctx, sp);
+}
+
+// ---------------------------------------------------------------- quota table
+int bgc_quota_table_set(bgc_ctx* ctx, uint32_t ns_count, uint32_t R, const int64_t* hard,
+                        const uint8_t* hard_mask, const uint8_t* unit) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(ns_count > 0 && ns_count < 0xFFFFFFFFu, "ns_count out of range");
+  NEED(R >= 1 && R <= BGC_MAX_R, "R must be 1..BGC_MAX_R");
+  NEED(hard && hard_mask && unit, "null table pointer");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaDeviceSynchronize());
+  if (ns_count != ctx->NS || (int)R != ctx->R) {
+    cudaFree(ctx->rows); ctx->rows = nullptr;
+    cudaFree(ctx->d_hard_mask); ctx->d_hard_mask = nullptr;
+    cudaFree(ctx->d_table_tmp); ctx->d_table_tmp = nullptr;
+    ctx->NS = 0; ctx->R = 0;
+    CU(cudaMalloc(&ctx->rows, (size_t)ns_count * sizeof(QuotaRow)));
+    CU(cudaMalloc(&ctx->d_hard_mask, ns_count));
+    CU(cudaMalloc(&ctx->d_table_tmp, (size_t)ns_count * R * 8));
+  }
+  ctx->NS = ns_count;
+  ctx->R = (int)R;
+  ctx->compute_mask = 0;
+  for (uint32_t r = 0; r < R; ++r) {
+    NEED(unit[r] <= BGC_UNIT_BYTES, "unknown unit");
+    if (unit[r] != BGC_UNIT_COUNT) ctx->compute_mask |= 1u << r;
+  }
+  CU(cudaMemcpyAsync(ctx->d_table_tmp, hard, (size_t)ns_count * R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
+  CU(cudaMemcpyAsync(ctx->d_hard_mask, hard_mask, ns_count, cudaMemcpyHostToDevice, ctx->own_stream));
+  const int grid = grid_for((size_t)ns_count * 8, 256, ctx->sm_count * 4);
+  k_rows_set_hard<<<grid, 256, 0, ctx->own_stream>>>(ctx->rows, ctx->d_table_tmp, ctx->d_hard_mask, ns_count, (int)R);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(ctx->own_stream));
+  return BGC_OK;
+}
+
+int bgc_usage_get(bgc_ctx* ctx, int64_t* used_out) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(used_out, "null output");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  int rc = export_used(ctx, ctx->own_stream, ctx->d_table_tmp);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(used_out, ctx->d_table_tmp, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyDeviceToHost, ctx->own_stream));
+  CU(cudaStreamSynchronize(ctx->own_stream));
+  return BGC_OK;
+}
+
+int bgc_usage_set(bgc_ctx* ctx, const int64_t* used) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(used, "null input");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaMemcpyAsync(ctx->d_table_tmp, used, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
+  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
+  k_rows_import_used<<<grid, 256, 0, ctx->own_stream>>>(ctx->rows, ctx->d_table_tmp, ctx->NS, ctx->R);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(ctx->own_stream));
+  return BGC_OK;
+}
+
+// ---------------------------------------------------------------- K1
+int bgc_usage_reduce_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req, size_t n,
+                         unsigned flags, int64_t* d_used_out) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(n == 0 || (d_ns_id && d_req), "null column pointer");
+  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  for (int r = 0; r < ctx->R && n; ++r) {
+    NEED(d_req[r], "null request column");
+    cols[r] = reinterpret_cast<const long long*>(d_req[r]);
+  }
+  CU(cudaSetDevice(ctx->device));
+  int rc;
+  if (!(flags & BGC_REDUCE_ACCUMULATE) && (rc = clear_used(ctx, ctx->stream))) return rc;
+  if ((rc = launch_k1(ctx, ctx->stream, d_ns_id, cols, n, flags))) return rc;
+  if (d_used_out) return export_used(ctx, ctx->stream, reinterpret_cast<long long*>(d_used_out));
+  return BGC_OK;
+}
+
+int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req, size_t n,
+                     unsigned flags, int64_t* used_out) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(n == 0 || (ns_id && req), "null column pointer");
+  const int R = ctx->R;
+  for (int r = 0; r < R && n; ++r) NEED(req[r], "null request column");
+  CU(cudaSetDevice(ctx->device));
+  ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
+  if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
+  int rc;
+  if (!(flags & BGC_REDUCE_ACCUMULATE) && (rc = clear_used(ctx, ctx->own_stream))) return rc;
+  Spans sp;
+  if (n) {
+    if ((rc = ensure_slots(ctx, n, R))) return rc;
+    ctx->ev_next = 0;
+    const size_t chunk = ctx->slot_pods;
+    size_t k = 0;
+    for (size_t off = 0; off < n; off += chunk, ++k) {
+      Slot& s = ctx->slot[k % kSlots];
+      const size_t m = (n - off < chunk) ? n - off : chunk;
+      cudaEvent_t a = next_event(ctx), b = next_event(ctx), c = next_event(ctx), d = next_event(ctx);
+      if (!d) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
+      if (s.used) CU(cudaStreamWaitEvent(ctx->h2d_stream, s.free_ev, 0));
+      CU(cudaEventRecord(a, ctx->h2d_stream));
+      CU(cudaMemcpyAsync(s.ns, ns_id + off, m * 4, cudaMemcpyHostToDevice, ctx->h2d_stream));
+      for (int r = 0; r < R; ++r)
+        CU(cudaMemcpyAsync(s.req[r], req[r] + off, m * 8, cudaMemcpyHostToDevice, ctx->h2d_stream));
+      CU(cudaEventRecord(b, ctx->h2d_stream));
+      CU(cudaEventRecord(s.h2d_done, ctx->h2d_stream));
+      CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+      CU(cudaEventRecord(c, ctx->own_stream));
+      if ((rc = launch_k1(ctx, ctx->own_stream, s.ns, s.req, m, flags))) return rc;
+      CU(cudaEventRecord(d, ctx->own_stream));
+      CU(cudaEventRecord(s.free_ev, ctx->own_stream));
+      s.used = true;
+      sp.h2d.push_back(a); sp.h2d.push_back(b);
+      sp.k.push_back(c); sp.k.push_back(d);
+    }
+  }
+  if (used_out) {
+    cudaEvent_t e = next_event(ctx), f = next_event(ctx);
+    if (!f) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
+    if ((rc = export_used(ctx, ctx->own_stream, ctx->d_table_tmp))) return rc;
+    CU(cudaEventRecord(e, ctx->own_stream));
+    CU(cudaMemcpyAsync(used_out, ctx->d_table_tmp, (size_t)ctx->NS * R * 8, cudaMemcpyDeviceToHost, ctx->own_stream));
+    CU(cudaEventRecord(f, ctx->own_stream));
+    sp.d2h.push_back(e); sp.d2h.push_back(f);
+  }
+  CU(cudaStreamSynchronize(ctx->own_stream));
+  return finish_timings(ctx, sp);
+}
+
+// ---------------------------------------------------------------- K2
+int bgc_quota_eval_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
+                       const uint8_t* d_req_mask, size_t n, uint8_t* d_verdict) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(n == 0 || (d_ns_id && d_req && d_verdict), "null column pointer");
+  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  for (int r = 0; r < ctx->R && n; ++r) {
+    NEED(d_req[r], "null request column");
+    cols[r] = reinterpret_cast<const long long*>(d_req[r]);
+  }
+  CU(cudaSetDevice(ctx->device));
+  return launch_k2(ctx, ctx->stream, d_ns_id, cols, d_req_mask, n, d_verdict);
+}
+
+int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
+                   const uint8_t* req_mask, size_t n, uint8_t* verdict) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(n == 0 || (ns_id && req && verdict), "null column pointer");
+  const int R = ctx->R;
+  for (int r = 0; r < R && n; ++r) NEED(req[r], "null request column");
+  CU(cudaSetDevice(ctx->device));
+  ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
+  if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
+  if (n == 0) return BGC_OK;
+  int rc;
+  if ((rc = ensure_slots(ctx, n, R))) return rc;
+  ctx->ev_next = 0;
+  Spans sp;
+  const size_t chunk = ctx->slot_pods;
+  size_t k = 0;
+  for (size_t off = 0; off < n; off += chunk, ++k) {
+    Slot& s = ctx->slot[k % kSlots];
+    const size_t m = (n - off < chunk) ? n - off : chunk;
+    cudaEvent_t a = next_event(ctx), b = next_event(ctx), c = next_event(ctx), d = next_event(ctx),
+                e = next_event(ctx), f = next_event(ctx);
+    if (!f) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
+    if (s.used) CU(cudaStreamWaitEvent(ctx->h2d_stream, s.free_ev, 0));
+    CU(cudaEventRecord(a, ctx->h2d_stream));
+    CU(cudaMemcpyAsync(s.ns, ns_id + off, m * 4, cudaMemcpyHostToDevice, ctx->h2d_stream));
+    for (int r = 0; r < R; ++r)
+      CU(cudaMemcpyAsync(s.req[r], req[r] + off, m * 8, cudaMemcpyHostToDevice, ctx->h2d_stream));
+    if (req_mask) CU(cudaMemcpyAsync(s.mask, req_mask + off, m, cudaMemcpyHostToDevice, ctx->h2d_stream));
+    CU(cudaEventRecord(b, ctx->h2d_stream));
+    CU(cudaEventRecord(s.h2d_done, ctx->h2d_stream));
+    CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+    CU(cudaEventRecord(c, ctx->own_stream));
+    if ((rc = launch_k2(ctx, ctx->own_stream, s.ns, s.req, req_mask ? s.mask : nullptr, m, s.out0))) return rc;
+    CU(cudaEventRecord(d, ctx->own_stream));
+    CU(cudaEventRecord(s.k_done, ctx->own_stream));
+    CU(cudaStreamWaitEvent(ctx->d2h_stream, s.k_done, 0));
+    CU(cudaEventRecord(e, ctx->d2h_stream));
+    CU(cudaMemcpyAsync(verdict + off, s.out0, m, cudaMemcpyDeviceToHost, ctx->d2h_stream));
+    CU(cudaEventRecord(f, ctx->d2h_stream));
+    CU(cudaEventRecord(s.free_ev, ctx->d2h_stream));
+    s.used = true;
+    sp.h2d.push_back(a); sp.h2d.push_back(b);
+    sp.k.push_back(c); sp.k.push_back(d);
+    sp.d2h.push_back(e); sp.d2h.push_back(f);
+  }
+  CU(cudaStreamSynchronize(ctx->d2h_stream));
+  return finish_timings(ctx, sp);
+}
+
+// ---------------------------------------------------------------- synthetic inputs / checksums
+int bgc_synth_pods_dev(bgc_ctx* ctx, const bgc_synth_params* p, uint64_t first, size_t count,
+                       uint32_t* d_ns_id, int64_t* const* d_req, uint8_t* d_req_mask) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(p && d_ns_id && d_req, "null pointer");
+  NEED(p->R >= 1 && p->R <= BGC_MAX_R, "R must be 1..BGC_MAX_R");
+  NEED(p->ns_count > 0, "ns_count must be positive");
+  NEED(p->dist != BGC_DIST_ZIPF_CDF || p->d_cdf, "zipf needs a device CDF table");
+  NEED(!p->grouped || p->n_total > 0, "grouped mode needs n_total");
+  if (count == 0) return BGC_OK;
+  CU(cudaSetDevice(ctx->device));
+  SynthArgs A{};
+  const uint32_t sbase = p->set * 16u;
+  A.key_ns = stream_key(p->seed, sbase + 0);
+  A.key_mask = stream_key(p->seed, sbase + 8);
+  for (uint32_t r = 0; r < p->R; ++r) {
+    A.key_req[r] = stream_key(p->seed, sbase + 1 + r);
+    A.kind[r] = p->kind[r];
+    A.req[r] = reinterpret_cast<long long*>(d_req[r]);
+    NEED(d_req[r], "null request column");
+  }
+  A.R = p->R; A.ns_count = p->ns_count; A.dist = p->dist; A.grouped = p->grouped;
+  A.step = p->n_total ? UINT64_MAX / p->n_total : 0;
+  A.a = p->scramble_a; A.b = p->scramble_b;
+  A.cdf = p->d_cdf; A.ns_id = d_ns_id; A.req_mask = d_req_mask;
+  const int grid = grid_for(count, 256, ctx->sm_count * 16);
+  k_synth_pods<<<grid, 256, 0, ctx->stream>>>(A, first, count);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+int bgc_synth_policy_dev(bgc_ctx* ctx, uint64_t seed, uint64_t first, size_t count, uint8_t* d_op,
+                         uint16_t* d_flags) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(d_op && d_flags, "null pointer");
+  if (count == 0) return BGC_OK;
+  CU(cudaSetDevice(ctx->device));
+  const int grid = grid_for(count, 256, ctx->sm_count * 16);
+  k_synth_policy<<<grid, 256, 0, ctx->stream>>>(stream_key(seed, 64), first, count, d_op, d_flags);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+int bgc_checksum_u8_dev(bgc_ctx* ctx, const uint8_t* d_v, uint64_t first, size_t count, uint64_t* out_host) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(out_host && (d_v || count == 0), "null pointer");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemsetAsync(ctx->d_scratch, 0, 8, ctx->stream));
+  if (count) {
+    const int grid = grid_for(count, 256, ctx->sm_count * 8);
+    k_checksum_u8<<<grid, 256, 0, ctx->stream>>>(d_v, first, count, ctx->d_scratch);
+    ctx->tm.launches++;
+    CU(cudaGetLastError());
+  }
+  CU(cudaMemcpyAsync(out_host, ctx->d_scratch, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return BGC_OK;
+}
+
+int bgc_histogram_u8_dev(bgc_ctx* ctx, const uint8_t* d_v, size_t count, uint64_t* out_host256) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(out_host256 && (d_v || count == 0), "null pointer");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemsetAsync(ctx->d_scratch, 0, 256 * 8, ctx->stream));
+  if (count) {
+    const int grid = grid_for(count, 256, ctx->sm_count * 4);
+    k_histogram_u8<<<grid, 256, 0, ctx->stream>>>(d_v, count, ctx->d_scratch);
+    ctx->tm.launches++;
+    CU(cudaGetLastError());
+  }
+  CU(cudaMemcpyAsync(out_host256, ctx->d_scratch, 256 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return BGC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,389 @@
+// bgc_host.cpp — host-side flattening and response rendering (include/bgc_host.h).
+//
+// Row A2: the string predicates mutate() evaluates (reference src/admission.rs:217-239, 263-270,
+// 312-386) become the (op, flags) columns K0 consumes.  Row A5: pod specs become the
+// (ns_id, req[r], req_mask) columns K1/K2 consume.  Plain C++17, no CUDA in this file; the only
+// device work is reached through the C ABI (bgc_policy_eval).
+#include <cstring>
+#include <string>
+#include <string_view>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/bgc_host.h"
+
+namespace {
+
+constexpr const char* kMessages[] = {
+    nullptr,
+    "cannot get requester's username from request",                                   // src/admission.rs:251
+    "user is not in authorized group",                                                // :277
+    "normal user is not allowed to delete resource",                                  // :287
+    "normal user is not allowed to update resource",                                  // :298
+    "invalid operation",                                                              // :306
+    "cannot get resource name from request",                                          // :324
+    "username not match with resource name",                                          // :333
+    "<serde error text: object is not a UserBootstrap>",                              // :345 (unpinned)
+    "kube_username field is empty. you are an admin, so fill it",                     // :369
+    "quota field is not empty. you are a normal user, so leave it empty",             // :379
+    "rolebinding field is not empty. you are a normal user, so leave it empty",       // :420
+    nullptr,
+    nullptr,
+};
+
+struct NameParts {
+  bool normal;
+  std::string_view kube_username;  // stripped for Normal, whole for Admin
+};
+
+// Username::from, src/admission.rs:217-239
+NameParts classify(std::string_view username, std::string_view prefix) {
+  if (username.substr(0, prefix.size()) == prefix) return {true, username.substr(prefix.size())};
+  return {false, username};
+}
+
+void json_escape(std::string& out, std::string_view s) {
+  out.push_back('"');
+  for (unsigned char c : s) {
+    switch (c) {
+      case '"': out += "\\\""; break;
+      case '\\': out += "\\\\"; break;
+      case '\n': out += "\\n"; break;
+      case '\r': out += "\\r"; break;
+      case '\t': out += "\\t"; break;
+      case '\b': out += "\\b"; break;
+      case '\f': out += "\\f"; break;
+      default:
+        if (c < 0x20) {
+          char b[8];
+          snprintf(b, sizeof b, "\\u%04x", c);
+          out += b;
+        } else {
+          out.push_back((char)c);
+        }
+    }
+  }
+  out.push_back('"');
+}
+
+}  // namespace
+
+struct bgc_nsmap {
+  std::unordered_map<std::string, uint32_t> ids;
+  std::vector<std::string> names;
+};
+
+extern "C" {
+
+size_t bgc_split_groups(const char* value, char* scratch, const char** out, size_t cap) {
+  size_t n = 0;
+  std::strcpy(scratch, value);
+  char* p = scratch;
+  for (;;) {
+    if (n < cap) out[n] = p;
+    ++n;
+    char* comma = std::strchr(p, ',');
+    if (!comma) break;
+    *comma = 0;
+    p = comma + 1;
+  }
+  return n;
+}
+
+const char* bgc_reason_message(int reason) {
+  if (reason < 0 || reason > 13) return nullptr;
+  return kMessages[reason];
+}
+
+int bgc_flatten_requests(const bgc_admission_config* cfg, const bgc_admission_request* reqs, size_t n,
+                         uint8_t* op, uint16_t* flags) {
+  if (!cfg || !cfg->oidc_username_prefix || (n && (!reqs || !op || !flags))) return BGC_E_BADARG;
+  const std::string_view prefix(cfg->oidc_username_prefix);
+  for (size_t i = 0; i < n; ++i) {
+    const bgc_admission_request& q = reqs[i];
+    unsigned f = 0;
+    NameParts who{false, {}};
+    if (q.username) {
+      f |= BGC_F_HAS_USERNAME;
+      who = classify(q.username, prefix);
+      if (who.normal) f |= BGC_F_IS_NORMAL;
+    }
+    // groups.iter().any(|g| authorized_group_names.contains(g)), src/admission.rs:263-270
+    bool in_group = false;
+    for (size_t g = 0; q.groups && g < q.n_groups && !in_group; ++g)
+      for (size_t a = 0; a < cfg->n_authorized; ++a)
+        if (std::strcmp(q.groups[g], cfg->authorized_group_names[a]) == 0) { in_group = true; break; }
+    if (in_group) f |= BGC_F_IN_GROUP;
+    if (q.has_object) {
+      f |= BGC_F_HAS_OBJECT;
+      if (q.name) {
+        f |= BGC_F_HAS_NAME;
+        if (q.username && who.kube_username == std::string_view(q.name)) f |= BGC_F_NAME_EQ;
+      }
+      if (q.parse_ok) {
+        f |= BGC_F_PARSE_OK;
+        if (q.spec_kube_username && q.spec_kube_username[0]) f |= BGC_F_KUBE_USERNAME_NONEMPTY;
+        if (q.has_quota) f |= BGC_F_HAS_QUOTA;
+        if (q.has_rolebinding) f |= BGC_F_HAS_ROLEBINDING;
+      }
+    }
+    op[i] = (uint8_t)((q.operation >= 0 && q.operation <= 2) ? q.operation : BGC_OP_OTHER);
+    flags[i] = (uint16_t)f;
+  }
+  return BGC_OK;
+}
+
+int bgc_mutate_batch(bgc_ctx* ctx, const bgc_admission_config* cfg, const bgc_admission_request* reqs,
+                     size_t n, bgc_admission_response* out) {
+  if (!ctx || (n && !out)) return BGC_E_BADARG;
+  std::vector<uint8_t> op(n), code(n), pm(n);
+  std::vector<uint16_t> flags(n);
+  int rc = bgc_flatten_requests(cfg, reqs, n, op.data(), flags.data());
+  if (rc) return rc;
+  rc = bgc_policy_eval(ctx, op.data(), flags.data(), n, code.data(), pm.data());
+  if (rc) return rc;
+  for (size_t i = 0; i < n; ++i) {
+    out[i].klass = code[i] >> 4;
+    out[i].reason = code[i] & 15;
+    out[i].patch_mask = pm[i];
+    out[i].allowed = out[i].klass <= BGC_ALLOW_PATCH;
+    out[i].message = bgc_reason_message(out[i].reason);
+  }
+  return BGC_OK;
+}
+
+long bgc_render_patch(const bgc_admission_config* cfg, const bgc_admission_request* req,
+                      uint8_t patch_mask, char* buf, size_t cap) {
+  if (!cfg || !req || !buf) return BGC_E_BADARG;
+  if (!(patch_mask & (BGC_P_USER | BGC_P_RB))) {
+    if (cap) buf[0] = 0;
+    return 0;
+  }
+  if (!req->username) return BGC_E_BADARG;
+  const NameParts who = classify(req->username, cfg->oidc_username_prefix);
+  std::string s = "[";
+  bool first = true;
+  if (patch_mask & BGC_P_USER) {  // src/admission.rs:354-357
+    s += "{\"op\":\"add\",\"path\":\"/spec/kube_username\",\"value\":";
+    json_escape(s, who.kube_username);
+    s += "}";
+    first = false;
+  }
+  if (patch_mask & BGC_P_RB) {  // src/admission.rs:387-416
+    if (!first) s += ",";
+    s += "{\"op\":\"add\",\"path\":\"/spec/rolebinding\",\"value\":{}},";
+    s += "{\"op\":\"add\",\"path\":\"/spec/rolebinding\",\"value\":{\"role_ref\":{\"apiGroup\":"
+         "\"rbac.authorization.k8s.io\",\"kind\":\"ClusterRole\",\"name\":";
+    json_escape(s, cfg->default_role_name ? cfg->default_role_name : "");
+    s += "},\"subjects\":[{\"apiGroup\":\"rbac.authorization.k8s.io\",\"kind\":\"User\",\"name\":";
+    const char* subject = (patch_mask & BGC_P_SUBJ_ORIG) ? req->username                      // :394
+                                                         : (req->spec_kube_username ? req->spec_kube_username : "");  // :396
+    json_escape(s, subject);
+    s += "}]}}";
+  }
+  s += "]";
+  if (s.size() + 1 > cap) return BGC_E_BADARG;
+  std::memcpy(buf, s.c_str(), s.size() + 1);
+  return (long)s.size();
+}
+
+// ------------------------------------------------------------------------------ row A5
+int bgc_parse_quantity(const char* s, int unit, int64_t* out) {
+  if (!s || !out) return BGC_E_BADARG;
+  const char* p = s;
+  bool neg = false;
+  if (*p == '+' || *p == '-') { neg = (*p == '-'); ++p; }
+  // mantissa digits → 128-bit integer and a decimal exponent
+  unsigned __int128 mant = 0;
+  int dec_exp = 0;
+  bool any = false, seen_dot = false;
+  const unsigned __int128 kLimit = (unsigned __int128)1 << 100;
+  for (;; ++p) {
+    if (*p >= '0' && *p <= '9') {
+      any = true;
+      if (mant >= kLimit) return BGC_E_BADARG;
+      mant = mant * 10 + (unsigned)(*p - '0');
+      if (seen_dot) --dec_exp;
+    } else if (*p == '.' && !seen_dot) {
+      seen_dot = true;
+    } else {
+      break;
+    }
+  }
+  if (!any) return BGC_E_BADARG;
+  int bin_exp = 0;
+  // suffix: binary SI, decimal SI, or decimal exponent
+  if (p[0] && p[1] == 'i' && !p[2]) {
+    switch (p[0]) {
+      case 'K': bin_exp = 10; break;
+      case 'M': bin_exp = 20; break;
+      case 'G': bin_exp = 30; break;
+      case 'T': bin_exp = 40; break;
+      case 'P': bin_exp = 50; break;
+      case 'E': bin_exp = 60; break;
+      default: return BGC_E_BADARG;
+    }
+  } else if ((p[0] == 'e' || p[0] == 'E') && (p[1] == '+' || p[1] == '-' || (p[1] >= '0' && p[1] <= '9'))) {
+    const char* e = p + 1;
+    bool eneg = false;
+    if (*e == '+' || *e == '-') { eneg = (*e == '-'); ++e; }
+    if (!(*e >= '0' && *e <= '9')) return BGC_E_BADARG;
+    int ev = 0;
+    for (; *e >= '0' && *e <= '9'; ++e) {
+      ev = ev * 10 + (*e - '0');
+      if (ev > 1000) return BGC_E_BADARG;
+    }
+    if (*e) return BGC_E_BADARG;
+    dec_exp += eneg ? -ev : ev;
+  } else if (p[0] && !p[1]) {
+    switch (p[0]) {
+      case 'n': dec_exp -= 9; break;
+      case 'u': dec_exp -= 6; break;
+      case 'm': dec_exp -= 3; break;
+      case 'k': dec_exp += 3; break;
+      case 'M': dec_exp += 6; break;
+      case 'G': dec_exp += 9; break;
+      case 'T': dec_exp += 12; break;
+      case 'P': dec_exp += 15; break;
+      case 'E': dec_exp += 18; break;
+      default: return BGC_E_BADARG;
+    }
+  } else if (p[0]) {
+    return BGC_E_BADARG;
+  }
+  if (unit == BGC_UNIT_MILLI) dec_exp += 3;
+  // value = mant * 2^bin_exp * 10^dec_exp, rounded away from zero for positives (ceil of |v|, as
+  // Kubernetes' Value()/MilliValue() round up)
+  if (mant == 0) { *out = 0; return BGC_OK; }
+  const unsigned __int128 kMax = (unsigned __int128)INT64_MAX;
+  for (; dec_exp > 0; --dec_exp) {
+    if (mant > kMax) return BGC_E_BADARG;
+    mant *= 10;
+  }
+  if (bin_exp) {
+    if (mant > (kMax >> 2)) {
+      // shifting would exceed 128 bits only for absurd inputs; reject instead
+      if (mant >> (127 - bin_exp)) return BGC_E_BADARG;
+    }
+    mant <<= bin_exp;
+  }
+  bool inexact = false;
+  for (; dec_exp < 0; ++dec_exp) {
+    if (mant % 10) inexact = true;
+    mant /= 10;
+    if (mant == 0 && dec_exp < -1) { dec_exp = -1; }
+  }
+  if (inexact && !neg) mant += 1;  // round up; negative values round toward zero (= up)
+  if (mant > kMax) return BGC_E_BADARG;
+  *out = neg ? -(int64_t)mant : (int64_t)mant;
+  return BGC_OK;
+}
+
+bgc_nsmap* bgc_nsmap_create(void) { return new (std::nothrow) bgc_nsmap; }
+void bgc_nsmap_destroy(bgc_nsmap* m) { delete m; }
+uint32_t bgc_nsmap_intern(bgc_nsmap* m, const char* name) {
+  auto it = m->ids.find(name);
+  if (it != m->ids.end()) return it->second;
+  const uint32_t id = (uint32_t)m->names.size();
+  m->names.emplace_back(name);
+  m->ids.emplace(m->names.back(), id);
+  return id;
+}
+uint32_t bgc_nsmap_lookup(const bgc_nsmap* m, const char* name) {
+  auto it = m->ids.find(name);
+  return it == m->ids.end() ? 0xFFFFFFFFu : it->second;
+}
+uint32_t bgc_nsmap_size(const bgc_nsmap* m) { return (uint32_t)m->names.size(); }
+const char* bgc_nsmap_name(const bgc_nsmap* m, uint32_t id) {
+  return id < m->names.size() ? m->names[id].c_str() : nullptr;
+}
+
+static int sum_list(const bgc_resource_list& l, const char* name, int unit, int64_t* v, bool* found) {
+  *found = false;
+  *v = 0;
+  for (size_t k = 0; k < l.n; ++k)
+    if (std::strcmp(l.names[k], name) == 0) {
+      *found = true;
+      return bgc_parse_quantity(l.quantities[k], unit, v);
+    }
+  return BGC_OK;
+}
+
+int bgc_flatten_pods(const bgc_pod_spec* pods, size_t n, const char* const* quota_keys,
+                     const uint8_t* unit, uint32_t R, bgc_nsmap* map, int intern, uint32_t* ns_id,
+                     int64_t* const* req, uint8_t* req_mask, size_t* n_out) {
+  if (!quota_keys || !unit || !map || !n_out || R < 1 || R > BGC_MAX_R) return BGC_E_BADARG;
+  if (n && (!pods || !ns_id || !req)) return BGC_E_BADARG;
+  struct Key { bool limits; const char* name; };
+  Key keys[BGC_MAX_R];
+  for (uint32_t r = 0; r < R; ++r) {
+    const char* k = quota_keys[r];
+    if (std::strncmp(k, "limits.", 7) == 0) keys[r] = {true, k + 7};
+    else if (std::strncmp(k, "requests.", 9) == 0) keys[r] = {false, k + 9};
+    else keys[r] = {false, k};
+  }
+  size_t w = 0;
+  for (size_t i = 0; i < n; ++i) {
+    const bgc_pod_spec& pod = pods[i];
+    if (pod.phase == BGC_PHASE_SUCCEEDED || pod.phase == BGC_PHASE_FAILED) continue;  // terminal pods hold no quota
+    unsigned mask = 0;
+    for (uint32_t r = 0; r < R; ++r) {
+      bool all_state = true;
+      uint64_t app = 0;
+      int64_t init_max = 0;
+      for (size_t c = 0; c < pod.n_containers; ++c) {
+        int64_t v; bool found;
+        const bgc_resource_list& l = keys[r].limits ? pod.containers[c].limits : pod.containers[c].requests;
+        if (int rc = sum_list(l, keys[r].name, unit[r], &v, &found)) return rc;
+        all_state = all_state && found;
+        app += (uint64_t)v;
+      }
+      for (size_t c = 0; c < pod.n_init_containers; ++c) {
+        int64_t v; bool found;
+        const bgc_resource_list& l = keys[r].limits ? pod.init_containers[c].limits : pod.init_containers[c].requests;
+        if (int rc = sum_list(l, keys[r].name, unit[r], &v, &found)) return rc;
+        all_state = all_state && found;
+        if (v > init_max) init_max = v;
+      }
+      int64_t total = (int64_t)app > init_max ? (int64_t)app : init_max;
+      if (pod.overhead) {
+        int64_t v; bool found;
+        if (int rc = sum_list(*pod.overhead, keys[r].name, unit[r], &v, &found)) return rc;
+        total = (int64_t)((uint64_t)total + (uint64_t)v);
+      }
+      req[r][w] = total;
+      if (all_state && pod.n_containers + pod.n_init_containers > 0) mask |= 1u << r;
+    }
+    ns_id[w] = intern ? bgc_nsmap_intern(map, pod.ns) : bgc_nsmap_lookup(map, pod.ns);
+    if (req_mask) req_mask[w] = (uint8_t)mask;
+    ++w;
+  }
+  *n_out = w;
+  return BGC_OK;
+}
+
+int bgc_hard_from_sheet_row(int64_t cpu_request, int64_t memory_request_gi, int64_t gpu_request,
+                            int64_t storage_request_gi, int64_t mig_request,
+                            const char* const* quota_keys, uint32_t R, int64_t* hard_out,
+                            uint8_t* unit_out) {
+  if (!quota_keys || !hard_out || !unit_out) return BGC_E_BADARG;
+  for (uint32_t r = 0; r < R; ++r) {
+    const std::string_view k(quota_keys[r]);
+    if (k == "requests.cpu" || k == "limits.cpu") {              // src/synchronizer.rs:251-253,259-261
+      hard_out[r] = cpu_request * 1000; unit_out[r] = BGC_UNIT_MILLI;
+    } else if (k == "requests.memory" || k == "limits.memory") { // :255-257,263-265 "<n>Gi"
+      hard_out[r] = (int64_t)((uint64_t)memory_request_gi << 30); unit_out[r] = BGC_UNIT_BYTES;
+    } else if (k == "requests.nvidia.com/gpu") {                 // :267-269
+      hard_out[r] = gpu_request; unit_out[r] = BGC_UNIT_COUNT;
+    } else if (k == "requests.storage") {                        // :271-273 "<n>Gi" (PVC-side key)
+      hard_out[r] = (int64_t)((uint64_t)storage_request_gi << 30); unit_out[r] = BGC_UNIT_COUNT;
+    } else if (k == "requests.nvidia.com/mig-1g.10gb") {         // :275-277
+      hard_out[r] = mig_request; unit_out[r] = BGC_UNIT_COUNT;
+    } else {
+      return BGC_E_BADARG;
+    }
+  }
+  return BGC_OK;
+}
+
+}  // extern "C"

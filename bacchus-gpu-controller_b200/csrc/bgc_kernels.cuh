@@ -1,0 +1,556 @@
+// bgc_kernels.cuh — sm_100a device code of libbgc.so.
+//
+// K0 policy_eval  : batched form of mutate(), reference src/admission.rs:241-431   (row A1)
+// K1 usage_reduce : per-namespace wrapping-i64 usage, no reference function        (row A3)
+// K2 quota_eval   : snapshot quota verdict per candidate pod, no reference function (row A4)
+//
+// All three are HBM-streaming integer kernels: no tensor cores, no TMEM.  What matters is
+// 128/256-bit coalesced read-only loads that bypass L1, enough loads in flight per thread, a
+// grid that is a multiple of the 148 SMs, and — for K1 — keeping the atomic traffic per pod low.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace bgc {
+
+constexpr int kMaxR = 4;
+constexpr uint32_t kBadNs = 0xFFFFFFFFu;
+
+// One namespace's quota state, one 64-byte line: w[2r] = used[r], w[2r+1] = hard[r];
+// for R <= 3, w[7] holds hard_mask so K2 needs a single gather per pod.
+struct __align__(64) QuotaRow {
+  long long w[8];
+};
+
+template <int R>
+struct ReqCols {
+  const long long* p[R];
+};
+
+// ------------------------------------------------------------------ load/store helpers
+__device__ __forceinline__ uint4 ldg_nc_u32x4(const uint32_t* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
+}
+// 256-bit streaming load (sm_100: LDG.E.256)
+__device__ __forceinline__ void ldg_nc_i64x4(const long long* p, long long (&v)[4]) {
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+               : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
+               : "l"(p));
+}
+// 256-bit gather of half a QuotaRow; table lines are re-used, so let them allocate in L1/L2
+__device__ __forceinline__ void ldg_row_half(const long long* p, long long (&v)[4]) {
+  asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];"
+               : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
+               : "l"(p));
+}
+__device__ __forceinline__ void red_add_i64(long long* p, long long v) {
+  asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ------------------------------------------------------------------ K0 policy_eval
+// Decision of one flattened request; restates src/admission.rs:241-431 in evaluation order.
+// Returns code | patch_mask << 8.
+__device__ __forceinline__ uint32_t policy_decide(uint32_t op, uint32_t f) {
+  const bool has_username = f & 1u, normal = f & 2u, in_group = f & 4u, has_object = f & 8u;
+  const bool has_name = f & 16u, name_eq = f & 32u, parse_ok = f & 64u, ku_nonempty = f & 128u;
+  const bool has_quota = f & 256u, has_rb = f & 512u;
+  auto ret = [](uint32_t klass, uint32_t reason, uint32_t patch) {
+    return (klass << 4) | reason | (patch << 8);
+  };
+  if (!has_username) return ret(3, 1, 0);                      // :248-255 invalid
+  if (op == 0) {                                               // Create :273-283
+    if (normal && !in_group) return ret(2, 2, 0);
+  } else if (op == 2) {                                        // Delete :284-294
+    return normal ? ret(2, 3, 0) : ret(0, 12, 0);
+  } else if (op == 1) {                                        // Update :295-304
+    if (normal) return ret(2, 4, 0);
+  } else {
+    return ret(3, 5, 0);                                       // :305-309 invalid operation
+  }
+  if (!has_object) return ret(0, 13, 0);                       // :312-318
+  if (!has_name) return ret(3, 6, 0);                          // :321-328
+  if (normal && !name_eq) return ret(2, 7, 0);                 // :331-338
+  if (!parse_ok) return ret(3, 8, 0);                          // :341-347
+  uint32_t patch = 0;
+  if (normal) patch |= 1;                                      // :352-358 P_USER
+  else if (!ku_nonempty) return ret(2, 9, 0);                  // :359-373
+  if (has_quota && normal) return ret(2, 10, 0);               // :376-383
+  if (!has_rb) patch |= normal ? (2u | 4u) : 2u;               // :386-416 P_RB (+ SUBJ_ORIG)
+  else if (normal) return ret(2, 11, 0);                       // :417-424
+  return ret(patch ? 1u : 0u, 0, patch);                       // :426-430
+}
+
+// The decision is a function of 12 bits, so each CTA tabulates it once (4096 x u16 = 8 KB of
+// shared memory) and the streaming loop is one LDS per request: 3 B in, 2 B out per request.
+constexpr int kK0Threads = 256;
+constexpr int kK0PerThread = 16;
+
+__global__ void __launch_bounds__(kK0Threads)
+k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flags, size_t n,
+               uint8_t* __restrict__ code, uint8_t* __restrict__ patch_mask, int vec_ok) {
+  __shared__ uint16_t lut[4096];
+  for (uint32_t i = threadIdx.x; i < 4096; i += kK0Threads)
+    lut[i] = (uint16_t)policy_decide(i >> 10, i & 1023u);
+  __syncthreads();
+
+  const size_t groups = vec_ok ? n / kK0PerThread : 0;
+  for (size_t g = (size_t)blockIdx.x * kK0Threads + threadIdx.x; g < groups;
+       g += (size_t)gridDim.x * kK0Threads) {
+    const size_t base = g * kK0PerThread;
+    const uint4 o = ldg_nc_u32x4(reinterpret_cast<const uint32_t*>(op + base));
+    const uint4 f0 = ldg_nc_u32x4(reinterpret_cast<const uint32_t*>(flags + base));
+    const uint4 f1 = ldg_nc_u32x4(reinterpret_cast<const uint32_t*>(flags + base + 8));
+    const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+    const uint32_t fw[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+    uint32_t cw[4], pw[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      uint32_t c = 0, p = 0;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const uint32_t o1 = (ow[w] >> (8 * b)) & 3u;  // anything outside 0..2 is "other"
+        const uint32_t raw = (ow[w] >> (8 * b)) & 0xFFu;
+        const uint32_t opv = raw > 2u ? 3u : o1;
+        const uint32_t fl = (fw[w * 2 + (b >> 1)] >> (16 * (b & 1))) & 1023u;
+        const uint32_t e = lut[(opv << 10) | fl];
+        c |= (e & 0xFFu) << (8 * b);
+        p |= (e >> 8) << (8 * b);
+      }
+      cw[w] = c;
+      pw[w] = p;
+    }
+    *reinterpret_cast<uint4*>(code + base) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+    *reinterpret_cast<uint4*>(patch_mask + base) = make_uint4(pw[0], pw[1], pw[2], pw[3]);
+  }
+  // scalar tail (and the whole batch when the pointers are not 16-byte aligned)
+  for (size_t i = groups * kK0PerThread + (size_t)blockIdx.x * kK0Threads + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * kK0Threads) {
+    const uint32_t raw = op[i];
+    const uint32_t e = lut[((raw > 2u ? 3u : raw) << 10) | (flags[i] & 1023u)];
+    code[i] = (uint8_t)(e & 0xFFu);
+    patch_mask[i] = (uint8_t)(e >> 8);
+  }
+}
+
+// ------------------------------------------------------------------ quota table maintenance
+// grid-stride over NS*R
+__global__ void k_rows_set_hard(QuotaRow* rows, const long long* __restrict__ hard,
+                                const uint8_t* __restrict__ hard_mask, uint32_t NS, int R) {
+  const size_t total = (size_t)NS * 8;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t ns = (uint32_t)(t >> 3), k = (uint32_t)(t & 7);
+    const int r = k >> 1;
+    long long v = 0;
+    if ((k & 1) && r < R) v = hard[(size_t)r * NS + ns];
+    if (k == 7 && R <= 3) v = hard_mask[ns];
+    rows[ns].w[k] = v;
+  }
+}
+__global__ void k_rows_clear_used(QuotaRow* rows, uint32_t NS, int R) {
+  const size_t total = (size_t)NS * R;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t ns = (uint32_t)(t / R);
+    const int r = (int)(t % R);
+    rows[ns].w[2 * r] = 0;
+  }
+}
+// used_out[r][ns] <- rows ; or rows <- used_in (set)
+__global__ void k_rows_export_used(const QuotaRow* __restrict__ rows, long long* used_out,
+                                   uint32_t NS, int R) {
+  const size_t total = (size_t)NS * R;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(t / NS);
+    const uint32_t ns = (uint32_t)(t % NS);
+    used_out[t] = rows[ns].w[2 * r];
+  }
+}
+__global__ void k_rows_import_used(QuotaRow* rows, const long long* __restrict__ used_in,
+                                   uint32_t NS, int R) {
+  const size_t total = (size_t)NS * R;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(t / NS);
+    const uint32_t ns = (uint32_t)(t % NS);
+    rows[ns].w[2 * r] = used_in[t];
+  }
+}
+
+// ------------------------------------------------------------------ K1 usage_reduce
+// One warp owns a contiguous chunk of pods and walks it in tiles of 128 (4 consecutive pods per
+// lane, so every warp-level load is a fully coalesced 512 B / 1 KB request).  Runs of equal
+// namespace are summed before anything is published:
+//   1. inside a lane (4 pods),
+//   2. across lanes with a segmented shuffle scan keyed on run boundaries,
+//   3. across tiles with a carry held by lane 0,
+// so pods grouped by namespace cost ~R atomics per 4096 pods, while fully shuffled input
+// degenerates to R updates per pod.  Updates go to one of three sinks:
+//   SINK_GLOBAL : red.global.add.u64 straight into the QuotaRow table (L2 atomics);
+//   SINK_DIRECT : CTA-private shared-memory table indexed by ns (NS*R*8 B must fit), flushed once;
+//   SINK_HASH   : CTA-private shared-memory table of S claim-once slots (hot namespaces claim
+//                 a slot first), cold namespaces fall through to global reds.
+// Shared-memory accumulators are split lo/hi u32 because ATOMS.ADD is native only for 32 bits
+// (a 64-bit shared atomicAdd compiles to a CAS spin loop): the carry out of the low word is
+// detected from the returned old value and folded into the high-word add, which is exact
+// modulo 2^64 under any interleaving.
+enum { SINK_GLOBAL = 0, SINK_DIRECT = 1, SINK_HASH = 2 };
+
+constexpr int kK1Tile = 128;            // pods per warp iteration
+constexpr uint32_t kHashEmpty = 0xFFFFFFFFu;
+
+template <int R, int SINK>
+struct K1Sink {
+  QuotaRow* rows;
+  uint32_t NS;
+  uint32_t* s_lo;   // [R][cap]
+  uint32_t* s_hi;   // [R][cap]
+  uint32_t* s_key;  // [cap] (hash)
+  uint32_t cap;     // NS (direct) or slots (hash, power of two)
+  uint32_t hash_shift;
+
+  __device__ __forceinline__ void smem_add(uint32_t idx, long long v) {
+    uint32_t lo = (uint32_t)(unsigned long long)v, hi = (uint32_t)((unsigned long long)v >> 32);
+    if (lo) {
+      const uint32_t old = atomicAdd(&s_lo[idx], lo);
+      hi += (old + lo < old);  // carry out of the low word
+    }
+    if (hi) atomicAdd(&s_hi[idx], hi);
+  }
+
+  __device__ __forceinline__ void add(uint32_t ns, const long long (&v)[R]) {
+    if (ns >= NS) return;  // kBadNs padding and out-of-range ids contribute nothing
+    if (SINK == SINK_GLOBAL) {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (v[r]) red_add_i64(&rows[ns].w[2 * r], v[r]);
+    } else if (SINK == SINK_DIRECT) {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (v[r]) smem_add(r * cap + ns, v[r]);
+    } else {
+      const uint32_t s = (ns * 0x9E3779B1u) >> hash_shift;
+      uint32_t k = s_key[s];
+      if (k == kHashEmpty) {
+        k = atomicCAS(&s_key[s], kHashEmpty, ns);
+        if (k == kHashEmpty) k = ns;
+      }
+      if (k == ns) {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if (v[r]) smem_add(r * cap + s, v[r]);
+      } else {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if (v[r]) red_add_i64(&rows[ns].w[2 * r], v[r]);
+      }
+    }
+  }
+};
+
+template <int R, int SINK, bool VEC>
+__global__ void __launch_bounds__(SINK == SINK_GLOBAL ? 512 : 1024, 1)
+k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRow* rows,
+                uint32_t NS, uint32_t cap, uint32_t chunk_tiles) {
+  extern __shared__ __align__(16) uint32_t k1_smem[];
+  K1Sink<R, SINK> sink;
+  sink.rows = rows;
+  sink.NS = NS;
+  sink.cap = cap;
+  sink.s_lo = k1_smem;
+  sink.s_hi = k1_smem + (size_t)R * cap;
+  sink.s_key = k1_smem + (size_t)2 * R * cap;
+  sink.hash_shift = 32 - (31 - __clz(cap | 1));
+  if (SINK != SINK_GLOBAL) {
+    for (uint32_t i = threadIdx.x; i < 2u * R * cap; i += blockDim.x) k1_smem[i] = 0;
+    if (SINK == SINK_HASH)
+      for (uint32_t i = threadIdx.x; i < cap; i += blockDim.x) sink.s_key[i] = kHashEmpty;
+    __syncthreads();
+  }
+
+  const uint32_t lane = threadIdx.x & 31u;
+  const size_t warps_total = (size_t)gridDim.x * (blockDim.x >> 5);
+  const size_t warp_global = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const size_t tiles = (n + kK1Tile - 1) / kK1Tile;
+  const size_t chunks = (tiles + chunk_tiles - 1) / chunk_tiles;
+
+  for (size_t c = warp_global; c < chunks; c += warps_total) {
+    const size_t t0 = c * chunk_tiles;
+    const size_t t1 = (t0 + chunk_tiles < tiles) ? t0 + chunk_tiles : tiles;
+    // carry = the still-open run at the end of the previous tile (meaningful on lane 0)
+    uint32_t carry_ns = kBadNs;
+    long long carry_v[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) carry_v[r] = 0;
+
+    for (size_t t = t0; t < t1; ++t) {
+      const size_t base = t * kK1Tile + lane * 4;
+      uint32_t ns[4];
+      long long q[R][4];
+      if (VEC && base + 4 <= n) {
+        const uint4 v = ldg_nc_u32x4(ns_id + base);
+        ns[0] = v.x; ns[1] = v.y; ns[2] = v.z; ns[3] = v.w;
+#pragma unroll
+        for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const bool ok = base + k < n;
+          ns[k] = ok ? ns_id[base + k] : kBadNs;
+#pragma unroll
+          for (int r = 0; r < R; ++r) q[r][k] = ok ? req.p[r][base + k] : 0;
+        }
+      }
+      // 1. runs inside the lane; interior runs are published by the lane itself
+      const uint32_t first_ns = ns[0];
+      uint32_t cur = ns[0];
+      long long acc[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[r] = q[r][0];
+      bool uniform = true;
+#pragma unroll
+      for (int k = 1; k < 4; ++k) {
+        if (ns[k] != cur) {
+          // the first run of a lane may continue the previous lane's run only when the lane is
+          // uniform; otherwise it is published here, which is still exact (sums commute)
+          sink.add(cur, acc);
+          cur = ns[k];
+          uniform = false;
+#pragma unroll
+          for (int r = 0; r < R; ++r) acc[r] = q[r][k];
+        } else {
+#pragma unroll
+          for (int r = 0; r < R; ++r) acc[r] += q[r][k];
+        }
+      }
+      // 2. segmented scan over the lanes' open (tail) runs
+      uint32_t prev_tail = __shfl_up_sync(0xFFFFFFFFu, cur, 1);
+      if (lane == 0) prev_tail = carry_ns;
+      const bool head = !uniform || first_ns != prev_tail;
+      const uint32_t heads = __ballot_sync(0xFFFFFFFFu, head);
+      if (lane == 0) {
+        if (head) {
+          sink.add(carry_ns, carry_v);  // the carried run ended at the tile boundary
+        } else {
+#pragma unroll
+          for (int r = 0; r < R; ++r) acc[r] += carry_v[r];
+        }
+      }
+      if (heads != 0xFFFFFFFFu) {  // at least one lane continues its predecessor
+        const uint32_t below = (heads | 1u) & (0xFFFFFFFFu >> (31u - lane));
+        const uint32_t dist = lane - (31u - __clz(below));
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const long long o = __shfl_up_sync(0xFFFFFFFFu, acc[r], d);
+            if (dist >= (uint32_t)d) acc[r] += o;
+          }
+        }
+      }
+      // a lane publishes its scanned run when the next lane starts a new one
+      const bool next_is_head = lane < 31u && ((heads >> (lane + 1u)) & 1u);
+      if (next_is_head) sink.add(cur, acc);
+      // 3. lane 31's run stays open and is carried to the next tile on lane 0
+      carry_ns = __shfl_sync(0xFFFFFFFFu, cur, 31);
+#pragma unroll
+      for (int r = 0; r < R; ++r) carry_v[r] = __shfl_sync(0xFFFFFFFFu, acc[r], 31);
+    }
+    if (lane == 0) sink.add(carry_ns, carry_v);
+  }
+
+  if (SINK != SINK_GLOBAL) {
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < R * cap; i += blockDim.x) {
+      const uint32_t r = i / cap, s = i - r * cap;
+      const unsigned long long v = ((unsigned long long)sink.s_hi[i] << 32) | sink.s_lo[i];
+      if (v) {
+        const uint32_t ns = (SINK == SINK_HASH) ? sink.s_key[s] : s;
+        red_add_i64(&rows[ns].w[2 * r], (long long)v);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ K2 quota_eval
+// 4 pods per thread: one 128-bit ns load, R 256-bit request loads, one (R<=2: half) QuotaRow
+// gather per pod, one 32-bit verdict store.  verdict = missing << 4 | exceeded.
+template <int R>
+__device__ __forceinline__ uint32_t quota_verdict(uint32_t ns, const long long (&q)[R], uint32_t rmask,
+                                                  const QuotaRow* __restrict__ rows,
+                                                  const uint8_t* __restrict__ hard_mask, uint32_t NS,
+                                                  uint32_t compute_mask) {
+  if (ns >= NS) return 0xFFu;
+  long long lo[4], hi[4];  // the whole 64-byte row: two 256-bit gathers of one line
+  ldg_row_half(&rows[ns].w[0], lo);
+  ldg_row_half(&rows[ns].w[4], hi);
+  const uint32_t hm = (R <= 3) ? (uint32_t)hi[3] : (uint32_t)hard_mask[ns];
+  uint32_t missing = 0, exceeded = 0;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const long long used = (r < 2) ? lo[2 * r] : hi[2 * (r - 2)];
+    const long long hard = (r < 2) ? lo[2 * r + 1] : hi[2 * (r - 2) + 1];
+    const bool constrained = (hm >> r) & 1u;
+    const bool present = (rmask >> r) & 1u;
+    const long long total = (long long)((unsigned long long)used + (unsigned long long)q[r]);
+    if (constrained && !present && ((compute_mask >> r) & 1u)) missing |= 1u << r;
+    if (constrained && present && q[r] > 0 && total > hard) exceeded |= 1u << r;
+  }
+  return (missing << 4) | exceeded;
+}
+
+constexpr int kK2Threads = 256;
+
+template <int R, bool HAS_MASK, bool VEC>
+__global__ void __launch_bounds__(kK2Threads)
+k2_quota_eval(const uint32_t* __restrict__ ns_id, ReqCols<R> req, const uint8_t* __restrict__ req_mask,
+              size_t n, const QuotaRow* __restrict__ rows, const uint8_t* __restrict__ hard_mask,
+              uint32_t NS, uint32_t compute_mask, uint8_t* __restrict__ verdict) {
+  const size_t groups = VEC ? n / 4 : 0;
+  for (size_t g = (size_t)blockIdx.x * kK2Threads + threadIdx.x; g < groups;
+       g += (size_t)gridDim.x * kK2Threads) {
+    const size_t base = g * 4;
+    const uint4 nv = ldg_nc_u32x4(ns_id + base);
+    const uint32_t ns[4] = {nv.x, nv.y, nv.z, nv.w};
+    long long q[R][4];
+#pragma unroll
+    for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
+    uint32_t rm = 0xFFFFFFFFu;
+    if (HAS_MASK) rm = __ldg(reinterpret_cast<const uint32_t*>(req_mask + base));
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      long long qk[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) qk[r] = q[r][k];
+      out |= quota_verdict<R>(ns[k], qk, (rm >> (8 * k)) & 0xFFu, rows, hard_mask, NS, compute_mask)
+             << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(verdict + base) = out;
+  }
+  for (size_t i = groups * 4 + (size_t)blockIdx.x * kK2Threads + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * kK2Threads) {
+    long long qk[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) qk[r] = req.p[r][i];
+    const uint32_t rm = HAS_MASK ? req_mask[i] : 0xFFu;
+    verdict[i] = (uint8_t)quota_verdict<R>(ns_id[i], qk, rm, rows, hard_mask, NS, compute_mask);
+  }
+}
+
+// ------------------------------------------------------------------ synthetic generator
+// Independent re-implementation of the generator spec of SURVEY.md §8(d) (integer only, so the
+// CPU oracle reproduces it bit for bit).
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__host__ __device__ __forceinline__ uint64_t stream_key(uint64_t seed, uint32_t stream) {
+  return mix64(seed ^ ((uint64_t)(stream + 1) * 0xD1B54A32D192ED03ull));
+}
+__host__ __device__ __forceinline__ uint64_t draw(uint64_t key, uint64_t index) {
+  return mix64(key ^ (index * 0x9E3779B97F4A7C15ull));
+}
+__device__ __forceinline__ long long synth_value(uint32_t kind, uint64_t h) {
+  const uint32_t t = (uint32_t)(h >> 32);
+  if (kind == 0) {
+    const uint32_t c = t % 100u;
+    return c < 50 ? 0 : c < 80 ? 1 : c < 90 ? 2 : c < 97 ? 4 : 8;
+  }
+  if (kind == 1) return 250ll << (t % 7u);
+  if (kind == 2) return 1ll << (28 + (t % 9u));
+  const uint32_t c = t % 100u;
+  return c < 90 ? 0 : c < 97 ? 1 : 2;
+}
+
+struct SynthArgs {
+  uint64_t key_ns, key_mask, key_req[kMaxR];
+  uint32_t kind[kMaxR];
+  uint32_t R, ns_count, dist, grouped;
+  uint64_t step, a, b;
+  const uint64_t* cdf;
+  uint32_t* ns_id;
+  long long* req[kMaxR];
+  uint8_t* req_mask;
+};
+
+__global__ void __launch_bounds__(256) k_synth_pods(SynthArgs A, uint64_t first, size_t count) {
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < count;
+       k += (size_t)gridDim.x * blockDim.x) {
+    const uint64_t i = first + k;
+    const uint64_t u = A.grouped ? i * A.step : draw(A.key_ns, i);
+    uint32_t rank;
+    if (A.dist == 1) {
+      uint32_t lo = 0, hi = A.ns_count;
+      while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (A.cdf[mid] > u) hi = mid; else lo = mid + 1;
+      }
+      rank = lo < A.ns_count ? lo : A.ns_count - 1;
+    } else {
+      rank = (uint32_t)(((u >> 32) * (uint64_t)A.ns_count) >> 32);
+    }
+    A.ns_id[k] = (uint32_t)(((uint64_t)rank * A.a + A.b) % A.ns_count);
+    for (uint32_t r = 0; r < A.R; ++r) A.req[r][k] = synth_value(A.kind[r], draw(A.key_req[r], i));
+    if (A.req_mask) {
+      const uint64_t h = draw(A.key_mask, i);
+      uint32_t m = 0xFFu;
+      for (uint32_t r = 0; r < A.R; ++r)
+        if (((h >> (8 * r)) & 0xFFu) < 8u) m &= ~(1u << r);
+      A.req_mask[k] = (uint8_t)m;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_synth_policy(uint64_t key, uint64_t first, size_t count, uint8_t* op, uint16_t* flags) {
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < count;
+       k += (size_t)gridDim.x * blockDim.x) {
+    const uint64_t h = draw(key, first + k);
+    op[k] = (uint8_t)(h & 3u);
+    flags[k] = (uint16_t)((h >> 8) & 0x3FFu);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_checksum_u8(const uint8_t* __restrict__ v, uint64_t first, size_t count, unsigned long long* out) {
+  unsigned long long s = 0;
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < count;
+       k += (size_t)gridDim.x * blockDim.x)
+    s += mix64((first + k) ^ ((uint64_t)v[k] << 56));
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, d);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
+__global__ void __launch_bounds__(256)
+k_histogram_u8(const uint8_t* __restrict__ v, size_t count, unsigned long long* out256) {
+  __shared__ unsigned int h[256];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  // uniform trip count per CTA, so the periodic flush (u32 bins cannot overflow) may sync
+  unsigned int done = 0;
+  for (size_t base = (size_t)blockIdx.x * blockDim.x; base < count;
+       base += (size_t)gridDim.x * blockDim.x) {
+    const size_t k = base + threadIdx.x;
+    if (k < count) atomicAdd(&h[v[k]], 1u);
+    if (++done == (1u << 20)) {
+      __syncthreads();
+      if (h[threadIdx.x]) atomicAdd(&out256[threadIdx.x], (unsigned long long)h[threadIdx.x]);
+      h[threadIdx.x] = 0;
+      done = 0;
+      __syncthreads();
+    }
+  }
+  __syncthreads();
+  if (h[threadIdx.x]) atomicAdd(&out256[threadIdx.x], (unsigned long long)h[threadIdx.x]);
+}
+
+}  // namespace bgc

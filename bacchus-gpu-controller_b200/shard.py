@@ -1,0 +1,49 @@
+"""Row E: namespace-hash sharding across GPUs (north_star).
+
+`shard = mix32(ns_id) % G`: every pod of a namespace lands on one rank, so each rank owns a
+disjoint slice of the usage/hard tables and produces final verdicts for its own pods with no
+data-path collective; the host only gathers.  Used by bench.py (one process per GPU under
+torchrun) and tested with world_size-2 gloo on CPU (tests/test_shard.py).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def mix32(x: np.ndarray) -> np.ndarray:
+    """Integer finaliser (murmur3 fmix32) — spreads dense ids over ranks."""
+    x = x.astype(np.uint32, copy=True)
+    x ^= x >> np.uint32(16)
+    x *= np.uint32(0x85EBCA6B)
+    x ^= x >> np.uint32(13)
+    x *= np.uint32(0xC2B2AE35)
+    x ^= x >> np.uint32(16)
+    return x
+
+
+def shard_of(ns_id: np.ndarray, world: int) -> np.ndarray:
+    return (mix32(ns_id) % np.uint32(world)).astype(np.uint32)
+
+
+def partition(ns_id: np.ndarray, cols: list, world: int):
+    """Host partition pass: returns, per rank, (index array into the batch, ns_id slice, column slices).
+    This is itself a full pass over the batch on the CPU — the cost SURVEY.md §8(e) says to state."""
+    s = shard_of(ns_id, world)
+    out = []
+    for g in range(world):
+        idx = np.nonzero(s == g)[0]
+        out.append((idx, ns_id[idx], [c[idx] for c in cols]))
+    return out
+
+
+def gather_verdicts(n: int, parts: list) -> np.ndarray:
+    """Host gather: parts = [(index array, verdict array)] from every rank."""
+    out = np.empty(n, np.uint8)
+    for idx, v in parts:
+        out[idx] = v
+    return out
+
+
+def owned_namespaces(NS: int, world: int, rank: int) -> np.ndarray:
+    ids = np.arange(NS, dtype=np.uint32)
+    return ids[shard_of(ids, world) == rank]

@@ -1,0 +1,139 @@
+/* bgc_host.h — host-side half of the boundary (libbgc.so, plain C++ behind a C ABI).
+ *
+ * Mirrors the reference's handler interface for the admission path: the same inputs the
+ * reference's `mutate(req, state)` reads (src/admission.rs:241-431), flattened on the host into
+ * the integer columns the kernels consume, and the response fields
+ * it produces.  The reference is Rust; with no Rust toolchain in this image the host layer is
+ * C++ exporting C symbols, which is what a Rust `extern "C"` block binds to.
+ */
+#ifndef BGC_HOST_H
+#define BGC_HOST_H
+#include "bgc.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- row A2: the fields mutate() reads from Config / AdmissionRequest ----------------------- */
+/* reference: struct Config, src/admission.rs:22-39 (only what mutate() uses) */
+typedef struct bgc_admission_config {
+  const char *oidc_username_prefix;          /* src/admission.rs:33  */
+  const char *default_role_name;             /* src/admission.rs:35  */
+  const char *const *authorized_group_names; /* src/admission.rs:38  */
+  size_t n_authorized;
+} bgc_admission_config;
+
+/* reference: AdmissionRequest<DynamicObject> as consumed by mutate() */
+typedef struct bgc_admission_request {
+  const char *username;           /* req.user_info.username; NULL = None   src/admission.rs:248 */
+  const char *const *groups;      /* req.user_info.groups;   NULL = None   src/admission.rs:263-267 */
+  size_t n_groups;
+  int operation;                  /* BGC_OP_*                               src/admission.rs:272 */
+  int has_object;                 /* req.object.is_some()                   src/admission.rs:312 */
+  const char *name;               /* obj.metadata.name; NULL = None         src/admission.rs:321 */
+  int parse_ok;                   /* obj parses as UserBootstrap            src/admission.rs:341 */
+  const char *spec_kube_username; /* ub.spec.kube_username; NULL = None     src/admission.rs:362-367 */
+  int has_quota;                  /* ub.spec.quota.is_some()                src/admission.rs:376 */
+  int has_rolebinding;            /* ub.spec.rolebinding.is_some()          src/admission.rs:386 */
+} bgc_admission_request;
+
+/* reference: AdmissionResponse fields set by mutate() (allowed, result.message, patch) */
+typedef struct bgc_admission_response {
+  uint8_t allowed;     /* 1 for ALLOW / ALLOW_PATCH */
+  uint8_t klass;       /* BGC_ALLOW .. BGC_INVALID */
+  uint8_t reason;      /* BGC_R_* */
+  uint8_t patch_mask;  /* BGC_P_* */
+  const char *message; /* static literal from src/admission.rs, NULL when allowed */
+} bgc_admission_response;
+
+/* comma_separated_deserialize, src/admission.rs:41-50: split on ',' without trimming, "" → [""].
+ * `scratch` must hold strlen(value)+1 bytes; returns the number of items (may exceed cap). */
+size_t bgc_split_groups(const char *value, char *scratch, const char **out, size_t cap);
+
+/* strings → (op, flags) columns; the string predicates of src/admission.rs:217-239,263-270,
+ * 312,321,332,341,362-367,376,386 */
+int bgc_flatten_requests(const bgc_admission_config *cfg, const bgc_admission_request *reqs, size_t n,
+                         uint8_t *op, uint16_t *flags);
+
+/* exact message literal of a reason (src/admission.rs:251,277,287,298,306,324,333,369,379,420);
+ * NULL for allow reasons; a placeholder for BGC_R_NOT_USERBOOTSTRAP (serde text, unpinned) */
+const char *bgc_reason_message(int reason);
+
+/* batched mutate(): flatten on the host, decide on the GPU (bgc_policy_eval), fill responses.
+ * Error convention follows the reference: a decision is never an error (deny/invalid are
+ * ordinary responses, src/admission.rs:253,279,...); only library failures return non-zero. */
+int bgc_mutate_batch(bgc_ctx *ctx, const bgc_admission_config *cfg, const bgc_admission_request *reqs,
+                     size_t n, bgc_admission_response *out);
+
+/* JSON-patch text the reference would attach (src/admission.rs:354-357,387-416,429) for one
+ * request, in push order.  Returns the length written (excluding NUL), 0 when there is no
+ * patch, or a negative BGC_E_* (buffer too small → BGC_E_BADARG).  Byte-level parity with
+ * json-patch 1.0 / serde_json is unpinned; field order follows k8s-openapi
+ * 0.18 RoleRef/Subject declaration order. */
+long bgc_render_patch(const bgc_admission_config *cfg, const bgc_admission_request *req,
+                      uint8_t patch_mask, char *buf, size_t cap);
+
+/* ---- row A5: pod specs → resource columns ----------------------------------------------------
+ * No reference function (the reference never reads pods).  Rules = public Kubernetes pod-usage
+ * semantics for the quota keys written at src/synchronizer.rs:249-281. */
+typedef struct bgc_resource_list {
+  const char *const *names;      /* e.g. "cpu", "memory", "nvidia.com/gpu" */
+  const char *const *quantities; /* Kubernetes quantity strings: "500m", "2", "4Gi", "1e3" */
+  size_t n;
+} bgc_resource_list;
+
+typedef struct bgc_container_spec {
+  bgc_resource_list requests;
+  bgc_resource_list limits;
+} bgc_container_spec;
+
+enum { BGC_PHASE_PENDING = 0, BGC_PHASE_RUNNING = 1, BGC_PHASE_SUCCEEDED = 2, BGC_PHASE_FAILED = 3, BGC_PHASE_UNKNOWN = 4 };
+
+typedef struct bgc_pod_spec {
+  const char *ns; /* namespace name; the reference names it after the lowercased UserBootstrap, src/controller.rs:55-63 */
+  int phase;
+  const bgc_container_spec *containers;
+  size_t n_containers;
+  const bgc_container_spec *init_containers;
+  size_t n_init_containers;
+  const bgc_resource_list *overhead; /* may be NULL */
+} bgc_pod_spec;
+
+/* quantity string → canonical integer (BGC_UNIT_MILLI: millicores; otherwise whole units), rounding
+ * up like Kubernetes' Quantity.MilliValue()/Value().  Returns BGC_E_BADARG on syntax error or
+ * overflow. */
+int bgc_parse_quantity(const char *s, int unit, int64_t *out);
+
+/* namespace name ↔ dense u32 id */
+typedef struct bgc_nsmap bgc_nsmap;
+bgc_nsmap *bgc_nsmap_create(void);
+void bgc_nsmap_destroy(bgc_nsmap *m);
+uint32_t bgc_nsmap_intern(bgc_nsmap *m, const char *name);        /* id, assigning the next one if new */
+uint32_t bgc_nsmap_lookup(const bgc_nsmap *m, const char *name);  /* id or 0xFFFFFFFF */
+uint32_t bgc_nsmap_size(const bgc_nsmap *m);
+const char *bgc_nsmap_name(const bgc_nsmap *m, uint32_t id);
+
+/* Flatten n pod specs into columns.  quota_keys[r] is a ResourceQuota key as written by the
+ * reference ("requests.cpu", "limits.memory", "requests.nvidia.com/gpu", ...,
+ * src/synchronizer.rs:251-279): the "limits." prefix selects container limits, anything else
+ * container requests.  Per resource: max(Σ containers, max over init containers) + overhead.
+ * Terminal pods (Succeeded/Failed) are skipped.  req_mask bit r is set when every container states
+ * the resource.  Unknown namespaces are interned when `intern` != 0, else get id 0xFFFFFFFF.
+ * Returns the number of rows written through *n_out. */
+int bgc_flatten_pods(const bgc_pod_spec *pods, size_t n, const char *const *quota_keys,
+                     const uint8_t *unit, uint32_t R, bgc_nsmap *map, int intern, uint32_t *ns_id,
+                     int64_t *const *req, uint8_t *req_mask, size_t *n_out);
+
+/* the `hard` values the reference's synchronizer writes for one sheet row
+ * (src/synchronizer.rs:249-281), in canonical units, for the given quota keys:
+ * cpu → cpu_request*1000 millicores, memory/storage → <n>Gi bytes, gpu/mig → count.
+ * Unknown keys yield BGC_E_BADARG. */
+int bgc_hard_from_sheet_row(int64_t cpu_request, int64_t memory_request_gi, int64_t gpu_request,
+                            int64_t storage_request_gi, int64_t mig_request,
+                            const char *const *quota_keys, uint32_t R, int64_t *hard_out,
+                            uint8_t *unit_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BGC_HOST_H */

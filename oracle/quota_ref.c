@@ -1,0 +1,165 @@
+/* oracle/quota_ref.c — TEST INFRASTRUCTURE ONLY.  See quota_ref.h: PARITY UNPINNED (the
+ * reference implements none of this; spec source = synchronizer.rs:249-281 key set + public
+ * Kubernetes ResourceQuota semantics, restated in SURVEY.md §8 rows A3/A4). */
+#include "quota_ref.h"
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+static inline int nthreads(int threads) { return threads > 0 ? threads : 1; }
+
+void quota_ref_usage_reduce(const uint32_t *ns_id, const int64_t *const *req, size_t n,
+                            uint32_t NS, uint32_t R, int64_t *used, int threads) {
+  const size_t tab = (size_t)R * NS;
+  memset(used, 0, tab * sizeof(int64_t));
+  const int T = nthreads(threads);
+  if (T == 1) {
+    /* the literal loop */
+    for (size_t i = 0; i < n; ++i) {
+      uint32_t ns = ns_id[i];
+      if (ns >= NS) continue;
+      for (uint32_t r = 0; r < R; ++r)
+        used[(size_t)r * NS + ns] = (int64_t)((uint64_t)used[(size_t)r * NS + ns] + (uint64_t)req[r][i]);
+    }
+    return;
+  }
+#ifdef _OPENMP
+  /* all-cores baseline: per-thread private tables merged at the end */
+  uint64_t *priv = (uint64_t *)calloc((size_t)T * tab, sizeof(uint64_t));
+#pragma omp parallel num_threads(T)
+  {
+    uint64_t *mine = priv + (size_t)omp_get_thread_num() * tab;
+#pragma omp for schedule(static)
+    for (long long i = 0; i < (long long)n; ++i) {
+      uint32_t ns = ns_id[i];
+      if (ns >= NS) continue;
+      for (uint32_t r = 0; r < R; ++r) mine[(size_t)r * NS + ns] += (uint64_t)req[r][i];
+    }
+#pragma omp for schedule(static)
+    for (long long k = 0; k < (long long)tab; ++k) {
+      uint64_t s = 0;
+      for (int t = 0; t < T; ++t) s += priv[(size_t)t * tab + k];
+      used[k] = (int64_t)s;
+    }
+  }
+  free(priv);
+#else
+  quota_ref_usage_reduce(ns_id, req, n, NS, R, used, 1);
+#endif
+}
+
+static inline uint8_t eval_one(uint32_t ns, const int64_t *const *req, uint8_t rmask, size_t j,
+                               uint32_t NS, uint32_t R, const int64_t *used, const int64_t *hard,
+                               const uint8_t *hard_mask, uint8_t compute_mask) {
+  if (ns >= NS) return QUOTA_REF_VERDICT_BAD_NS;
+  const uint8_t hm = hard_mask[ns];
+  unsigned missing = 0, exceeded = 0;
+  for (uint32_t r = 0; r < R; ++r) {
+    if (!((hm >> r) & 1)) continue;               /* resource not constrained in this namespace */
+    if (!((rmask >> r) & 1)) {                    /* pod does not state this resource */
+      if ((compute_mask >> r) & 1) missing |= 1u << r;
+      continue;
+    }
+    const int64_t q = req[r][j];
+    if (q <= 0) continue;
+    const int64_t total = (int64_t)((uint64_t)used[(size_t)r * NS + ns] + (uint64_t)q);
+    if (total > hard[(size_t)r * NS + ns]) exceeded |= 1u << r;
+  }
+  return (uint8_t)((missing << 4) | exceeded);
+}
+
+void quota_ref_quota_eval(const uint32_t *ns_id, const int64_t *const *req,
+                          const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
+                          const int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
+                          uint8_t compute_mask, uint8_t *verdict, int threads) {
+  (void)threads;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthreads(threads))
+#endif
+  for (long long j = 0; j < (long long)n; ++j)
+    verdict[j] = eval_one(ns_id[j], req, req_mask ? req_mask[j] : 0xFF, (size_t)j, NS, R, used,
+                          hard, hard_mask, compute_mask);
+}
+
+/* ------------------------------------------------------------------ generator spec */
+static inline uint64_t sm64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+uint64_t gen_ref_hash(uint64_t seed, uint32_t stream, uint64_t index) {
+  const uint64_t key = sm64(seed ^ ((uint64_t)(stream + 1) * 0xD1B54A32D192ED03ull));
+  return sm64(key ^ (index * 0x9E3779B97F4A7C15ull));
+}
+
+static inline uint32_t upper_bound_u64(const uint64_t *a, uint32_t n, uint64_t u) {
+  uint32_t lo = 0, hi = n; /* first k with a[k] > u */
+  while (lo < hi) {
+    uint32_t mid = lo + ((hi - lo) >> 1);
+    if (a[mid] > u) hi = mid; else lo = mid + 1;
+  }
+  return lo < n ? lo : n - 1;
+}
+
+static inline int64_t gen_value(uint32_t kind, uint64_t h) {
+  const uint32_t t = (uint32_t)(h >> 32);
+  switch (kind) {
+    case GEN_KIND_GPU: { /* {0,1,2,4,8} w.p. {.5,.3,.1,.07,.03} */
+      uint32_t c = t % 100u;
+      return c < 50 ? 0 : c < 80 ? 1 : c < 90 ? 2 : c < 97 ? 4 : 8;
+    }
+    case GEN_KIND_CPU_MILLI: return (int64_t)250 << (t % 7u);          /* 250..16000 millicores */
+    case GEN_KIND_MEM_BYTES: return (int64_t)1 << (28 + (t % 9u));     /* 2^28..2^36 bytes */
+    default: { uint32_t c = t % 100u; return c < 90 ? 0 : c < 97 ? 1 : 2; } /* MIG slices */
+  }
+}
+
+void gen_ref_fill(const gen_ref_params *p, uint64_t first, size_t count, uint32_t *ns_id,
+                  int64_t *const *req, uint8_t *req_mask, int threads) {
+  (void)threads;
+  const uint32_t sbase = p->set * 16u;
+  const uint64_t step = p->n_total ? UINT64_MAX / p->n_total : 0;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthreads(threads))
+#endif
+  for (long long k = 0; k < (long long)count; ++k) {
+    const uint64_t i = first + (uint64_t)k;
+    const uint64_t u = p->grouped ? i * step : gen_ref_hash(p->seed, sbase + 0, i);
+    uint32_t rank;
+    if (p->dist == GEN_DIST_ZIPF_CDF) rank = upper_bound_u64(p->cdf, p->ns_count, u);
+    else rank = (uint32_t)(((u >> 32) * (uint64_t)p->ns_count) >> 32);
+    ns_id[k] = (uint32_t)(((uint64_t)rank * p->scramble_a + p->scramble_b) % p->ns_count);
+    for (uint32_t r = 0; r < p->R; ++r)
+      req[r][k] = gen_value(p->kind[r], gen_ref_hash(p->seed, sbase + 1 + r, i));
+    if (req_mask) {
+      const uint64_t h = gen_ref_hash(p->seed, sbase + 8, i);
+      unsigned m = 0xFF;
+      for (uint32_t r = 0; r < p->R; ++r)
+        if (((h >> (8 * r)) & 0xFF) < 8) m &= ~(1u << r); /* ~3 % of pods omit resource r */
+      req_mask[k] = (uint8_t)m;
+    }
+  }
+}
+
+void gen_ref_policy_fill(uint64_t seed, uint64_t first, size_t count, uint8_t *op,
+                         uint16_t *flags, int threads) {
+  (void)threads;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthreads(threads))
+#endif
+  for (long long k = 0; k < (long long)count; ++k) {
+    const uint64_t h = gen_ref_hash(seed, 64, first + (uint64_t)k);
+    op[k] = (uint8_t)(h & 3);
+    flags[k] = (uint16_t)((h >> 8) & 0x3FF);
+  }
+}
+
+uint64_t gen_ref_checksum_u8(const uint8_t *v, uint64_t first, size_t count) {
+  uint64_t s = 0;
+  for (size_t k = 0; k < count; ++k) s += sm64((first + k) ^ ((uint64_t)v[k] << 56));
+  return s;
+}

@@ -1,0 +1,150 @@
+"""CPU tests: the C++ host layer of libbgc (rows A2, A5, and the response renderer) against the
+oracle's restatements.  No GPU calls."""
+import json
+
+import numpy as np
+import pytest
+
+from oracle import policy_ref as P
+
+
+def test_flatten_requests_matches_oracle_on_every_constructible_request(bgc, oracle):
+    A = bgc.admission
+    cfg_py = P.Config()
+    cfg = A.AdmissionConfig()
+    reviews, expect = [], []
+    for op in range(4):
+        for fl in range(1024):
+            req = P.request_from_bits(op, fl, cfg_py)
+            if req is not None:
+                reviews.append(req)
+                expect.append((op, fl))
+    reqs = [A.AdmissionRequest.from_review(r) for r in reviews]
+    op, flags = A.flatten_requests(cfg, reqs)
+    assert [(int(o), int(f)) for o, f in zip(op, flags)] == expect
+
+
+@pytest.mark.parametrize("prefix,groups", [("oidc:", ["gpu", "admin"]), ("", ["gpu"]), ("oidc:", [""]), ("sso/", ["a", " b"])])
+def test_flatten_requests_string_edge_cases(bgc, oracle, prefix, groups):
+    A = bgc.admission
+    cfg = A.AdmissionConfig(prefix, "edit", groups)
+    names = [None, "", "alice", "Alice", "oidc:alice", "sso/al"]
+    users = [None, "", prefix, prefix + "alice", "alice", "admin", "sso/al"]
+    glists = [None, [], ["gpu"], [""], [" b"], ["x", "admin"]]
+    reqs, expect = [], []
+    for u in users:
+        for nm in names:
+            for g in glists:
+                for op in (0, 1, 2, 3, 7):
+                    for ku in (None, "", "bob"):
+                        q = dict(username=u, groups=g, operation=op, has_object=True, name=nm, parse_ok=True,
+                                 spec_kube_username=ku, has_quota=bool(op & 1), has_rolebinding=bool(op & 2))
+                        reqs.append(A.AdmissionRequest(**q))
+                        expect.append(oracle.policy_flatten_strings((prefix, "edit", groups), **q))
+    op, flags = A.flatten_requests(cfg, reqs)
+    assert [(int(o), int(f)) for o, f in zip(op, flags)] == expect
+
+
+def test_split_groups_matches_reference_semantics(bgc, oracle):
+    for s in ["", "gpu,admin", "gpu, admin,", ",", "a,,b", "한글,gpu"]:
+        assert bgc.admission.split_groups(s) == s.split(",") == oracle.split_groups(s)
+
+
+def test_reason_messages_are_the_reference_literals(bgc):
+    for reason, (_, msg, _line) in P.REASONS.items():
+        got = bgc.lib.bgc_reason_message(reason)
+        if reason != 8:
+            assert (None if got is None else got.decode()) == msg
+
+
+def test_render_patch_equals_python_oracle_patches(bgc):
+    A = bgc.admission
+    cfg_py, cfg = P.Config(), A.AdmissionConfig()
+    seen = 0
+    for op in range(2):
+        for fl in range(1024):
+            rv = P.request_from_bits(op, fl, cfg_py)
+            if rv is None:
+                continue
+            d = P.mutate(rv, cfg_py)
+            txt = A.render_patch(cfg, A.AdmissionRequest.from_review(rv), d.patch_mask)
+            if d.patch_mask:
+                assert json.loads(txt) == d.patches
+                assert list(json.loads(txt)[-1]["value"].keys()) == ["role_ref", "subjects"] or not (d.patch_mask & 2)
+                seen += 1
+            else:
+                assert txt is None
+    assert seen > 10
+    # JSON escaping of odd user names
+    q = A.AdmissionRequest('oidc:a"b\\c\n', ["gpu"], 0, True, 'a"b\\c\n')
+    assert json.loads(A.render_patch(cfg, q, 7))[0]["value"] == 'a"b\\c\n'
+
+
+QUANT = [
+    ("0", 0, 0), ("1", 0, 1), ("500m", 1, 500), ("2", 1, 2000), ("0.5", 1, 500), ("1.5", 0, 2), ("100m", 0, 1),
+    ("1Ki", 2, 1024), ("4Gi", 2, 4 << 30), ("1.5Gi", 2, 1610612736), ("1e3", 0, 1000), ("1E3", 0, 1000),
+    ("1e-3", 1, 1), ("129M", 2, 129_000_000), ("1k", 0, 1000), ("5n", 1, 1), ("250u", 1, 1), ("12345678901", 0, 12345678901),
+    ("8Ei", 2, None), ("+3", 0, 3), ("-1", 0, -1), ("2Ti", 2, 2 << 40), ("0.1Ki", 2, 103), ("16", 1, 16000),
+]
+
+
+@pytest.mark.parametrize("s,unit,want", QUANT)
+def test_parse_quantity(bgc, s, unit, want):
+    if want is None:
+        with pytest.raises(ValueError):
+            bgc.pods.parse_quantity(s, unit)
+    else:
+        assert bgc.pods.parse_quantity(s, unit) == want
+
+
+@pytest.mark.parametrize("bad", ["", "abc", "1x", "1Kii", "1e", "--1", "1.2.3", "Gi", "1 Gi"])
+def test_parse_quantity_rejects(bgc, bad):
+    with pytest.raises(ValueError):
+        bgc.pods.parse_quantity(bad, 0)
+
+
+def _pod(ns, containers, init=None, overhead=None, phase="Running"):
+    def c(req, lim=None):
+        return {"resources": {"requests": req, **({"limits": lim} if lim else {})}}
+    return {"metadata": {"namespace": ns}, "status": {"phase": phase},
+            "spec": {"containers": [c(*x) if isinstance(x, tuple) else c(x) for x in containers],
+                     **({"initContainers": [c(x) for x in init]} if init else {}),
+                     **({"overhead": overhead} if overhead else {})}}
+
+
+def test_flatten_pods_usage_rules(bgc):
+    Pd = bgc.pods
+    keys = ["requests.nvidia.com/gpu", "requests.cpu", "limits.memory"]
+    m = Pd.NamespaceMap()
+    pods = [
+        _pod("alice", [({"cpu": "500m", "nvidia.com/gpu": "1"}, {"memory": "1Gi"}), ({"cpu": "1"}, {"memory": "512Mi"})]),
+        _pod("bob", [{"cpu": "100m"}], init=[{"cpu": "2"}, {"cpu": "1"}], overhead={"cpu": "250m"}),
+        _pod("alice", [{"cpu": "8"}], phase="Succeeded"),          # terminal → skipped
+        _pod("carol", [{"memory": "1Gi"}]),                        # states no cpu → mask bit clear
+        _pod("alice", [{"cpu": "1"}], phase="Failed"),
+    ]
+    ns, req, mask, unit = Pd.flatten_pods(pods, keys, m)
+    assert ns.tolist() == [0, 1, 2] and len(m) == 3 and m.name(1) == "bob" and m.lookup("nobody") == 0xFFFFFFFF
+    assert req[0].tolist() == [1, 0, 0]
+    assert req[1].tolist() == [1500, 2250, 0]                      # max(Σ app, max init) + overhead
+    assert req[2].tolist() == [(1 << 30) + (512 << 20), 0, 0]
+    assert mask.tolist() == [0b110, 0b010, 0b000]                  # gpu only on one container; bob has no limits
+    assert unit.tolist() == [0, 1, 2]
+    # without interning, unknown namespaces become BAD ids
+    ns2, *_ = Pd.flatten_pods([_pod("zed", [{"cpu": "1"}])], keys, m, intern=False)
+    assert ns2.tolist() == [0xFFFFFFFF]
+    with pytest.raises(bgc.BgcError):
+        Pd.flatten_pods([_pod("x", [{"cpu": "lots"}])], keys, m)
+
+
+def test_hard_from_sheet_row_follows_synchronizer(bgc):
+    # synchronizer.rs:249-281: cpu → "<n>" cores, memory/storage → "<n>Gi", gpu/mig → "<n>"
+    keys = ["requests.cpu", "requests.memory", "limits.cpu", "limits.memory"]
+    hard, unit = bgc.pods.hard_from_sheet_row(16, 64, 2, 500, 1, keys)
+    assert hard.tolist() == [16000, 64 << 30, 16000, 64 << 30] and unit.tolist() == [1, 2, 1, 2]
+    hard, unit = bgc.pods.hard_from_sheet_row(16, 64, 2, 500, 1, ["requests.nvidia.com/gpu", "requests.nvidia.com/mig-1g.10gb", "requests.storage"])
+    assert hard.tolist() == [2, 1, 500 << 30] and unit.tolist() == [0, 0, 0]
+    # the same numbers through the quantity parser, as Kubernetes would read the strings the reference writes
+    assert bgc.pods.parse_quantity("16", 1) == 16000 and bgc.pods.parse_quantity("64Gi", 2) == 64 << 30
+    with pytest.raises(bgc.BgcError):
+        bgc.pods.hard_from_sheet_row(1, 1, 1, 1, 1, ["requests.foo"])
