@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py — pods evaluated/s and achieved HBM GB/s of the batched quota-evaluation path.
+
+A step = one pass of the hot path over one batch: K1 usage_reduce over the running set
+(n pods) followed by K2 quota_eval over the candidate set (n pods), both through the C ABI of
+libbgc.so.  `value` = candidate pods evaluated per second with inputs resident in HBM; `e2e` =
+the same step through the host-pointer entry points with pinned HOST buffers (H2D of both sets
+and D2H of the verdicts inside the timed region).  Default workload = BASELINE.json configs[2]
+(10^8 pods, Zipf(1.1) over 10^4 namespaces, R=3: gpu, cpu, memory) — the configuration the
+north_star quotes its HBM target on; it fits one B200.  With --gpus N every rank owns an
+independent namespace shard of the same size (weak scaling, no data-path collective).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c3|c2|c5]
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    # name: (pods per GPU, namespaces per GPU, R, dist, zipf s, description)
+    "c3": (100_000_000, 10_000, 3, 1, 1.1, "C3: 1e8 pods, Zipf(1.1) over 1e4 namespaces, R=3 (gpu,cpu,memory), arrival order"),
+    "c2": (1_048_576, 10_000, 2, 0, 0.0, "C2: 2^20 pods x 1e4 namespaces, uniform, R=2 (gpu,cpu)"),
+    "c5": (125_000_000, 125_000, 3, 1, 1.1, "C5 shard: 1.25e8 pods x 1.25e5 namespaces per GPU (1e9 x 1e6 over 8), Zipf(1.1), R=3"),
+}
+SEED = {"c3": 0xB2000003, "c2": 0xB2000002, "c5": 0xB2000005}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.device}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except Exception:
+                continue
+            for nm, val in zip(names, r[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        busy = sorted(x for x in sm if mx is None or x > 0.3 * mx) or sorted(sm)
+        med = busy[len(busy) // 2] if busy else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_info():
+    model = "unknown"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    return os.cpu_count() or 1, model
+
+
+def cpu_step(oracle, Q, wl, sample: int, threads: int, seed: int):
+    """The CPU path on a bounded sample of the workload: inputs generated untimed, then one timed
+    step (usage_reduce + quota_eval) of the oracle with `threads` OpenMP threads."""
+    from workloads import make_hard, KINDS
+    n, NS, R, dist, s, _ = wl
+    a, b = Q.scramble_params(NS)
+    cdf = Q.zipf_cdf(NS, s) if dist else None
+    run = oracle.gen_fill(oracle.gen_params(seed, 0, NS, dist, 0, sample, a, b, cdf, KINDS[R]), 0, sample, threads=threads)
+    cand = oracle.gen_fill(oracle.gen_params(seed, 1, NS, dist, 0, sample, a, b, cdf, KINDS[R]), 0, sample, threads=threads)
+    used = oracle.usage_reduce(run[0], run[1], NS, threads=threads)
+    hard, hm = make_hard(used, seed)
+
+    def step():
+        t0 = time.perf_counter()
+        u = oracle.usage_reduce(run[0], run[1], NS, threads=threads)
+        oracle.quota_eval(cand[0], cand[1], None, NS, u, hard, hm, 0b110 & ((1 << R) - 1), threads=threads)
+        return time.perf_counter() - t0
+    return step
+
+
+def run_reference(args, wl, rank):
+    """--impl reference: the reference has no implementation of this path and cannot be built here
+    (Rust, no cargo), so the CPU arm is the oracle port on all host cores (kind = "port")."""
+    if rank != 0:
+        return
+    import oracle
+    from oracle import quota_ref as Q
+    oracle.build()
+    cores, model = cpu_info()
+    sample = min(wl[0], 1 << 24)
+    step = cpu_step(oracle, Q, wl, sample, cores, SEED[args.workload])
+    for _ in range(args.warmup):
+        step()
+    ts = [step() for _ in range(args.steps)]
+    t = sum(ts) / len(ts)
+    v = sample / t
+    line = {
+        "impl": "reference", "metric": "pods_evaluated_per_s", "value": v, "unit": "pods/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": {"workload": wl[5], "pods_per_step": sample, "namespaces": wl[1], "resources": wl[2]},
+        "cpu_baseline": {"value": v, "unit": "pods/s", "cores": cores, "kind": "port", "cpu_model": model,
+                         "sample": f"{sample} running + {sample} candidate pods per step (oracle/quota_ref.c, OpenMP, {cores} threads)"},
+        "e2e": {"value": v, "unit": "pods/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--pods", type=int, default=0, help="override pods per GPU")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--k1", type=int, default=0, help="force a K1 variant (BGC_K1_*)")
+    ap.add_argument("--grouped", action="store_true", help="running set grouped by namespace (segmented path)")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = max(args.warmup, 0)
+    wl = list(WORKLOADS[args.workload])
+    if args.pods:
+        wl[0] = args.pods
+    wl = tuple(wl)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, wl, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    from workloads import make_hard, KINDS, UNITS
+    from oracle import quota_ref as Q  # zipf table + scramble parameters are INPUTS shared with the checker
+    bgc = importlib.import_module("bacchus-gpu-controller_b200")
+    eng = bgc.Engine(local)
+    eng.use_torch_stream()
+    if args.k1:
+        eng.set_k1_variant(args.k1)
+
+    n, NS, R, dist_kind, zs, desc = wl
+    seed = SEED[args.workload] + 7919 * rank          # every rank owns an independent namespace shard
+    a, b = Q.scramble_params(NS)
+    cdf = Q.zipf_cdf(NS, zs) if dist_kind else None
+    d_cdf = torch.from_numpy(cdf.view(np.int64)).cuda() if dist_kind else None
+    dev = torch.device("cuda", local)
+
+    def alloc_set():
+        return (torch.empty(n, dtype=torch.int32, device=dev), [torch.empty(n, dtype=torch.int64, device=dev) for _ in range(R)])
+    run_ns, run_req = alloc_set()
+    cand_ns, cand_req = alloc_set()
+    d_verdict = torch.empty(n, dtype=torch.uint8, device=dev)
+    eng.synth_pods_dev(bgc.synth_params(seed, 0, NS, dist_kind, int(args.grouped), n, a, b, d_cdf, KINDS[R]), 0, n, run_ns, run_req)
+    eng.synth_pods_dev(bgc.synth_params(seed, 1, NS, dist_kind, 0, n, a, b, d_cdf, KINDS[R]), 0, n, cand_ns, cand_req)
+    # quota table: hard drawn from the running set's own usage so that about half the verdicts deny
+    eng.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
+    flags = bgc.REDUCE_GROUPED if args.grouped else 0
+    eng.usage_reduce_dev(run_ns, run_req, flags)
+    torch.cuda.synchronize()
+    used0 = eng.usage_get()
+    hard, hard_mask = make_hard(used0, seed)
+    eng.quota_table_set(hard, hard_mask, UNITS[R])
+
+    def step():
+        eng.usage_reduce_dev(run_ns, run_req, flags)
+        eng.quota_eval_dev(cand_ns, cand_req, None, d_verdict)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    launches0 = eng.timings()["launches"]
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    barrier()
+    t_all0 = torch.cuda.Event(enable_timing=True); t_all1 = torch.cuda.Event(enable_timing=True)
+    t_all0.record()
+    for k in range(args.steps):
+        ev[k][0].record()
+        eng.usage_reduce_dev(run_ns, run_req, flags)
+        ev[k][1].record()
+        eng.quota_eval_dev(cand_ns, cand_req, None, d_verdict)
+        ev[k][2].record()
+    t_all1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = eng.timings()["launches"] - launches0
+    total_ms = t_all0.elapsed_time(t_all1)
+    k1_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
+    k2_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
+    if world > 1:
+        t = torch.tensor([total_ms, k1_ms, k2_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, k1_ms, k2_ms = t.tolist()
+    ms_per_step = total_ms / args.steps
+    value = world * n / (ms_per_step * 1e-3)
+
+    # ---- parity spot-check of what was just timed (checker only; not in any timed region)
+    import oracle
+    oracle.build()
+    verified = None
+    if rank == 0:
+        cnt = min(n, 1 << 20)
+        p1 = oracle.gen_params(seed, 1, NS, dist_kind, 0, n, a, b, cdf, KINDS[R])
+        cns, creq, _ = oracle.gen_fill(p1, n - cnt, cnt, threads=8)
+        used_now = eng.usage_get()
+        v = oracle.quota_eval(cns, creq, None, NS, used_now, hard, hard_mask, 0b110 & ((1 << R) - 1), threads=8)
+        verified = bool(np.array_equal(used_now, used0)) and oracle.checksum_u8(v, n - cnt) == eng.checksum_u8_dev(d_verdict[n - cnt:], n - cnt)
+        if n <= (1 << 25):
+            p0 = oracle.gen_params(seed, 0, NS, dist_kind, int(args.grouped), n, a, b, cdf, KINDS[R])
+            rns, rreq, _ = oracle.gen_fill(p0, 0, n, threads=8)
+            verified = verified and bool(np.array_equal(oracle.usage_reduce(rns, rreq, NS, threads=8), used_now))
+
+    # ---- end to end through the host-pointer entry points (pinned host buffers)
+    e2e = None
+    if not args.no_e2e:
+        h_run_ns = torch.empty(n, dtype=torch.int32, pin_memory=True); h_run_ns.copy_(run_ns)
+        h_run_req = [torch.empty(n, dtype=torch.int64, pin_memory=True) for _ in range(R)]
+        h_cand_ns = torch.empty(n, dtype=torch.int32, pin_memory=True); h_cand_ns.copy_(cand_ns)
+        h_cand_req = [torch.empty(n, dtype=torch.int64, pin_memory=True) for _ in range(R)]
+        for r in range(R):
+            h_run_req[r].copy_(run_req[r]); h_cand_req[r].copy_(cand_req[r])
+        h_verdict = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+        torch.cuda.synchronize()
+        del run_ns, run_req, cand_ns, cand_req
+        eng.set_stream(None)
+
+        def e2e_step():
+            eng.usage_reduce_ptr(h_run_ns.data_ptr(), [t.data_ptr() for t in h_run_req], n, flags, 0)
+            eng.quota_eval_ptr(h_cand_ns.data_ptr(), [t.data_ptr() for t in h_cand_req], 0, n, h_verdict.data_ptr())
+        e2e_steps = args.steps
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()              # each host-pointer call returns after its last D2H has completed
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tm = eng.timings()
+        if world > 1:
+            t = torch.tensor([dt], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = t.item()
+        if rank == 0 and verified is not None:
+            verified = verified and oracle.checksum_u8(v, n - cnt) == oracle.checksum_u8(h_verdict[n - cnt:].numpy(), n - cnt)
+        e2e = {"value": world * n * e2e_steps / dt, "unit": "pods/s", "h2d_bytes_per_step": 2 * n * (4 + 8 * R),
+               "d2h_bytes_per_step": n, "ms_per_step": dt / e2e_steps * 1e3, "host_memory": "pinned",
+               "last_quota_eval_call": {"h2d_ms": tm["h2d_ns"] / 1e6, "kernel_ms": tm["kernel_ns"] / 1e6, "d2h_ms": tm["d2h_ns"] / 1e6}}
+
+    # ---- CPU baseline beside it (rank 0, bounded sample, all host cores)
+    cpu = None
+    if rank == 0 and not args.no_cpu and world == 1:
+        cores, model = cpu_info()
+        sample = min(n, 1 << 24)
+        cstep = cpu_step(oracle, Q, wl, sample, cores, SEED[args.workload])
+        cstep()
+        t1 = cstep()
+        reps = int(max(1, min(20, 10.0 / max(t1, 1e-3))))
+        ts = [cstep() for _ in range(reps)]
+        c1 = cpu_step(oracle, Q, wl, min(sample, 1 << 22), 1, SEED[args.workload])
+        c1(); t_1t = min(c1() for _ in range(2))
+        cpu = {"value": sample / (sum(ts) / len(ts)), "unit": "pods/s", "cores": cores, "kind": "port", "cpu_model": model,
+               "sample": f"{sample} running + {sample} candidate pods per step x {reps} steps (oracle/quota_ref.c, OpenMP)",
+               "single_thread_pods_per_s": min(sample, 1 << 22) / t_1t}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        k1_bytes = n * (4 + 8 * R)
+        achieved = k1_bytes / (k1_ms * 1e-3) / 1e9
+        k2_bytes = n * (4 + 8 * R + 1)
+        line = {
+            "metric": "pods_evaluated_per_s", "value": value, "unit": "pods/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+            "config": {"workload": desc, "pods_per_gpu": n, "namespaces_per_gpu": NS, "resources": R,
+                       "step": "K1 usage_reduce(running set) + K2 quota_eval(candidate set)", "running_set": "grouped" if args.grouped else "arrival order",
+                       "l2": f"inputs {(k1_bytes + k2_bytes) / 1e6:.0f} MB per step >> 126 MB L2 (no flush needed)" if k1_bytes > 4e8 else "inputs fit in L2: treat GB/s as cache bandwidth",
+                       "k1_variant": eng.last_k1_variant(), "sharding": "namespace-hash shards, independent per rank, no collective"},
+            "roofline": {"bound": "hbm", "kernel": "k1_usage_reduce", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "frac_of_8000_datasheet": achieved / 8000.0,
+                         "algorithmic_bytes_per_pod": 4 + 8 * R, "k1_ms": k1_ms,
+                         "k2": {"ms": k2_ms, "achieved": k2_bytes / (k2_ms * 1e-3) / 1e9, "frac": k2_bytes / (k2_ms * 1e-3) / 1e9 / peak,
+                                "algorithmic_bytes_per_pod": 4 + 8 * R + 1}},
+            "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches), "verified_vs_oracle": verified,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    eng.close()
+
+
+if __name__ == "__main__":
+    main()
