@@ -38,7 +38,7 @@ DIST_UNIFORM, DIST_ZIPF_CDF = 0, 1
 
 # every symbol include/*.h declares (tests check the library exports all of them)
 EXPORTS = [
-    "bgc_ctx_create", "bgc_ctx_destroy", "bgc_last_error", "bgc_ctx_set_stream", "bgc_ctx_sync",
+    "bgc_ctx_create", "bgc_ctx_destroy", "bgc_last_error", "bgc_ctx_set_stream", "bgc_ctx_reset_stream", "bgc_ctx_sync",
     "bgc_timings_get", "bgc_policy_eval", "bgc_policy_eval_dev", "bgc_quota_table_set",
     "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_quota_eval",
     "bgc_quota_eval_dev", "bgc_ctx_set_k1_variant", "bgc_last_k1_variant", "bgc_version",
@@ -69,6 +69,7 @@ lib.bgc_reason_message.restype = C.c_char_p
 lib.bgc_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
 lib.bgc_ctx_destroy.argtypes = [C.c_void_p]
 lib.bgc_ctx_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+lib.bgc_ctx_reset_stream.argtypes = [C.c_void_p]
 lib.bgc_ctx_sync.argtypes = [C.c_void_p]
 lib.bgc_timings_get.argtypes = [C.c_void_p, C.POINTER(Timings)]
 lib.bgc_ctx_set_k1_variant.argtypes = [C.c_void_p, C.c_int]
@@ -140,7 +141,11 @@ class Engine:
 
     # -- plumbing
     def set_stream(self, cuda_stream_handle: int | None):
-        self._ck(lib.bgc_ctx_set_stream(self._h, C.c_void_p(cuda_stream_handle or 0)))
+        """A cudaStream_t handle (0 = legacy default stream); None = back to the engine's own stream."""
+        if cuda_stream_handle is None:
+            self._ck(lib.bgc_ctx_reset_stream(self._h))
+        else:
+            self._ck(lib.bgc_ctx_set_stream(self._h, C.c_void_p(cuda_stream_handle)))
 
     def use_torch_stream(self):
         import torch

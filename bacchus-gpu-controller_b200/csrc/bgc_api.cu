@@ -369,7 +369,13 @@ const char* bgc_last_error(const bgc_ctx* ctx) { return ctx ? ctx->err.c_str() :
 
 int bgc_ctx_set_stream(bgc_ctx* ctx, void* cuda_stream) {
   if (!ctx) return BGC_E_BADARG;
-  ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  ctx->stream = static_cast<cudaStream_t>(cuda_stream);
+  return BGC_OK;
+}
+
+int bgc_ctx_reset_stream(bgc_ctx* ctx) {
+  if (!ctx) return BGC_E_BADARG;
+  ctx->stream = ctx->own_stream;
   return BGC_OK;
 }
 

@@ -105,8 +105,11 @@ typedef struct bgc_timings {
 int bgc_ctx_create(int device, bgc_ctx **out);
 int bgc_ctx_destroy(bgc_ctx *ctx);
 const char *bgc_last_error(const bgc_ctx *ctx);
-/* stream the `_dev` entry points enqueue on (a cudaStream_t; NULL restores the ctx's own) */
+/* stream the `_dev` entry points enqueue on: any cudaStream_t, NULL being the legacy default
+ * stream (what PyTorch uses unless told otherwise); a new ctx starts on its own stream */
 int bgc_ctx_set_stream(bgc_ctx *ctx, void *cuda_stream);
+/* back to the context's own non-blocking stream */
+int bgc_ctx_reset_stream(bgc_ctx *ctx);
 int bgc_ctx_sync(bgc_ctx *ctx);
 int bgc_timings_get(bgc_ctx *ctx, bgc_timings *out);
 
