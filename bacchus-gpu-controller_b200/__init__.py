@@ -46,7 +46,7 @@ EXPORTS = [
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
     "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
     "bgc_nsmap_intern", "bgc_nsmap_lookup", "bgc_nsmap_size", "bgc_nsmap_name", "bgc_flatten_pods",
-    "bgc_hard_from_sheet_row",
+    "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev",
 ]
 
 

@@ -89,7 +89,7 @@ __device__ __forceinline__ uint32_t policy_decide(uint32_t op, uint32_t f) {
 constexpr int kK0Threads = 256;
 constexpr int kK0PerThread = 16;
 
-__global__ void __launch_bounds__(kK0Threads)
+static __global__ void __launch_bounds__(kK0Threads)
 k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flags, size_t n,
                uint8_t* __restrict__ code, uint8_t* __restrict__ patch_mask, int vec_ok) {
   __shared__ uint16_t lut[4096];
@@ -138,7 +138,7 @@ k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flag
 
 // ------------------------------------------------------------------ quota table maintenance
 // grid-stride over NS*R
-__global__ void k_rows_set_hard(QuotaRow* rows, const long long* __restrict__ hard,
+static __global__ void k_rows_set_hard(QuotaRow* rows, const long long* __restrict__ hard,
                                 const uint8_t* __restrict__ hard_mask, uint32_t NS, int R) {
   const size_t total = (size_t)NS * 8;
   for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
@@ -151,7 +151,7 @@ __global__ void k_rows_set_hard(QuotaRow* rows, const long long* __restrict__ ha
     rows[ns].w[k] = v;
   }
 }
-__global__ void k_rows_clear_used(QuotaRow* rows, uint32_t NS, int R) {
+static __global__ void k_rows_clear_used(QuotaRow* rows, uint32_t NS, int R) {
   const size_t total = (size_t)NS * R;
   for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
        t += (size_t)gridDim.x * blockDim.x) {
@@ -161,7 +161,7 @@ __global__ void k_rows_clear_used(QuotaRow* rows, uint32_t NS, int R) {
   }
 }
 // used_out[r][ns] <- rows ; or rows <- used_in (set)
-__global__ void k_rows_export_used(const QuotaRow* __restrict__ rows, long long* used_out,
+static __global__ void k_rows_export_used(const QuotaRow* __restrict__ rows, long long* used_out,
                                    uint32_t NS, int R) {
   const size_t total = (size_t)NS * R;
   for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
@@ -171,7 +171,7 @@ __global__ void k_rows_export_used(const QuotaRow* __restrict__ rows, long long*
     used_out[t] = rows[ns].w[2 * r];
   }
 }
-__global__ void k_rows_import_used(QuotaRow* rows, const long long* __restrict__ used_in,
+static __global__ void k_rows_import_used(QuotaRow* rows, const long long* __restrict__ used_in,
                                    uint32_t NS, int R) {
   const size_t total = (size_t)NS * R;
   for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
@@ -481,7 +481,7 @@ struct SynthArgs {
   uint8_t* req_mask;
 };
 
-__global__ void __launch_bounds__(256) k_synth_pods(SynthArgs A, uint64_t first, size_t count) {
+static __global__ void __launch_bounds__(256) k_synth_pods(SynthArgs A, uint64_t first, size_t count) {
   for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < count;
        k += (size_t)gridDim.x * blockDim.x) {
     const uint64_t i = first + k;
@@ -509,7 +509,7 @@ __global__ void __launch_bounds__(256) k_synth_pods(SynthArgs A, uint64_t first,
   }
 }
 
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_synth_policy(uint64_t key, uint64_t first, size_t count, uint8_t* op, uint16_t* flags) {
   for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < count;
        k += (size_t)gridDim.x * blockDim.x) {
@@ -519,7 +519,7 @@ k_synth_policy(uint64_t key, uint64_t first, size_t count, uint8_t* op, uint16_t
   }
 }
 
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_checksum_u8(const uint8_t* __restrict__ v, uint64_t first, size_t count, unsigned long long* out) {
   unsigned long long s = 0;
   for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < count;
@@ -530,7 +530,7 @@ k_checksum_u8(const uint8_t* __restrict__ v, uint64_t first, size_t count, unsig
   if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
 }
 
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_histogram_u8(const uint8_t* __restrict__ v, size_t count, unsigned long long* out256) {
   __shared__ unsigned int h[256];
   h[threadIdx.x] = 0;

@@ -1,0 +1,191 @@
+// bgc_noalloc.cu — bgc_usage_reduce_static_dev: per-namespace usage without any allocation.
+//
+// Who this is for: a caller that must not (or cannot) allocate device memory at call time — a
+// serving process that handed all of HBM to its own pool at start-up, so a cudaMalloc issued by a
+// library would fail or eat into memory someone else has budgeted; or a request handler on a
+// latency-critical path, where the implicit device-wide synchronisation of cudaMalloc/cudaFree
+// would stall every other stream.  The regular entry points (bgc_ctx_create,
+// bgc_quota_table_set, bgc_usage_reduce*) allocate their accumulation table, staging buffers and
+// streams; this one allocates nothing, ever: no cudaMalloc, no cudaFree, no stream or event
+// creation, no library routine that allocates.
+//
+// How: the accumulation table the reduction kernel scatters into lives in a file-scope
+// `static __device__` array of fixed size (BGC_STATIC_MAX_NS namespaces x 64 B = 1 MiB), which
+// every GPU that loads libbgc.so holds from module load until the process exits.  The caller
+// passes the inputs (pod columns) and the output (used[R][NS]) as device pointers, plus the stream
+// to run on.
+//
+// Things a user must know:
+//   * It works on the CURRENT device (the one the pointers belong to).  The first call on each
+//     device performs a one-time set-up — it asks the runtime for the device address of the
+//     static array (cudaGetSymbolAddress) and opts the kernels into large shared memory.  Make
+//     that first call before starting any stream capture on that device.
+//   * ns_count above BGC_STATIC_MAX_NS (or R outside 1..BGC_MAX_R) is rejected with BGC_E_BADARG
+//     and a message in `errbuf`; nothing is launched.
+//   * Every call on a device shares the one array, and the array keeps whatever the previous call
+//     left in it.  Each call therefore first clears the slots it is about to use; but two calls
+//     whose kernels overlap on the GPU (different streams, or different host threads) race on the
+//     table and produce garbage.  Serialise calls per device.
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+
+#include "../../include/bgc.h"
+#include "bgc_kernels.cuh"
+
+using namespace bgc;
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+constexpr size_t kStaticSmemBudget = 200 * 1024;
+
+// The scratch itself.  In HOST code the name `g_static_rows` is only a handle for the runtime
+// (a host-side shadow symbol), not a device address; kernels must be given the pointer obtained
+// from cudaGetSymbolAddress below.
+static __device__ __align__(256) QuotaRow g_static_rows[BGC_STATIC_MAX_NS];
+
+struct PerDevice {
+  bool ready = false;
+  QuotaRow* rows = nullptr;  // device address of g_static_rows on this device
+  int sm_count = 0;
+};
+PerDevice g_dev[kMaxDevices];
+std::mutex g_mu;
+
+int say(char* errbuf, size_t cap, int code, const char* fmt, ...) {
+  if (errbuf && cap) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(errbuf, cap, fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+#define SCU(call)                                                                          \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess) return say(errbuf, errbuf_len, BGC_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+// one-time set-up for the current device (called under g_mu)
+int setup_device(int dev, char* errbuf, size_t errbuf_len) {
+  PerDevice& d = g_dev[dev];
+  void* p = nullptr;
+  SCU(cudaGetSymbolAddress(&p, g_static_rows));
+  if (!p) return say(errbuf, errbuf_len, BGC_E_CUDA, "cudaGetSymbolAddress returned a null address");
+  SCU(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+  d.rows = static_cast<QuotaRow*>(p);
+  d.ready = true;
+  return BGC_OK;
+}
+
+template <int R, int SINK, bool VEC>
+int launch_reduce(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const long long* const* req, size_t n,
+                  uint32_t NS, uint32_t cap, char* errbuf, size_t errbuf_len) {
+  ReqCols<R> cols;
+  for (int r = 0; r < R; ++r) cols.p[r] = req[r];
+  auto kern = k1_usage_reduce<R, SINK, VEC>;
+  size_t smem = 0;
+  int threads = 512, blocks_per_sm = 1;
+  if (SINK == SINK_GLOBAL) {
+    SCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, threads, 0));
+    if (blocks_per_sm < 1) blocks_per_sm = 1;
+  } else {
+    threads = 1024;
+    smem = (size_t)2 * R * cap * 4 + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
+    SCU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  const size_t tiles = (n + kK1Tile - 1) / kK1Tile;
+  const size_t wpb = threads / 32;
+  int grid = d.sm_count * blocks_per_sm;
+  if ((size_t)grid * wpb > tiles) grid = (int)((tiles + wpb - 1) / wpb);
+  if (grid < 1) grid = 1;
+  size_t chunk_tiles = tiles / ((size_t)grid * wpb * 4);
+  if (chunk_tiles < 1) chunk_tiles = 1;
+  if (chunk_tiles > 32) chunk_tiles = 32;
+  kern<<<grid, threads, smem, st>>>(ns, cols, n, d.rows, NS, cap, (uint32_t)chunk_tiles);
+  SCU(cudaGetLastError());
+  return BGC_OK;
+}
+
+template <int R>
+int reduce_r(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const long long* const* req, size_t n,
+             uint32_t NS, unsigned flags, char* errbuf, size_t errbuf_len) {
+  bool vec = (reinterpret_cast<uintptr_t>(ns) & 15) == 0;
+  for (int r = 0; r < R; ++r) vec = vec && (reinterpret_cast<uintptr_t>(req[r]) & 31) == 0;
+  const bool direct_fits = (size_t)NS * R * 8 <= kStaticSmemBudget;
+  if (flags & BGC_REDUCE_GROUPED)
+    return vec ? launch_reduce<R, SINK_GLOBAL, true>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len)
+               : launch_reduce<R, SINK_GLOBAL, false>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len);
+  if (direct_fits)
+    return vec ? launch_reduce<R, SINK_DIRECT, true>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len)
+               : launch_reduce<R, SINK_DIRECT, false>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len);
+  uint32_t cap = 1;
+  while ((size_t)cap * 2 * (8 * R + 4) <= kStaticSmemBudget) cap *= 2;
+  return vec ? launch_reduce<R, SINK_HASH, true>(d, st, ns, req, n, NS, cap, errbuf, errbuf_len)
+             : launch_reduce<R, SINK_HASH, false>(d, st, ns, req, n, NS, cap, errbuf, errbuf_len);
+}
+
+}  // namespace
+
+extern "C" int bgc_usage_reduce_static_dev(const uint32_t* d_ns_id, const int64_t* const* d_req, uint32_t R,
+                                           size_t n, uint32_t ns_count, unsigned flags, int64_t* d_used_out,
+                                           void* cuda_stream, char* errbuf, size_t errbuf_len) {
+  if (errbuf && errbuf_len) errbuf[0] = 0;
+  if (R < 1 || R > BGC_MAX_R)
+    return say(errbuf, errbuf_len, BGC_E_BADARG, "R = %u is outside 1..%d", R, BGC_MAX_R);
+  if (ns_count < 1 || ns_count > BGC_STATIC_MAX_NS)
+    return say(errbuf, errbuf_len, BGC_E_BADARG,
+               "ns_count = %u exceeds the static table (BGC_STATIC_MAX_NS = %d namespaces); use bgc_usage_reduce_dev",
+               ns_count, BGC_STATIC_MAX_NS);
+  if (!d_used_out || (n && (!d_ns_id || !d_req)))
+    return say(errbuf, errbuf_len, BGC_E_BADARG, "null pointer argument");
+  if (flags & BGC_REDUCE_ACCUMULATE)
+    return say(errbuf, errbuf_len, BGC_E_BADARG, "BGC_REDUCE_ACCUMULATE is not supported: the table is cleared on every call");
+  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  for (uint32_t r = 0; r < R && n; ++r) {
+    if (!d_req[r]) return say(errbuf, errbuf_len, BGC_E_BADARG, "null request column %u", r);
+    cols[r] = reinterpret_cast<const long long*>(d_req[r]);
+  }
+  int dev = 0;
+  SCU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return say(errbuf, errbuf_len, BGC_E_BADARG, "device index %d not supported", dev);
+  {
+    std::lock_guard<std::mutex> lock(g_mu);
+    if (!g_dev[dev].ready) {
+      const int rc = setup_device(dev, errbuf, errbuf_len);
+      if (rc) return rc;
+    }
+  }
+  const PerDevice& d = g_dev[dev];
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+
+  // the table keeps the previous call's sums: zero the used[] slots this call accumulates into
+  {
+    const size_t total = (size_t)ns_count * R;
+    int grid = (int)((total + 255) / 256);
+    if (grid > d.sm_count * 4) grid = d.sm_count * 4;
+    k_rows_clear_used<<<grid, 256, 0, st>>>(d.rows, ns_count, (int)R);
+    SCU(cudaGetLastError());
+  }
+  int rc = BGC_OK;
+  if (n) {
+    switch (R) {
+      case 1: rc = reduce_r<1>(d, st, d_ns_id, cols, n, ns_count, flags, errbuf, errbuf_len); break;
+      case 2: rc = reduce_r<2>(d, st, d_ns_id, cols, n, ns_count, flags, errbuf, errbuf_len); break;
+      case 3: rc = reduce_r<3>(d, st, d_ns_id, cols, n, ns_count, flags, errbuf, errbuf_len); break;
+      default: rc = reduce_r<4>(d, st, d_ns_id, cols, n, ns_count, flags, errbuf, errbuf_len); break;
+    }
+    if (rc) return rc;
+  }
+  {
+    const size_t total = (size_t)ns_count * R;
+    int grid = (int)((total + 255) / 256);
+    if (grid > d.sm_count * 4) grid = d.sm_count * 4;
+    k_rows_export_used<<<grid, 256, 0, st>>>(d.rows, reinterpret_cast<long long*>(d_used_out), ns_count, (int)R);
+    SCU(cudaGetLastError());
+  }
+  return BGC_OK;
+}

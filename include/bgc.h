@@ -149,6 +149,26 @@ int bgc_quota_eval(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *re
 int bgc_quota_eval_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
                        const uint8_t *d_req_mask, size_t n, uint8_t *d_verdict);
 
+/* ---- allocation-free usage reduction ---------------------------------------------------------
+ * No counterpart in the reference.  For callers that cannot allocate device memory when they
+ * call (all of HBM already handed to their own pool, or a latency-critical handler that must not
+ * trigger cudaMalloc's device-wide synchronisation): the same result as bgc_usage_reduce_dev, but
+ * without a bgc_ctx and without a single allocation — the accumulation table is a static device
+ * array of BGC_STATIC_MAX_NS namespaces (1 MiB per GPU, held from library load to process exit).
+ *   - runs on the CURRENT device, on `cuda_stream`; inputs and d_used_out ([R][ns_count]) are
+ *     device pointers owned by the caller;
+ *   - ns_count > BGC_STATIC_MAX_NS or R outside 1..BGC_MAX_R → BGC_E_BADARG, message in errbuf
+ *     (errbuf may be NULL);
+ *   - the first call on a device does a one-time set-up (resolves the array's device address);
+ *     make that call before any stream capture on the device;
+ *   - all calls on a device share the one table, which keeps the last call's contents: each call
+ *     clears what it uses first, and calls that overlap on the GPU race — serialise them;
+ *   - flags: BGC_REDUCE_GROUPED only. */
+#define BGC_STATIC_MAX_NS 16384
+int bgc_usage_reduce_static_dev(const uint32_t *d_ns_id, const int64_t *const *d_req, uint32_t R,
+                                size_t n, uint32_t ns_count, unsigned flags, int64_t *d_used_out,
+                                void *cuda_stream, char *errbuf, size_t errbuf_len);
+
 /* ---- tuning / introspection ---------------------------------------------------------------- */
 /* K1 kernel choice: 0 = automatic; otherwise force BGC_K1_* (tests exercise every variant) */
 enum { BGC_K1_AUTO = 0, BGC_K1_GLOBAL = 1, BGC_K1_SMEM_DIRECT = 2, BGC_K1_SMEM_HASH = 3 };
