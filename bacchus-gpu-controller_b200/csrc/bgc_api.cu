@@ -19,7 +19,7 @@ using namespace bgc;
 namespace {
 
 constexpr size_t kChunkPods = size_t(4) << 20;      // host-pointer calls move 4 Mi pods per stage
-constexpr size_t kSmemBudget = 200 * 1024;          // CTA-private K1 table budget (<= 227 KB opt-in)
+constexpr size_t kSmemBudget = 224 * 1024;          // CTA-private K1 table budget (<= 227 KB opt-in)
 constexpr int kSlots = 2;
 
 struct Slot {
@@ -47,6 +47,9 @@ struct bgc_ctx {
   uint32_t NS = 0;
   int R = 0;
   uint32_t compute_mask = 0;
+  uint32_t wide_mask = 0;            // byte-valued columns: K1 keeps their high words in shared memory
+  HeadRow* head = nullptr;           // K2's compact table (hard - used, mask), rebuilt when stale
+  bool head_stale = true;
   // K1
   int k1_forced = BGC_K1_AUTO;
   const char* last_k1 = "none";
@@ -117,6 +120,11 @@ int launch_k0(bgc_ctx* ctx, cudaStream_t st, const uint8_t* op, const uint16_t* 
   return BGC_OK;
 }
 
+// bytes of CTA-private table per slot: a low word per column, a high word per wide column
+size_t k1_slot_bytes(const bgc_ctx* ctx, int R) {
+  return 4 * (size_t)(R + __builtin_popcount(ctx->wide_mask & ((1u << R) - 1u)));
+}
+
 template <int R, int SINK, bool VEC>
 int launch_k1_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
                    size_t n, uint32_t cap) {
@@ -130,7 +138,7 @@ int launch_k1_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
     if (blocks_per_sm < 1) blocks_per_sm = 1;
   } else {
     threads = 1024;
-    smem = (size_t)2 * R * cap * 4 + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
+    smem = k1_slot_bytes(ctx, R) * cap + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   const size_t tiles = (n + kK1Tile - 1) / kK1Tile;
@@ -142,7 +150,8 @@ int launch_k1_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
   size_t chunk_tiles = tiles / ((size_t)grid * warps_per_block * 4);
   if (chunk_tiles < 1) chunk_tiles = 1;
   if (chunk_tiles > 32) chunk_tiles = 32;
-  kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->rows, ctx->NS, cap, (uint32_t)chunk_tiles);
+  kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->rows, ctx->NS, cap, (uint32_t)chunk_tiles, ctx->wide_mask);
+  ctx->head_stale = true;
   ctx->tm.launches++;
   CU(cudaGetLastError());
   return BGC_OK;
@@ -155,7 +164,7 @@ int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long lo
   for (int r = 0; r < R; ++r) vec = vec && aligned(req[r], 32);
   // variant choice
   int variant = ctx->k1_forced;
-  const size_t direct_bytes = (size_t)ctx->NS * R * 8;
+  const size_t direct_bytes = (size_t)ctx->NS * k1_slot_bytes(ctx, R);
   if (variant == BGC_K1_AUTO) {
     if (flags & BGC_REDUCE_GROUPED) variant = BGC_K1_GLOBAL;
     else if (direct_bytes <= kSmemBudget) variant = BGC_K1_SMEM_DIRECT;
@@ -165,7 +174,7 @@ int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long lo
   uint32_t cap = ctx->NS;
   if (variant == BGC_K1_SMEM_HASH) {
     cap = 1;
-    while ((size_t)cap * 2 * (8 * R + 4) <= kSmemBudget) cap *= 2;
+    while ((size_t)cap * 2 * (k1_slot_bytes(ctx, R) + 4) <= kSmemBudget) cap *= 2;
   }
   switch (variant) {
     case BGC_K1_GLOBAL:
@@ -203,13 +212,20 @@ int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
     cols.p[r] = req[r];
     vec = vec && aligned(req[r], 32);
   }
+  if (ctx->head_stale) {  // usage or limits changed since the compact table was built
+    const int g = grid_for((size_t)ctx->NS * 4, 256, ctx->sm_count * 4);
+    k_build_headroom<<<g, 256, 0, st>>>(ctx->rows, ctx->d_hard_mask, ctx->head, ctx->NS, R);
+    ctx->tm.launches++;
+    CU(cudaGetLastError());
+    ctx->head_stale = false;
+  }
   const int grid = grid_for((n + 3) / 4, kK2Threads, ctx->sm_count * 8);
   if (vec)
     k2_quota_eval<R, HAS_MASK, true><<<grid, kK2Threads, 0, st>>>(
-        ns, cols, mask, n, ctx->rows, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
   else
     k2_quota_eval<R, HAS_MASK, false><<<grid, kK2Threads, 0, st>>>(
-        ns, cols, mask, n, ctx->rows, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
   ctx->tm.launches++;
   CU(cudaGetLastError());
   return BGC_OK;
@@ -234,6 +250,7 @@ int launch_k2(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long
 }
 
 int clear_used(bgc_ctx* ctx, cudaStream_t st) {
+  ctx->head_stale = true;
   const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
   k_rows_clear_used<<<grid, 256, 0, st>>>(ctx->rows, ctx->NS, ctx->R);
   ctx->tm.launches++;
@@ -355,6 +372,7 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   }
   for (auto e : ctx->ev_pool) cudaEventDestroy(e);
   cudaFree(ctx->rows);
+  cudaFree(ctx->head);
   cudaFree(ctx->d_hard_mask);
   cudaFree(ctx->d_table_tmp);
   cudaFree(ctx->d_scratch);
@@ -470,19 +488,24 @@ int bgc_quota_table_set(bgc_ctx* ctx, uint32_t ns_count, uint32_t R, const int64
   CU(cudaDeviceSynchronize());
   if (ns_count != ctx->NS || (int)R != ctx->R) {
     cudaFree(ctx->rows); ctx->rows = nullptr;
+    cudaFree(ctx->head); ctx->head = nullptr;
     cudaFree(ctx->d_hard_mask); ctx->d_hard_mask = nullptr;
     cudaFree(ctx->d_table_tmp); ctx->d_table_tmp = nullptr;
     ctx->NS = 0; ctx->R = 0;
     CU(cudaMalloc(&ctx->rows, (size_t)ns_count * sizeof(QuotaRow)));
+    CU(cudaMalloc(&ctx->head, (size_t)ns_count * sizeof(HeadRow)));
     CU(cudaMalloc(&ctx->d_hard_mask, ns_count));
     CU(cudaMalloc(&ctx->d_table_tmp, (size_t)ns_count * R * 8));
   }
   ctx->NS = ns_count;
   ctx->R = (int)R;
   ctx->compute_mask = 0;
+  ctx->wide_mask = 0;
+  ctx->head_stale = true;
   for (uint32_t r = 0; r < R; ++r) {
     NEED(unit[r] <= BGC_UNIT_BYTES, "unknown unit");
     if (unit[r] != BGC_UNIT_COUNT) ctx->compute_mask |= 1u << r;
+    if (unit[r] == BGC_UNIT_BYTES) ctx->wide_mask |= 1u << r;
   }
   CU(cudaMemcpyAsync(ctx->d_table_tmp, hard, (size_t)ns_count * R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
   CU(cudaMemcpyAsync(ctx->d_hard_mask, hard_mask, ns_count, cudaMemcpyHostToDevice, ctx->own_stream));
@@ -516,6 +539,7 @@ int bgc_usage_set(bgc_ctx* ctx, const int64_t* used) {
   CU(cudaMemcpyAsync(ctx->d_table_tmp, used, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
   const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
   k_rows_import_used<<<grid, 256, 0, ctx->own_stream>>>(ctx->rows, ctx->d_table_tmp, ctx->NS, ctx->R);
+  ctx->head_stale = true;
   ctx->tm.launches++;
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(ctx->own_stream));

@@ -16,8 +16,9 @@ namespace bgc {
 constexpr int kMaxR = 4;
 constexpr uint32_t kBadNs = 0xFFFFFFFFu;
 
-// One namespace's quota state, one 64-byte line: w[2r] = used[r], w[2r+1] = hard[r];
-// for R <= 3, w[7] holds hard_mask so K2 needs a single gather per pod.
+// One namespace's quota state, one 64-byte line: w[2r] = used[r], w[2r+1] = hard[r]
+// (w[7] = hard_mask for R <= 3).  K1 accumulates into it; K2 reads the compact HeadRow derived
+// from it (see k_build_headroom).
 struct __align__(64) QuotaRow {
   long long w[8];
 };
@@ -208,19 +209,27 @@ template <int R, int SINK>
 struct K1Sink {
   QuotaRow* rows;
   uint32_t NS;
-  uint32_t* s_lo;   // [R][cap]
-  uint32_t* s_hi;   // [R][cap]
+  uint32_t* s_lo;   // [R][cap]      low words of every column
+  uint32_t* s_hi;   // [nwide][cap]  high words of the wide columns only
   uint32_t* s_key;  // [cap] (hash)
   uint32_t cap;     // NS (direct) or slots (hash, power of two)
   uint32_t hash_shift;
+  uint32_t wide_mask;  // bit r: column r keeps its high word in shared memory (byte-valued columns)
 
-  __device__ __forceinline__ void smem_add(uint32_t idx, long long v) {
+  __device__ __forceinline__ uint32_t hi_slot(int r) const { return __popc(wide_mask & ((1u << r) - 1u)); }
+
+  // Narrow columns (counts, millicores) almost never carry into bit 32, so they get a low word
+  // only and the rare carry / high part goes straight to the global table.
+  __device__ __forceinline__ void smem_add(int r, uint32_t idx, uint32_t ns, long long v) {
     uint32_t lo = (uint32_t)(unsigned long long)v, hi = (uint32_t)((unsigned long long)v >> 32);
     if (lo) {
-      const uint32_t old = atomicAdd(&s_lo[idx], lo);
+      const uint32_t old = atomicAdd(&s_lo[r * cap + idx], lo);
       hi += (old + lo < old);  // carry out of the low word
     }
-    if (hi) atomicAdd(&s_hi[idx], hi);
+    if (hi) {
+      if ((wide_mask >> r) & 1u) atomicAdd(&s_hi[hi_slot(r) * cap + idx], hi);
+      else red_add_i64(&rows[ns].w[2 * r], (long long)((unsigned long long)hi << 32));
+    }
   }
 
   __device__ __forceinline__ void add(uint32_t ns, const long long (&v)[R]) {
@@ -232,7 +241,7 @@ struct K1Sink {
     } else if (SINK == SINK_DIRECT) {
 #pragma unroll
       for (int r = 0; r < R; ++r)
-        if (v[r]) smem_add(r * cap + ns, v[r]);
+        if (v[r]) smem_add(r, ns, ns, v[r]);
     } else {
       const uint32_t s = (ns * 0x9E3779B1u) >> hash_shift;
       uint32_t k = s_key[s];
@@ -243,7 +252,7 @@ struct K1Sink {
       if (k == ns) {
 #pragma unroll
         for (int r = 0; r < R; ++r)
-          if (v[r]) smem_add(r * cap + s, v[r]);
+          if (v[r]) smem_add(r, s, ns, v[r]);
       } else {
 #pragma unroll
         for (int r = 0; r < R; ++r)
@@ -256,18 +265,20 @@ struct K1Sink {
 template <int R, int SINK, bool VEC>
 __global__ void __launch_bounds__(SINK == SINK_GLOBAL ? 512 : 1024, 1)
 k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRow* rows,
-                uint32_t NS, uint32_t cap, uint32_t chunk_tiles) {
+                uint32_t NS, uint32_t cap, uint32_t chunk_tiles, uint32_t wide_mask) {
   extern __shared__ __align__(16) uint32_t k1_smem[];
   K1Sink<R, SINK> sink;
+  const uint32_t nwide = __popc(wide_mask & ((1u << R) - 1u));
   sink.rows = rows;
   sink.NS = NS;
   sink.cap = cap;
+  sink.wide_mask = wide_mask;
   sink.s_lo = k1_smem;
   sink.s_hi = k1_smem + (size_t)R * cap;
-  sink.s_key = k1_smem + (size_t)2 * R * cap;
+  sink.s_key = k1_smem + (size_t)(R + nwide) * cap;
   sink.hash_shift = 32 - (31 - __clz(cap | 1));
   if (SINK != SINK_GLOBAL) {
-    for (uint32_t i = threadIdx.x; i < 2u * R * cap; i += blockDim.x) k1_smem[i] = 0;
+    for (uint32_t i = threadIdx.x; i < (R + nwide) * cap; i += blockDim.x) k1_smem[i] = 0;
     if (SINK == SINK_HASH)
       for (uint32_t i = threadIdx.x; i < cap; i += blockDim.x) sink.s_key[i] = kHashEmpty;
     __syncthreads();
@@ -368,7 +379,8 @@ k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, Qu
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < R * cap; i += blockDim.x) {
       const uint32_t r = i / cap, s = i - r * cap;
-      const unsigned long long v = ((unsigned long long)sink.s_hi[i] << 32) | sink.s_lo[i];
+      const uint32_t hi = ((wide_mask >> r) & 1u) ? sink.s_hi[sink.hi_slot(r) * cap + s] : 0u;
+      const unsigned long long v = ((unsigned long long)hi << 32) | sink.s_lo[i];
       if (v) {
         const uint32_t ns = (SINK == SINK_HASH) ? sink.s_key[s] : s;
         red_add_i64(&rows[ns].w[2 * r], (long long)v);
@@ -378,28 +390,50 @@ k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, Qu
 }
 
 // ------------------------------------------------------------------ K2 quota_eval
-// 4 pods per thread: one 128-bit ns load, R 256-bit request loads, one (R<=2: half) QuotaRow
-// gather per pod, one 32-bit verdict store.  verdict = missing << 4 | exceeded.
+// K2 gathers one 32-byte sector per pod from a compact table derived from the QuotaRows:
+// head[ns].h[r] = hard[r] - used[r], saturated to the i64 range, and for R <= 3 h[3] = hard_mask.
+// "exceeded" is the overflow-free comparison used + req > hard (as Kubernetes' arbitrary-precision
+// Quantity arithmetic would decide it), i.e. req > hard - used with the difference saturated.
+struct __align__(32) HeadRow {
+  long long h[4];
+};
+
+__device__ __forceinline__ long long sat_sub_i64(long long a, long long b) {
+  const long long d = (long long)((unsigned long long)a - (unsigned long long)b);
+  if (((a ^ b) & (a ^ d)) < 0) return a < 0 ? (long long)0x8000000000000000ull : 0x7FFFFFFFFFFFFFFFll;
+  return d;
+}
+
+static __global__ void k_build_headroom(const QuotaRow* __restrict__ rows, const uint8_t* __restrict__ hard_mask,
+                                        HeadRow* head, uint32_t NS, int R) {
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < (size_t)NS * 4;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t ns = (uint32_t)(t >> 2), r = (uint32_t)(t & 3);
+    long long v = 0;
+    if ((int)r < R) v = sat_sub_i64(rows[ns].w[2 * r + 1], rows[ns].w[2 * r]);
+    else if (r == 3) v = hard_mask[ns];
+    head[ns].h[r] = v;
+  }
+}
+
+// 4 pods per thread: one 128-bit ns load, R 256-bit request loads, one 256-bit HeadRow gather per
+// pod, one 32-bit verdict store.  verdict = missing << 4 | exceeded.
 template <int R>
 __device__ __forceinline__ uint32_t quota_verdict(uint32_t ns, const long long (&q)[R], uint32_t rmask,
-                                                  const QuotaRow* __restrict__ rows,
+                                                  const HeadRow* __restrict__ head,
                                                   const uint8_t* __restrict__ hard_mask, uint32_t NS,
                                                   uint32_t compute_mask) {
   if (ns >= NS) return 0xFFu;
-  long long lo[4], hi[4];  // the whole 64-byte row: two 256-bit gathers of one line
-  ldg_row_half(&rows[ns].w[0], lo);
-  ldg_row_half(&rows[ns].w[4], hi);
-  const uint32_t hm = (R <= 3) ? (uint32_t)hi[3] : (uint32_t)hard_mask[ns];
+  long long h[4];
+  ldg_row_half(&head[ns].h[0], h);
+  const uint32_t hm = (R <= 3) ? (uint32_t)h[3] : (uint32_t)hard_mask[ns];
   uint32_t missing = 0, exceeded = 0;
 #pragma unroll
   for (int r = 0; r < R; ++r) {
-    const long long used = (r < 2) ? lo[2 * r] : hi[2 * (r - 2)];
-    const long long hard = (r < 2) ? lo[2 * r + 1] : hi[2 * (r - 2) + 1];
     const bool constrained = (hm >> r) & 1u;
     const bool present = (rmask >> r) & 1u;
-    const long long total = (long long)((unsigned long long)used + (unsigned long long)q[r]);
     if (constrained && !present && ((compute_mask >> r) & 1u)) missing |= 1u << r;
-    if (constrained && present && q[r] > 0 && total > hard) exceeded |= 1u << r;
+    if (constrained && present && q[r] > 0 && q[r] > h[r]) exceeded |= 1u << r;
   }
   return (missing << 4) | exceeded;
 }
@@ -409,7 +443,7 @@ constexpr int kK2Threads = 256;
 template <int R, bool HAS_MASK, bool VEC>
 __global__ void __launch_bounds__(kK2Threads)
 k2_quota_eval(const uint32_t* __restrict__ ns_id, ReqCols<R> req, const uint8_t* __restrict__ req_mask,
-              size_t n, const QuotaRow* __restrict__ rows, const uint8_t* __restrict__ hard_mask,
+              size_t n, const HeadRow* __restrict__ rows, const uint8_t* __restrict__ hard_mask,
               uint32_t NS, uint32_t compute_mask, uint8_t* __restrict__ verdict) {
   const size_t groups = VEC ? n / 4 : 0;
   for (size_t g = (size_t)blockIdx.x * kK2Threads + threadIdx.x; g < groups;

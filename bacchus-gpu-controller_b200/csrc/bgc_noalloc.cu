@@ -105,7 +105,7 @@ int launch_reduce(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const
   size_t chunk_tiles = tiles / ((size_t)grid * wpb * 4);
   if (chunk_tiles < 1) chunk_tiles = 1;
   if (chunk_tiles > 32) chunk_tiles = 32;
-  kern<<<grid, threads, smem, st>>>(ns, cols, n, d.rows, NS, cap, (uint32_t)chunk_tiles);
+  kern<<<grid, threads, smem, st>>>(ns, cols, n, d.rows, NS, cap, (uint32_t)chunk_tiles, (1u << R) - 1u);
   SCU(cudaGetLastError());
   return BGC_OK;
 }

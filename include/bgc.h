@@ -86,7 +86,11 @@ enum { BGC_UNIT_COUNT = 0, BGC_UNIT_MILLI = 1, BGC_UNIT_BYTES = 2 };
 
 #define BGC_VERDICT_ALLOW 0x00u
 #define BGC_VERDICT_BAD_NS 0xFFu /* ns_id >= NS */
-/* verdict = missing << 4 | exceeded, one bit per resource r < R */
+/* verdict = missing << 4 | exceeded, one bit per resource r < R.
+ * exceeded bit r: namespace constrains r, the pod states r, req > 0 and used + req > hard, decided
+ * without 64-bit overflow (as Kubernetes' Quantity arithmetic would);
+ * missing bit r : namespace constrains r, r is a compute resource (MILLI/BYTES) and the pod does
+ * not state it (req_mask bit clear).  0 = allow. */
 
 /* flags of bgc_usage_reduce* */
 #define BGC_REDUCE_GROUPED 1u    /* hint: pods arrive grouped by namespace (any order of groups) */

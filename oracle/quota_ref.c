@@ -64,8 +64,9 @@ static inline uint8_t eval_one(uint32_t ns, const int64_t *const *req, uint8_t r
     }
     const int64_t q = req[r][j];
     if (q <= 0) continue;
-    const int64_t total = (int64_t)((uint64_t)used[(size_t)r * NS + ns] + (uint64_t)q);
-    if (total > hard[(size_t)r * NS + ns]) exceeded |= 1u << r;
+    /* overflow-free: decided in 128 bits, as Kubernetes' arbitrary-precision Quantity would */
+    const __int128 total = (__int128)used[(size_t)r * NS + ns] + (__int128)q;
+    if (total > (__int128)hard[(size_t)r * NS + ns]) exceeded |= 1u << r;
   }
   return (uint8_t)((missing << 4) | exceeded);
 }

@@ -31,7 +31,10 @@ void quota_ref_usage_reduce(const uint32_t *ns_id, const int64_t *const *req, si
  *   for r < R with hard_mask[ns] bit r set:
  *     req_mask given and bit r clear:  compute resource (compute_mask bit r) → missing bit r;
  *                                      otherwise the request counts as 0 → nothing
- *     else if req > 0 and (int64)(used + req wrapping) > hard → exceeded bit r
+ *     else if req > 0 and used + req > hard, evaluated WITHOUT overflow (in Z) → exceeded bit r
+ *       (SURVEY.md §8 A4 wrote the sum as wrapping only so that CPU and GPU agree; the exact
+ *        comparison is what Kubernetes' Quantity arithmetic decides and is identical whenever the
+ *        64-bit sum does not overflow — see DESIGN.md §3)
  *   ns_id >= NS → QUOTA_REF_VERDICT_BAD_NS.  req_mask may be NULL (all present). */
 void quota_ref_quota_eval(const uint32_t *ns_id, const int64_t *const *req,
                           const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,

@@ -37,9 +37,11 @@ def quota_eval(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask) ->
         present = ((rm >> r) & 1).astype(bool)
         if (compute_mask >> r) & 1:
             missing |= ((constrained & ~present).astype(np.uint8) << r)
+        u = used[r][ns]
         with np.errstate(over="ignore"):
-            total = used[r][ns] + req[r]
-        ex = constrained & present & (req[r] > 0) & (total > hard[r][ns])
+            total = u + req[r]                       # wraps; a positive overflow shows as total < u
+        overflow = (req[r] > 0) & (total < u)       # true sum > INT64_MAX >= hard
+        ex = constrained & present & (req[r] > 0) & (overflow | (total > hard[r][ns]))
         exceeded |= (ex.astype(np.uint8) << r)
     out = ((missing << 4) | exceeded).astype(np.uint8)
     out[bad] = VERDICT_BAD_NS

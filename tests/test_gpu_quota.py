@@ -131,7 +131,7 @@ def test_k2_vs_oracle(engine, oracle, R, with_mask, n):
     assert np.array_equal(got, want)
 
 
-def test_k2_wrapping_sum_and_extremes(engine, oracle):
+def test_k2_overflow_free_compare_and_extremes(engine, oracle):
     NS, R = 4, 2
     used = np.array([[2**63 - 10, -5, 0, 2**62], [0, 0, -2**63, 1]], np.int64)
     hard = np.array([[2**63 - 1, 0, 0, 2**62], [0, -1, 2**63 - 1, 1]], np.int64)
@@ -142,6 +142,18 @@ def test_k2_wrapping_sum_and_extremes(engine, oracle):
     req = [np.array([5, 9, 100, 5, 6, 1, 0, 1, 2**62], np.int64), np.array([0, 1, 2**63 - 1, 0, 1, 2**63 - 1, 5, 0, 0], np.int64)]
     want = oracle.quota_eval(ns, req, None, NS, used, hard, hm, 0)
     assert np.array_equal(engine.quota_eval(ns, req), want)
+    # saturating headroom: every combination of extreme used / hard / req
+    ext = np.array([-2**63, -2**63 + 1, -1, 0, 1, 2**62, 2**63 - 2, 2**63 - 1], np.int64)
+    U, H = np.meshgrid(ext, ext, indexing="ij")
+    NS2 = U.size
+    engine.quota_table_set(H.reshape(1, NS2).copy(), np.ones(NS2, np.uint8), [0])
+    engine.usage_set(U.reshape(1, NS2).copy())
+    ns2 = np.repeat(np.arange(NS2, dtype=np.uint32), ext.size)
+    q2 = [np.tile(ext, NS2)]
+    want2 = oracle.quota_eval(ns2, q2, None, NS2, U.reshape(1, NS2), H.reshape(1, NS2), np.ones(NS2, np.uint8), 0)
+    assert np.array_equal(engine.quota_eval(ns2, q2), want2)
+    py = np.array([int(q > 0 and int(u) + int(q) > int(h)) for u, h in zip(U.ravel(), H.ravel()) for q in ext], np.uint8)
+    assert np.array_equal(want2, py)
 
 
 def test_k2_device_pointers_misaligned(engine, oracle):

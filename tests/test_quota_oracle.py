@@ -56,8 +56,8 @@ def test_quota_eval_c_vs_numpy(oracle, R, with_mask):
     assert (a[::101] == 0xFF).all()
 
 
-def test_quota_eval_wrapping_sum_is_defined(oracle):
-    # used + req wraps modulo 2^64 and is then compared as signed: spec'd so CPU and GPU agree
+def test_quota_eval_is_overflow_free(oracle):
+    # used + req is compared with hard as integers (no 64-bit wrap): a sum past INT64_MAX exceeds
     NS = 1
     used = np.array([[2**63 - 10]], np.int64)
     hard = np.array([[2**63 - 1]], np.int64)
@@ -65,12 +65,17 @@ def test_quota_eval_wrapping_sum_is_defined(oracle):
     ns = np.zeros(3, np.uint32)
     req = [np.array([5, 9, 100], np.int64)]
     v = oracle.quota_eval(ns, req, None, NS, used, hard, hm, 0)
-    # 5 → fits, 9 → exactly hard, 100 → wraps negative → not > hard
-    assert v.tolist() == [0, 0, 0]
+    assert v.tolist() == [0, 0, 1]          # fits, exactly hard, overflows → exceeded
     assert np.array_equal(v, Q.quota_eval(ns, req, None, NS, used, hard, hm, 0))
-    req = [np.array([10], np.int64)]
-    hard2 = np.array([[2**63 - 2]], np.int64)
-    assert oracle.quota_eval(ns[:1], [np.array([9], np.int64)], None, NS, used, hard2, hm, 0).tolist() == [1]
+    # negative usage (a wrapped or corrected table) and extreme limits
+    used = np.array([[-2**63, -5, 2**62, 0]], np.int64)
+    hard = np.array([[2**63 - 1, -1, -2**63, 2**63 - 1]], np.int64)
+    hm = np.ones(4, np.uint8)
+    ns = np.array([0, 0, 1, 1, 2, 3], np.uint32)
+    req = [np.array([2**63 - 1, 1, 4, 5, 1, 2**63 - 1], np.int64)]
+    v = oracle.quota_eval(ns, req, None, 4, used, hard, hm, 0)
+    assert v.tolist() == [0, 0, 0, 1, 1, 0]
+    assert np.array_equal(v, Q.quota_eval(ns, req, None, 4, used, hard, hm, 0))
 
 
 def test_semantics_examples(oracle):
