@@ -52,6 +52,7 @@ struct bgc_ctx {
   bool head_stale = true;
   // K1
   int k1_forced = BGC_K1_AUTO;
+  int k1_shape = 0;                  // scatter kernel launch shape (tuning knob, see bgc_ctx_set_k1_variant)
   const char* last_k1 = "none";
   // staging for host-pointer calls
   Slot slot[kSlots];
@@ -157,6 +158,33 @@ int launch_k1_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
   return BGC_OK;
 }
 
+// arrival-order input -> lean scatter kernel (one persistent CTA per SM, CTA-private table)
+template <int R, int SINK, bool VEC>
+int launch_k1_scatter(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
+                      size_t n, uint32_t cap) {
+  ReqCols<R> cols;
+  for (int r = 0; r < R; ++r) cols.p[r] = req[r];
+  const size_t smem = k1_slot_bytes(ctx, R) * cap + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
+  const size_t groups = (n + 3) / 4;
+  auto go = [&](auto kern, int threads) -> int {
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = ctx->sm_count;
+    if ((size_t)grid * threads > groups) grid = (int)((groups + threads - 1) / threads);
+    if (grid < 1) grid = 1;
+    kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->rows, ctx->NS, cap, ctx->wide_mask);
+    ctx->head_stale = true;
+    ctx->tm.launches++;
+    CU(cudaGetLastError());
+    return BGC_OK;
+  };
+  switch (ctx->k1_shape) {
+    case 1: return go(k1_scatter<R, SINK, VEC, 512, 2>, 512);
+    case 2: return go(k1_scatter<R, SINK, VEC, 1024, 2>, 1024);
+    case 3: return go(k1_scatter<R, SINK, VEC, 512, 1>, 512);
+    default: return go(k1_scatter<R, SINK, VEC, 1024, 1>, 1024);
+  }
+}
+
 template <int R>
 int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
                 size_t n, unsigned flags) {
@@ -178,15 +206,25 @@ int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long lo
   }
   switch (variant) {
     case BGC_K1_GLOBAL:
-      ctx->last_k1 = "global_red";
+      ctx->last_k1 = "segmented_global_red";
       return vec ? launch_k1_inst<R, SINK_GLOBAL, true>(ctx, st, ns, req, n, cap)
                  : launch_k1_inst<R, SINK_GLOBAL, false>(ctx, st, ns, req, n, cap);
     case BGC_K1_SMEM_DIRECT:
-      ctx->last_k1 = "smem_direct";
+      if (!(flags & BGC_REDUCE_GROUPED)) {
+        ctx->last_k1 = "scatter_smem_direct";
+        return vec ? launch_k1_scatter<R, SINK_DIRECT, true>(ctx, st, ns, req, n, cap)
+                   : launch_k1_scatter<R, SINK_DIRECT, false>(ctx, st, ns, req, n, cap);
+      }
+      ctx->last_k1 = "segmented_smem_direct";
       return vec ? launch_k1_inst<R, SINK_DIRECT, true>(ctx, st, ns, req, n, cap)
                  : launch_k1_inst<R, SINK_DIRECT, false>(ctx, st, ns, req, n, cap);
     default:
-      ctx->last_k1 = "smem_hash";
+      if (!(flags & BGC_REDUCE_GROUPED)) {
+        ctx->last_k1 = "scatter_smem_hash";
+        return vec ? launch_k1_scatter<R, SINK_HASH, true>(ctx, st, ns, req, n, cap)
+                   : launch_k1_scatter<R, SINK_HASH, false>(ctx, st, ns, req, n, cap);
+      }
+      ctx->last_k1 = "segmented_smem_hash";
       return vec ? launch_k1_inst<R, SINK_HASH, true>(ctx, st, ns, req, n, cap)
                  : launch_k1_inst<R, SINK_HASH, false>(ctx, st, ns, req, n, cap);
   }
@@ -414,8 +452,9 @@ int bgc_timings_get(bgc_ctx* ctx, bgc_timings* out) {
 
 int bgc_ctx_set_k1_variant(bgc_ctx* ctx, int variant) {
   if (!ctx) return BGC_E_BADARG;
-  NEED(variant >= BGC_K1_AUTO && variant <= BGC_K1_SMEM_HASH, "unknown K1 variant");
-  ctx->k1_forced = variant;
+  NEED((variant & 0xFF) >= BGC_K1_AUTO && (variant & 0xFF) <= BGC_K1_SMEM_HASH, "unknown K1 variant");
+  ctx->k1_forced = variant & 0xFF;
+  ctx->k1_shape = (variant >> 8) & 0xFF;  // bits 8..15: scatter launch shape (development knob)
   return BGC_OK;
 }
 

@@ -31,14 +31,14 @@ struct ReqCols {
 // ------------------------------------------------------------------ load/store helpers
 __device__ __forceinline__ uint4 ldg_nc_u32x4(const uint32_t* p) {
   uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+  asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                : "l"(p));
   return v;
 }
 // 256-bit streaming load (sm_100: LDG.E.256)
 __device__ __forceinline__ void ldg_nc_i64x4(const long long* p, long long (&v)[4]) {
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+  asm("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
                : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
                : "l"(p));
 }
@@ -385,6 +385,163 @@ k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, Qu
         const uint32_t ns = (SINK == SINK_HASH) ? sink.s_key[s] : s;
         red_add_i64(&rows[ns].w[2 * r], (long long)v);
       }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ K1, arrival-order input
+// When the caller does not promise grouped input, merging runs buys nothing (two neighbouring pods
+// share a namespace with probability sum p_i^2), and the segmented machinery above costs ~120
+// issued instructions per pod slot.  k1_scatter is the lean form for that case: every thread takes
+// U groups of 4 consecutive pods, issues all of its loads, then all of its shared-memory atomics
+// (native 32-bit ATOMS on shared-window addresses, so no generic-address conversion per access),
+// and only afterwards looks at the returned old values to propagate the rare carries.
+__device__ __forceinline__ uint32_t atoms_add_u32(uint32_t saddr, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(saddr), "r"(v));
+  return old;
+}
+__device__ __forceinline__ void reds_add_u32(uint32_t saddr, uint32_t v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(saddr), "r"(v));
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ uint32_t atoms_cas_u32(uint32_t saddr, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.shared.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "r"(saddr), "r"(cmp), "r"(val));
+  return old;
+}
+
+template <int R, int SINK>
+struct ScatterCtx {
+  QuotaRow* rows;
+  uint32_t NS, cap, wide_mask, hash_shift;
+  uint32_t lo_base[R];  // shared-window byte address of column r's low words
+  uint32_t hi_base[R];  // ... of its high words (wide columns only)
+  uint32_t key_base;
+
+  // slot of a namespace in the CTA-private table, or kHashEmpty when it has none (hash sink, cold)
+  __device__ __forceinline__ uint32_t slot_of(uint32_t ns) const {
+    if (SINK == SINK_DIRECT) return ns;
+    const uint32_t s = (ns * 0x9E3779B1u) >> hash_shift;
+    const uint32_t kaddr = key_base + s * 4u;
+    uint32_t k = lds_u32(kaddr);
+    if (k == kHashEmpty) {
+      k = atoms_cas_u32(kaddr, kHashEmpty, ns);
+      if (k == kHashEmpty) k = ns;
+    }
+    return k == ns ? s : kHashEmpty;
+  }
+};
+
+template <int R, int SINK, int PODS>
+__device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const uint32_t (&ns)[PODS],
+                                             const long long (&q)[R][PODS]) {
+  uint32_t slot[PODS];
+  uint32_t old[R][PODS];
+#pragma unroll
+  for (int k = 0; k < PODS; ++k) slot[k] = ns[k] < C.NS ? C.slot_of(ns[k]) : kHashEmpty;
+  // phase 1: every low-word atomic of the group is in flight before any result is consumed
+#pragma unroll
+  for (int k = 0; k < PODS; ++k) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t lo = (uint32_t)(unsigned long long)q[r][k];
+      old[r][k] = 0;
+      if (slot[k] != kHashEmpty && lo) old[r][k] = atoms_add_u32(C.lo_base[r] + slot[k] * 4u, lo);
+    }
+  }
+  // phase 2: high words and carries
+#pragma unroll
+  for (int k = 0; k < PODS; ++k) {
+    if (ns[k] >= C.NS) continue;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const unsigned long long v = (unsigned long long)q[r][k];
+      if (slot[k] == kHashEmpty) {  // cold namespace of the hash sink: straight to the global table
+        if (v) red_add_i64(&C.rows[ns[k]].w[2 * r], (long long)v);
+        continue;
+      }
+      const uint32_t lo = (uint32_t)v;
+      const uint32_t hi = (uint32_t)(v >> 32) + (uint32_t)(old[r][k] + lo < old[r][k]);
+      if (hi) {
+        if ((C.wide_mask >> r) & 1u) reds_add_u32(C.hi_base[r] + slot[k] * 4u, hi);
+        else red_add_i64(&C.rows[ns[k]].w[2 * r], (long long)((unsigned long long)hi << 32));
+      }
+    }
+  }
+}
+
+template <int R, int SINK, bool VEC, int THREADS, int U>
+__global__ void __launch_bounds__(THREADS, 1)
+k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRow* rows, uint32_t NS,
+           uint32_t cap, uint32_t wide_mask) {
+  extern __shared__ __align__(16) uint32_t k1_smem[];
+  const uint32_t nwide = __popc(wide_mask & ((1u << R) - 1u));
+  const uint32_t words = (R + nwide) * cap;
+  for (uint32_t i = threadIdx.x; i < words; i += THREADS) k1_smem[i] = 0;
+  if (SINK == SINK_HASH)
+    for (uint32_t i = threadIdx.x; i < cap; i += THREADS) k1_smem[words + i] = kHashEmpty;
+  ScatterCtx<R, SINK> C;
+  C.rows = rows; C.NS = NS; C.cap = cap; C.wide_mask = wide_mask;
+  C.hash_shift = 32 - (31 - __clz(cap | 1));
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(k1_smem);
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    C.lo_base[r] = sbase + (uint32_t)r * cap * 4u;
+    C.hi_base[r] = sbase + (R + __popc(wide_mask & ((1u << r) - 1u))) * cap * 4u;
+  }
+  C.key_base = sbase + words * 4u;
+  __syncthreads();
+
+  const size_t groups = VEC ? n / 4 : 0;
+  const size_t stride = (size_t)gridDim.x * THREADS;
+  size_t g = (size_t)blockIdx.x * THREADS + threadIdx.x;
+  // U groups per trip: all loads first (U*(1+R) independent 128/256-bit requests per thread)
+  for (; g + (U - 1) * stride < groups; g += U * stride) {
+    uint32_t ns[U][4];
+    long long q[U][R][4];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t base = (g + u * stride) * 4;
+      const uint4 v = ldg_nc_u32x4(ns_id + base);
+      ns[u][0] = v.x; ns[u][1] = v.y; ns[u][2] = v.z; ns[u][3] = v.w;
+#pragma unroll
+      for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[u][r]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) scatter_pods<R, SINK, 4>(C, ns[u], q[u]);
+  }
+  for (; g < groups; g += stride) {
+    uint32_t ns[4];
+    long long q[R][4];
+    const size_t base = g * 4;
+    const uint4 v = ldg_nc_u32x4(ns_id + base);
+    ns[0] = v.x; ns[1] = v.y; ns[2] = v.z; ns[3] = v.w;
+#pragma unroll
+    for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
+    scatter_pods<R, SINK, 4>(C, ns, q);
+  }
+  // scalar tail (and everything when the columns are not 16/32-byte aligned)
+  for (size_t i = groups * 4 + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
+    uint32_t ns[1] = {ns_id[i]};
+    long long q[R][1];
+#pragma unroll
+    for (int r = 0; r < R; ++r) q[r][0] = req.p[r][i];
+    scatter_pods<R, SINK, 1>(C, ns, q);
+  }
+
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < R * cap; i += THREADS) {
+    const uint32_t r = i / cap, sl = i - r * cap;
+    const uint32_t hi = ((wide_mask >> r) & 1u) ? k1_smem[(R + __popc(wide_mask & ((1u << r) - 1u))) * cap + sl] : 0u;
+    const unsigned long long v = ((unsigned long long)hi << 32) | k1_smem[i];
+    if (v) {
+      const uint32_t ns = (SINK == SINK_HASH) ? k1_smem[words + sl] : sl;
+      red_add_i64(&rows[ns].w[2 * r], (long long)v);
     }
   }
 }

@@ -9,6 +9,7 @@ from workloads import make_hard, KINDS, UNITS, SEEDS
 pytestmark = pytest.mark.gpu
 
 VARIANTS = [1, 2, 3]  # BGC_K1_GLOBAL, SMEM_DIRECT, SMEM_HASH
+SHAPES = [v | (sh << 8) for v in (2, 3) for sh in (1, 2, 3)]  # scatter-kernel launch shapes (bits 8..15)
 
 
 def _table(engine, oracle, run, NS, R, seed=1, units=None):
@@ -23,7 +24,7 @@ def _compute_mask(units):
 
 
 @pytest.mark.parametrize("R", [1, 2, 3, 4])
-@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("variant", VARIANTS + SHAPES)
 @pytest.mark.parametrize("n,NS", [(1, 1), (127, 3), (128, 10), (129, 10), (4099, 1000), (250_007, 10_000), (300_000, 70_000)])
 def test_k1_variants_random_values(engine, oracle, R, variant, n, NS):
     rng = np.random.default_rng(R * 100 + variant * 10 + n)
@@ -38,6 +39,9 @@ def test_k1_variants_random_values(engine, oracle, R, variant, n, NS):
     got = engine.usage_reduce(ns, req)
     assert np.array_equal(got, want), engine.last_k1_variant()
     assert np.array_equal(engine.usage_get(), want)
+    if variant < 256:
+        got = engine.usage_reduce(ns, req, flags=1)      # grouped hint on shuffled input: slower, still exact
+        assert np.array_equal(got, want), engine.last_k1_variant()
 
 
 @pytest.mark.parametrize("variant", [0] + VARIANTS)

@@ -56,7 +56,10 @@ def main():
         eng.synth_pods_dev(bgc.synth_params(0xB2000003, 0, NS, dist, grouped, n, a, b, d_cdf, KINDS[R]), 0, n, ns, req)
         eng.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
         ref = None
-        for variant in (1, 2, 3):
+        todo = [1, 2, 3] if grouped else [1] + [v | (sh << 8) for v in (2, 3) for sh in (0, 1, 2, 3)]
+        if not grouped and (dist and NS > 100):
+            todo = todo[1:]          # global reds on a Zipf head take tens of ms: measured once, skip
+        for variant in todo:
             eng.set_k1_variant(variant)
             flags = 1 if grouped else 0
             try:
@@ -69,7 +72,7 @@ def main():
                 ref = used
             gbs = n * (4 + 8 * R) / ms / 1e6
             print(json.dumps({"kernel": "k1", "NS": NS, "R": R, "dist": "zipf%.1f" % s if dist else "uniform", "grouped": grouped,
-                              "variant": eng.last_k1_variant(), "ms": round(ms, 4), "GBps": round(gbs, 1), "frac": round(gbs / PEAK, 3),
+                              "variant": eng.last_k1_variant(), "shape": variant >> 8, "ms": round(ms, 4), "GBps": round(gbs, 1), "frac": round(gbs / PEAK, 3),
                               "Gpods_s": round(n / ms / 1e6, 2), "same_as_first": bool(np.array_equal(used, ref))}), flush=True)
         # K2 on the same columns
         hard, hm = make_hard(ref, 1)
