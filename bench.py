@@ -38,6 +38,19 @@ WORKLOADS = {
 SEED = {"c3": 0xB2000003, "c2": 0xB2000002, "c5": 0xB2000005}
 
 
+def ncu_traffic(workload: str, kernel: str, n: int, default_n: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture of the
+    same command (profiles/r01_ncu_traffic.json); only valid for the workload/size it was taken on."""
+    p = os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")
+    try:
+        d = json.load(open(p))[workload][kernel]
+    except Exception:
+        return None
+    if n != default_n:
+        return None
+    return d["dram_bytes_read"] + d["dram_bytes_write"]
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -341,7 +354,9 @@ def main():
                        "l2": f"inputs {(k1_bytes + k2_bytes) / 1e6:.0f} MB per step >> 126 MB L2 (no flush needed)" if k1_bytes > 4e8 else "inputs fit in L2: treat GB/s as cache bandwidth",
                        "k1_variant": eng.last_k1_variant(), "sharding": "namespace-hash shards, independent per rank, no collective"},
             "roofline": {"bound": "hbm", "kernel": "k1_usage_reduce", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "frac_of_8000_datasheet": achieved / 8000.0,
+                         "frac": achieved / peak,
+                         "traffic": None if args.grouped or args.k1 else ncu_traffic(args.workload, "k1_usage_reduce", n, WORKLOADS[args.workload][0]),
+                         "algorithmic_bytes_per_launch": k1_bytes, "peak_source": peak_src, "frac_of_8000_datasheet": achieved / 8000.0,
                          "algorithmic_bytes_per_pod": 4 + 8 * R, "k1_ms": k1_ms,
                          "k2": {"ms": k2_ms, "achieved": k2_bytes / (k2_ms * 1e-3) / 1e9, "frac": k2_bytes / (k2_ms * 1e-3) / 1e9 / peak,
                                 "algorithmic_bytes_per_pod": 4 + 8 * R + 1}},
