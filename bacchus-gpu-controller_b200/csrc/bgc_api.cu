@@ -5,6 +5,7 @@
 // integer status codes, no exceptions across the boundary, no CPU fallback.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -21,6 +22,8 @@ namespace {
 constexpr size_t kChunkPods = size_t(4) << 20;      // host-pointer calls move 4 Mi pods per stage
 constexpr size_t kSmemBudget = 224 * 1024;          // CTA-private K1 table budget (<= 227 KB opt-in)
 constexpr int kSlots = 2;
+constexpr size_t kZeroCopyMaxPods = 262144;         // host batches up to this size take the latency path
+constexpr size_t kZeroCopyBytes = kZeroCopyMaxPods * (4 + 8 * 4 + 1 + 1 + 2) + 16 * 256;
 
 struct Slot {
   uint32_t* ns = nullptr;
@@ -55,12 +58,17 @@ struct bgc_ctx {
   int k1_shape = 0;                  // scatter kernel launch shape (tuning knob, see bgc_ctx_set_k1_variant)
   const char* last_k1 = "none";
   // staging for host-pointer calls
+  size_t zc_max_pods = kZeroCopyMaxPods;  // BGC_ZEROCOPY_MAX_PODS overrides (0 disables the latency path)
   Slot slot[kSlots];
   size_t slot_pods = 0;
   int slot_R = 0;
   std::vector<cudaEvent_t> ev_pool;
   size_t ev_next = 0;
   unsigned long long* d_scratch = nullptr;  // 256 x u64
+  // latency path: small host batches are read by the kernel straight over PCIe (zero-copy) from
+  // the caller's pinned buffers, or from this pinned, device-mapped staging area
+  uint8_t* zc_host = nullptr;
+  uint8_t* zc_dev = nullptr;
   bgc_timings tm{};
 };
 
@@ -346,6 +354,36 @@ int ensure_slots(bgc_ctx* ctx, size_t pods, int R) {
   return BGC_OK;
 }
 
+// Latency path helpers.  A column that already lives in pinned (page-locked) host memory is handed
+// to the kernel as is; a pageable one is copied into the context's pinned staging area first.
+struct ZcCursor {
+  size_t off = 0;
+};
+
+const void* zc_in(bgc_ctx* ctx, ZcCursor& cur, const void* host, size_t bytes) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, host) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer)
+    return a.devicePointer;
+  cudaGetLastError();
+  const size_t at = cur.off;
+  cur.off = (cur.off + bytes + 255) & ~size_t(255);
+  std::memcpy(ctx->zc_host + at, host, bytes);
+  return ctx->zc_dev + at;
+}
+
+// returns the device-visible address to write to; *bounce = staging address to copy back from (or null)
+void* zc_out(bgc_ctx* ctx, ZcCursor& cur, void* host, size_t bytes, uint8_t** bounce) {
+  cudaPointerAttributes a{};
+  *bounce = nullptr;
+  if (cudaPointerGetAttributes(&a, host) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer)
+    return a.devicePointer;
+  cudaGetLastError();
+  const size_t at = cur.off;
+  cur.off = (cur.off + bytes + 255) & ~size_t(255);
+  *bounce = ctx->zc_host + at;
+  return ctx->zc_dev + at;
+}
+
 struct Spans {
   std::vector<cudaEvent_t> h2d, k, d2h;  // start/stop pairs
 };
@@ -389,11 +427,17 @@ int bgc_ctx_create(int device, bgc_ctx** out) {
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaMalloc(&ctx->d_scratch, 256 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaHostAlloc(&ctx->zc_host, kZeroCopyBytes, cudaHostAllocMapped);
+  if (e == cudaSuccess) e = cudaHostGetDevicePointer(&ctx->zc_dev, ctx->zc_host, 0);
   if (e != cudaSuccess) {
     delete ctx;
     return BGC_E_CUDA;
   }
   ctx->stream = ctx->own_stream;
+  if (const char* v = std::getenv("BGC_ZEROCOPY_MAX_PODS")) {
+    const long long want = std::atoll(v);
+    ctx->zc_max_pods = want < 0 ? 0 : ((size_t)want > kZeroCopyMaxPods ? kZeroCopyMaxPods : (size_t)want);
+  }
   *out = ctx;
   return BGC_OK;
 }
@@ -414,6 +458,7 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   cudaFree(ctx->d_hard_mask);
   cudaFree(ctx->d_table_tmp);
   cudaFree(ctx->d_scratch);
+  cudaFreeHost(ctx->zc_host);
   cudaStreamDestroy(ctx->own_stream);
   cudaStreamDestroy(ctx->h2d_stream);
   cudaStreamDestroy(ctx->d2h_stream);
@@ -477,11 +522,28 @@ int bgc_policy_eval(bgc_ctx* ctx, const uint8_t* op, const uint16_t* flags, size
   ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   if (n == 0) return BGC_OK;
+  if (n <= ctx->zc_max_pods) {  // latency path: one launch, no staged copies
+    ZcCursor cur;
+    uint8_t *b0, *b1;
+    const uint8_t* z_op = static_cast<const uint8_t*>(zc_in(ctx, cur, op, n));
+    const uint16_t* z_fl = static_cast<const uint16_t*>(zc_in(ctx, cur, flags, n * 2));
+    uint8_t* z_c = static_cast<uint8_t*>(zc_out(ctx, cur, code, n, &b0));
+    uint8_t* z_p = static_cast<uint8_t*>(zc_out(ctx, cur, patch_mask, n, &b1));
+    if (int rc0 = launch_k0(ctx, ctx->own_stream, z_op, z_fl, n, z_c, z_p)) return rc0;
+    CU(cudaStreamSynchronize(ctx->own_stream));
+    if (b0) std::memcpy(code, b0, n);
+    if (b1) std::memcpy(patch_mask, b1, n);
+    return BGC_OK;
+  }
   int rc = ensure_slots(ctx, n, ctx->slot_R);
   if (rc) return rc;
   ctx->ev_next = 0;
   Spans sp;
   const size_t chunk = ctx->slot_pods;
+  const bool single = n <= chunk;  // one chunk: copy-in, kernel, copy-out on one stream, no hand-offs
+  cudaStream_t hs = single ? ctx->own_stream : ctx->h2d_stream;
+  cudaStream_t ds = single ? ctx->own_stream : ctx->d2h_stream;
+  (void)ds;
   size_t k = 0;
   for (size_t off = 0; off < n; off += chunk, ++k) {
     Slot& s = ctx->slot[k % kSlots];
@@ -489,30 +551,34 @@ int bgc_policy_eval(bgc_ctx* ctx, const uint8_t* op, const uint16_t* flags, size
     cudaEvent_t a = next_event(ctx), b = next_event(ctx), c = next_event(ctx), d = next_event(ctx),
                 e = next_event(ctx), f = next_event(ctx);
     if (!f) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
-    if (s.used) CU(cudaStreamWaitEvent(ctx->h2d_stream, s.free_ev, 0));
-    CU(cudaEventRecord(a, ctx->h2d_stream));
-    CU(cudaMemcpyAsync(s.mask, op + off, m, cudaMemcpyHostToDevice, ctx->h2d_stream));  // op column staged in `mask`
-    CU(cudaMemcpyAsync(s.flags, flags + off, m * 2, cudaMemcpyHostToDevice, ctx->h2d_stream));
-    CU(cudaEventRecord(b, ctx->h2d_stream));
-    CU(cudaEventRecord(s.h2d_done, ctx->h2d_stream));
-    CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+    if (s.used && !single) CU(cudaStreamWaitEvent(hs, s.free_ev, 0));
+    CU(cudaEventRecord(a, hs));
+    CU(cudaMemcpyAsync(s.mask, op + off, m, cudaMemcpyHostToDevice, hs));  // op column staged in `mask`
+    CU(cudaMemcpyAsync(s.flags, flags + off, m * 2, cudaMemcpyHostToDevice, hs));
+    CU(cudaEventRecord(b, hs));
+    if (!single) {
+      CU(cudaEventRecord(s.h2d_done, hs));
+      CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+    }
     CU(cudaEventRecord(c, ctx->own_stream));
     rc = launch_k0(ctx, ctx->own_stream, s.mask, s.flags, m, s.out0, s.out1);
     if (rc) return rc;
     CU(cudaEventRecord(d, ctx->own_stream));
-    CU(cudaEventRecord(s.k_done, ctx->own_stream));
-    CU(cudaStreamWaitEvent(ctx->d2h_stream, s.k_done, 0));
-    CU(cudaEventRecord(e, ctx->d2h_stream));
-    CU(cudaMemcpyAsync(code + off, s.out0, m, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-    CU(cudaMemcpyAsync(patch_mask + off, s.out1, m, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-    CU(cudaEventRecord(f, ctx->d2h_stream));
-    CU(cudaEventRecord(s.free_ev, ctx->d2h_stream));
-    s.used = true;
+    if (!single) {
+      CU(cudaEventRecord(s.k_done, ctx->own_stream));
+      CU(cudaStreamWaitEvent(ds, s.k_done, 0));
+    }
+    CU(cudaEventRecord(e, ds));
+    CU(cudaMemcpyAsync(code + off, s.out0, m, cudaMemcpyDeviceToHost, ds));
+    CU(cudaMemcpyAsync(patch_mask + off, s.out1, m, cudaMemcpyDeviceToHost, ds));
+    CU(cudaEventRecord(f, ds));
+    if (!single) CU(cudaEventRecord(s.free_ev, ds));
+    s.used = !single;
     sp.h2d.push_back(a); sp.h2d.push_back(b);
     sp.k.push_back(c); sp.k.push_back(d);
     sp.d2h.push_back(e); sp.d2h.push_back(f);
   }
-  CU(cudaStreamSynchronize(ctx->d2h_stream));
+  CU(cudaStreamSynchronize(ds));
   return finish_timings(ctx, sp);
 }
 
@@ -621,25 +687,29 @@ int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
     if ((rc = ensure_slots(ctx, n, R))) return rc;
     ctx->ev_next = 0;
     const size_t chunk = ctx->slot_pods;
+    const bool single = n <= chunk;
+    cudaStream_t hs = single ? ctx->own_stream : ctx->h2d_stream;
     size_t k = 0;
     for (size_t off = 0; off < n; off += chunk, ++k) {
       Slot& s = ctx->slot[k % kSlots];
       const size_t m = (n - off < chunk) ? n - off : chunk;
       cudaEvent_t a = next_event(ctx), b = next_event(ctx), c = next_event(ctx), d = next_event(ctx);
       if (!d) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
-      if (s.used) CU(cudaStreamWaitEvent(ctx->h2d_stream, s.free_ev, 0));
-      CU(cudaEventRecord(a, ctx->h2d_stream));
-      CU(cudaMemcpyAsync(s.ns, ns_id + off, m * 4, cudaMemcpyHostToDevice, ctx->h2d_stream));
+      if (s.used && !single) CU(cudaStreamWaitEvent(hs, s.free_ev, 0));
+      CU(cudaEventRecord(a, hs));
+      CU(cudaMemcpyAsync(s.ns, ns_id + off, m * 4, cudaMemcpyHostToDevice, hs));
       for (int r = 0; r < R; ++r)
-        CU(cudaMemcpyAsync(s.req[r], req[r] + off, m * 8, cudaMemcpyHostToDevice, ctx->h2d_stream));
-      CU(cudaEventRecord(b, ctx->h2d_stream));
-      CU(cudaEventRecord(s.h2d_done, ctx->h2d_stream));
-      CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+        CU(cudaMemcpyAsync(s.req[r], req[r] + off, m * 8, cudaMemcpyHostToDevice, hs));
+      CU(cudaEventRecord(b, hs));
+      if (!single) {
+        CU(cudaEventRecord(s.h2d_done, hs));
+        CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+      }
       CU(cudaEventRecord(c, ctx->own_stream));
       if ((rc = launch_k1(ctx, ctx->own_stream, s.ns, s.req, m, flags))) return rc;
       CU(cudaEventRecord(d, ctx->own_stream));
-      CU(cudaEventRecord(s.free_ev, ctx->own_stream));
-      s.used = true;
+      if (!single) CU(cudaEventRecord(s.free_ev, ctx->own_stream));
+      s.used = !single;
       sp.h2d.push_back(a); sp.h2d.push_back(b);
       sp.k.push_back(c); sp.k.push_back(d);
     }
@@ -684,10 +754,27 @@ int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* re
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   if (n == 0) return BGC_OK;
   int rc;
+  if (n <= ctx->zc_max_pods) {  // latency path: one launch, the kernel reads/writes host memory itself
+    ZcCursor cur;
+    uint8_t* bounce;
+    const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+    const uint32_t* z_ns = static_cast<const uint32_t*>(zc_in(ctx, cur, ns_id, n * 4));
+    for (int r = 0; r < R; ++r) cols[r] = static_cast<const long long*>(zc_in(ctx, cur, req[r], n * 8));
+    const uint8_t* z_mask = req_mask ? static_cast<const uint8_t*>(zc_in(ctx, cur, req_mask, n)) : nullptr;
+    uint8_t* z_v = static_cast<uint8_t*>(zc_out(ctx, cur, verdict, n, &bounce));
+    if ((rc = launch_k2(ctx, ctx->own_stream, z_ns, cols, z_mask, n, z_v))) return rc;
+    CU(cudaStreamSynchronize(ctx->own_stream));
+    if (bounce) std::memcpy(verdict, bounce, n);
+    return BGC_OK;
+  }
   if ((rc = ensure_slots(ctx, n, R))) return rc;
   ctx->ev_next = 0;
   Spans sp;
   const size_t chunk = ctx->slot_pods;
+  const bool single = n <= chunk;  // one chunk: copy-in, kernel, copy-out on one stream, no hand-offs
+  cudaStream_t hs = single ? ctx->own_stream : ctx->h2d_stream;
+  cudaStream_t ds = single ? ctx->own_stream : ctx->d2h_stream;
+  (void)ds;
   size_t k = 0;
   for (size_t off = 0; off < n; off += chunk, ++k) {
     Slot& s = ctx->slot[k % kSlots];
@@ -695,30 +782,34 @@ int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* re
     cudaEvent_t a = next_event(ctx), b = next_event(ctx), c = next_event(ctx), d = next_event(ctx),
                 e = next_event(ctx), f = next_event(ctx);
     if (!f) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
-    if (s.used) CU(cudaStreamWaitEvent(ctx->h2d_stream, s.free_ev, 0));
-    CU(cudaEventRecord(a, ctx->h2d_stream));
-    CU(cudaMemcpyAsync(s.ns, ns_id + off, m * 4, cudaMemcpyHostToDevice, ctx->h2d_stream));
+    if (s.used && !single) CU(cudaStreamWaitEvent(hs, s.free_ev, 0));
+    CU(cudaEventRecord(a, hs));
+    CU(cudaMemcpyAsync(s.ns, ns_id + off, m * 4, cudaMemcpyHostToDevice, hs));
     for (int r = 0; r < R; ++r)
-      CU(cudaMemcpyAsync(s.req[r], req[r] + off, m * 8, cudaMemcpyHostToDevice, ctx->h2d_stream));
-    if (req_mask) CU(cudaMemcpyAsync(s.mask, req_mask + off, m, cudaMemcpyHostToDevice, ctx->h2d_stream));
-    CU(cudaEventRecord(b, ctx->h2d_stream));
-    CU(cudaEventRecord(s.h2d_done, ctx->h2d_stream));
-    CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+      CU(cudaMemcpyAsync(s.req[r], req[r] + off, m * 8, cudaMemcpyHostToDevice, hs));
+    if (req_mask) CU(cudaMemcpyAsync(s.mask, req_mask + off, m, cudaMemcpyHostToDevice, hs));
+    CU(cudaEventRecord(b, hs));
+    if (!single) {
+      CU(cudaEventRecord(s.h2d_done, hs));
+      CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
+    }
     CU(cudaEventRecord(c, ctx->own_stream));
     if ((rc = launch_k2(ctx, ctx->own_stream, s.ns, s.req, req_mask ? s.mask : nullptr, m, s.out0))) return rc;
     CU(cudaEventRecord(d, ctx->own_stream));
-    CU(cudaEventRecord(s.k_done, ctx->own_stream));
-    CU(cudaStreamWaitEvent(ctx->d2h_stream, s.k_done, 0));
-    CU(cudaEventRecord(e, ctx->d2h_stream));
-    CU(cudaMemcpyAsync(verdict + off, s.out0, m, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-    CU(cudaEventRecord(f, ctx->d2h_stream));
-    CU(cudaEventRecord(s.free_ev, ctx->d2h_stream));
-    s.used = true;
+    if (!single) {
+      CU(cudaEventRecord(s.k_done, ctx->own_stream));
+      CU(cudaStreamWaitEvent(ds, s.k_done, 0));
+    }
+    CU(cudaEventRecord(e, ds));
+    CU(cudaMemcpyAsync(verdict + off, s.out0, m, cudaMemcpyDeviceToHost, ds));
+    CU(cudaEventRecord(f, ds));
+    if (!single) CU(cudaEventRecord(s.free_ev, ds));
+    s.used = !single;
     sp.h2d.push_back(a); sp.h2d.push_back(b);
     sp.k.push_back(c); sp.k.push_back(d);
     sp.d2h.push_back(e); sp.d2h.push_back(f);
   }
-  CU(cudaStreamSynchronize(ctx->d2h_stream));
+  CU(cudaStreamSynchronize(ds));
   return finish_timings(ctx, sp);
 }
 
