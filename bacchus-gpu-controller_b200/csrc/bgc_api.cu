@@ -121,7 +121,7 @@ cudaEvent_t next_event(bgc_ctx* ctx) {
 int launch_k0(bgc_ctx* ctx, cudaStream_t st, const uint8_t* op, const uint16_t* flags, size_t n,
               uint8_t* code, uint8_t* pm) {
   if (n == 0) return BGC_OK;
-  const int vec = aligned(op, 16) && aligned(flags, 16) && aligned(code, 16) && aligned(pm, 16);
+  const int vec = aligned(op, 32) && aligned(flags, 32) && aligned(code, 32) && aligned(pm, 32);
   const int grid = grid_for((n + kK0PerThread - 1) / kK0PerThread, kK0Threads, ctx->sm_count * 8);
   k0_policy_eval<<<grid, kK0Threads, 0, st>>>(op, flags, n, code, pm, vec);
   ctx->tm.launches++;

@@ -48,6 +48,17 @@ __device__ __forceinline__ void ldg_row_half(const long long* p, long long (&v)[
                : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
                : "l"(p));
 }
+// 256-bit streaming load / store of 8 words (one full 32-byte sector per thread)
+__device__ __forceinline__ void ldg_nc_u32x8(const void* p, uint32_t (&v)[8]) {
+  asm("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+      : "l"(p));
+}
+__device__ __forceinline__ void stg_u32x8(void* p, const uint32_t (&v)[8]) {
+  asm volatile("st.global.L1::no_allocate.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]),
+               "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
 __device__ __forceinline__ void red_add_i64(long long* p, long long v) {
   asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
@@ -88,7 +99,7 @@ __device__ __forceinline__ uint32_t policy_decide(uint32_t op, uint32_t f) {
 // The decision is a function of 12 bits, so each CTA tabulates it once (4096 x u16 = 8 KB of
 // shared memory) and the streaming loop is one LDS per request: 3 B in, 2 B out per request.
 constexpr int kK0Threads = 256;
-constexpr int kK0PerThread = 16;
+constexpr int kK0PerThread = 32;
 
 static __global__ void __launch_bounds__(kK0Threads)
 k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flags, size_t n,
@@ -98,24 +109,23 @@ k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flag
     lut[i] = (uint16_t)policy_decide(i >> 10, i & 1023u);
   __syncthreads();
 
+  // 32 requests per thread, every access a whole 32-byte sector: one 256-bit op load, two 256-bit
+  // flags loads, one 256-bit store each for code and patch_mask
   const size_t groups = vec_ok ? n / kK0PerThread : 0;
   for (size_t g = (size_t)blockIdx.x * kK0Threads + threadIdx.x; g < groups;
        g += (size_t)gridDim.x * kK0Threads) {
     const size_t base = g * kK0PerThread;
-    const uint4 o = ldg_nc_u32x4(reinterpret_cast<const uint32_t*>(op + base));
-    const uint4 f0 = ldg_nc_u32x4(reinterpret_cast<const uint32_t*>(flags + base));
-    const uint4 f1 = ldg_nc_u32x4(reinterpret_cast<const uint32_t*>(flags + base + 8));
-    const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
-    const uint32_t fw[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
-    uint32_t cw[4], pw[4];
+    uint32_t ow[8], fw[16], cw[8], pw[8];
+    ldg_nc_u32x8(op + base, ow);
+    ldg_nc_u32x8(flags + base, *reinterpret_cast<uint32_t(*)[8]>(&fw[0]));
+    ldg_nc_u32x8(flags + base + 16, *reinterpret_cast<uint32_t(*)[8]>(&fw[8]));
 #pragma unroll
-    for (int w = 0; w < 4; ++w) {
+    for (int w = 0; w < 8; ++w) {
       uint32_t c = 0, p = 0;
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
-        const uint32_t o1 = (ow[w] >> (8 * b)) & 3u;  // anything outside 0..2 is "other"
-        const uint32_t raw = (ow[w] >> (8 * b)) & 0xFFu;
-        const uint32_t opv = raw > 2u ? 3u : o1;
+        const uint32_t raw = (ow[w] >> (8 * b)) & 0xFFu;   // anything outside 0..2 is "other"
+        const uint32_t opv = raw > 2u ? 3u : raw;
         const uint32_t fl = (fw[w * 2 + (b >> 1)] >> (16 * (b & 1))) & 1023u;
         const uint32_t e = lut[(opv << 10) | fl];
         c |= (e & 0xFFu) << (8 * b);
@@ -124,10 +134,10 @@ k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flag
       cw[w] = c;
       pw[w] = p;
     }
-    *reinterpret_cast<uint4*>(code + base) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
-    *reinterpret_cast<uint4*>(patch_mask + base) = make_uint4(pw[0], pw[1], pw[2], pw[3]);
+    stg_u32x8(code + base, cw);
+    stg_u32x8(patch_mask + base, pw);
   }
-  // scalar tail (and the whole batch when the pointers are not 16-byte aligned)
+  // scalar tail (and the whole batch when the pointers are not 32-byte aligned)
   for (size_t i = groups * kK0PerThread + (size_t)blockIdx.x * kK0Threads + threadIdx.x; i < n;
        i += (size_t)gridDim.x * kK0Threads) {
     const uint32_t raw = op[i];

@@ -1,0 +1,109 @@
+"""BASELINE.json configs[0] (C1): in-process replay, no cluster, of
+  (1a) 10k UserBootstrap AdmissionReviews through the batched mutate() (the only thing the reference
+       admission handler can replay: src/admission.rs:184-431) — covered in test_gpu_policy.py; and
+  (1b) 10k Pod-create records against 100 namespace quotas: pod JSON → columns by the C++ flattener
+       (row A5), usage over the running pods (K1), verdicts for the candidates (K2), all compared with
+       an independent pure-Python evaluation of the same pod objects.  Not a reference path: the
+       reference never evaluates pods."""
+import json
+from fractions import Fraction
+
+import numpy as np
+import pytest
+
+from workloads import C1_KEYS, c1_namespaces, c1_pods
+
+pytestmark = pytest.mark.gpu
+
+_SUFFIX = {"": Fraction(1), "m": Fraction(1, 1000), "k": Fraction(1000), "M": Fraction(10**6), "G": Fraction(10**9),
+           "Ki": Fraction(1 << 10), "Mi": Fraction(1 << 20), "Gi": Fraction(1 << 30)}
+
+
+def _quantity(s: str) -> Fraction:
+    """Tiny exact Kubernetes-quantity reader for the strings the C1 generator emits."""
+    if "e" in s:                       # decimal-exponent form (no SI suffix allowed with it)
+        mant, exp = s.split("e")
+        return Fraction(mant) * Fraction(10) ** int(exp)
+    i = len(s)
+    while i and not (s[i - 1].isdigit() or s[i - 1] == "."):
+        i -= 1
+    return Fraction(s[:i]) * _SUFFIX[s[i:]]
+
+
+def _ceil(f: Fraction) -> int:
+    return -((-f.numerator) // f.denominator)
+
+
+def _pod_usage(pod, key):
+    """max(sum of containers, max of init containers) + overhead, in canonical units (python ints)."""
+    res = key.split(".", 1)[1] if key.startswith(("requests.", "limits.")) else key
+    milli = res == "cpu"
+    def val(d):
+        q = (d or {}).get(res)
+        return None if q is None else _ceil(_quantity(q) * (1000 if milli else 1))
+    spec = pod["spec"]
+    app = [val(c["resources"].get("requests")) for c in spec["containers"]]
+    init = [val(c["resources"].get("requests")) for c in spec.get("initContainers", [])]
+    stated = all(v is not None for v in app + init)
+    total = max(sum(v or 0 for v in app), max([v or 0 for v in init], default=0)) + (val(spec.get("overhead")) or 0)
+    return total, stated
+
+
+def test_c1_pod_reviews_against_100_namespace_quotas(bgc, engine):
+    namespaces = c1_namespaces()
+    nsmap = bgc.pods.NamespaceMap()
+    for ns in namespaces:
+        nsmap.intern(ns["name"])
+    R = len(C1_KEYS)
+    hard = np.zeros((R, len(namespaces)), np.int64)
+    hard_mask = np.zeros(len(namespaces), np.uint8)
+    for i, ns in enumerate(namespaces):
+        h, unit = bgc.pods.hard_from_sheet_row(ns["cpu"], ns["memory"], ns["gpu"], ns["storage"], ns["mig"], C1_KEYS)
+        hard[:, i] = h
+        hard_mask[i] = (1 << R) - 1 if ns["has_quota"] else 0
+    engine.quota_table_set(hard, hard_mask, unit)
+
+    running = c1_pods(10_000, namespaces, running=True)
+    cands = c1_pods(10_000, namespaces, running=False)
+    cands[17]["metadata"]["namespace"] = "not-a-namespace"
+
+    r_ns, r_req, r_mask, _ = bgc.pods.flatten_pods(running, C1_KEYS, nsmap, intern=False)
+    used = engine.usage_reduce(r_ns, r_req)
+    c_ns, c_req, c_mask, _ = bgc.pods.flatten_pods(cands, C1_KEYS, nsmap, intern=False)
+    verdict = engine.quota_eval(c_ns, c_req, c_mask)
+
+    # independent evaluation in plain Python on the pod objects themselves
+    idx = {ns["name"]: i for i, ns in enumerate(namespaces)}
+    want_used = [[0] * len(namespaces) for _ in range(R)]
+    live = 0
+    for pod in running:
+        if pod["status"]["phase"] in ("Succeeded", "Failed"):
+            continue
+        live += 1
+        for r, key in enumerate(C1_KEYS):
+            want_used[r][idx[pod["metadata"]["namespace"]]] += _pod_usage(pod, key)[0]
+    assert live == r_ns.shape[0]
+    assert used.tolist() == want_used
+    compute = [False, True, True, False]
+    want = []
+    for pod in cands:
+        i = idx.get(pod["metadata"]["namespace"])
+        if i is None:
+            want.append(0xFF)
+            continue
+        missing = exceeded = 0
+        for r, key in enumerate(C1_KEYS):
+            if not (hard_mask[i] >> r) & 1:
+                continue
+            q, stated = _pod_usage(pod, key)
+            if not stated:
+                if compute[r]:
+                    missing |= 1 << r
+                continue
+            if q > 0 and want_used[r][i] + q > int(hard[r][i]):
+                exceeded |= 1 << r
+        want.append((missing << 4) | exceeded)
+    assert verdict.tolist() == want
+    deny = np.mean(np.array(want) != 0)
+    assert 0.05 < deny < 0.999
+    assert verdict[17] == bgc.VERDICT_BAD_NS

@@ -38,3 +38,54 @@ def make_hard(used: np.ndarray, seed: int):
     hm = _sm64(ns ^ np.uint64(seed ^ 0x5151))
     hard_mask = np.where((hm % np.uint64(100)) < np.uint64(5), 0, (1 << R) - 1).astype(np.uint8)
     return hard, hard_mask
+
+
+# ---------------------------------------------------------------- C1 (BASELINE.json configs[0])
+C1_KEYS = ["requests.nvidia.com/gpu", "requests.cpu", "requests.memory", "requests.nvidia.com/mig-1g.10gb"]
+
+
+def c1_namespaces(seed: int = SEEDS["C1"], count: int = 100):
+    """100 namespaces `ns-000..099`, each with the quota a sheet row would give it
+    (reference src/synchronizer.rs:249-281): cpu in {8,16,32,64} cores, memory in {32,64,128,256} Gi,
+    gpu in {1,2,4,8}, mig in {0,1,2}, storage in {100,500} Gi.  5 namespaces have no quota object."""
+    rng = np.random.default_rng(seed)
+    rows = []
+    for i in range(count):
+        rows.append(dict(name=f"ns-{i:03d}", cpu=int(rng.choice([8, 16, 32, 64])), memory=int(rng.choice([32, 64, 128, 256])),
+                         gpu=int(rng.choice([1, 2, 4, 8])), mig=int(rng.choice([0, 1, 2])), storage=int(rng.choice([100, 500])),
+                         has_quota=bool(i % 20 != 7)))
+    return rows
+
+
+def c1_pods(n: int, namespaces, seed: int = SEEDS["C1"], running: bool = True):
+    """Synthetic Pod JSON objects (the shape kube-apiserver would send in a pod-create AdmissionReview)."""
+    rng = np.random.default_rng(seed + (1 if running else 2))
+    pods = []
+    cpu_choices = ["250m", "500m", "1", "2", "4000m", "0.5", "5e-1", "1.5"]
+    mem_choices = ["256Mi", "1Gi", "2Gi", "4096Mi", "8Gi", "1G", "1500M"]
+    for i in range(n):
+        ns = namespaces[int(rng.integers(0, len(namespaces)))]["name"]
+        nc = int(rng.integers(1, 4))
+        containers = []
+        for c in range(nc):
+            req = {}
+            if rng.random() < 0.97:
+                req["cpu"] = str(rng.choice(cpu_choices))
+            if rng.random() < 0.97:
+                req["memory"] = str(rng.choice(mem_choices))
+            if rng.random() < 0.3:
+                req["nvidia.com/gpu"] = str(int(rng.choice([1, 1, 2, 4])))
+            if rng.random() < 0.05:
+                req["nvidia.com/mig-1g.10gb"] = "1"
+            containers.append({"name": f"c{c}", "resources": {"requests": req, "limits": dict(req)}})
+        spec = {"containers": containers}
+        if rng.random() < 0.2:
+            spec["initContainers"] = [{"name": "init", "resources": {"requests": {"cpu": str(rng.choice(["2", "6"])), "memory": "512Mi"}}}]
+        if rng.random() < 0.1:
+            spec["overhead"] = {"cpu": "100m", "memory": "64Mi"}
+        phase = "Running" if running else "Pending"
+        if running and rng.random() < 0.1:
+            phase = str(rng.choice(["Succeeded", "Failed"]))
+        pods.append({"apiVersion": "v1", "kind": "Pod", "metadata": {"name": f"pod-{i}", "namespace": ns},
+                     "spec": spec, "status": {"phase": phase}})
+    return pods
