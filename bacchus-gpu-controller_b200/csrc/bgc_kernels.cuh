@@ -452,8 +452,27 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
                                              const long long (&q)[R][PODS]) {
   uint32_t slot[PODS];
   uint32_t old[R][PODS];
+  if (SINK == SINK_HASH) {
+    // all key probes of the group are issued before any is examined (independent LDS in flight)
+    uint32_t s[PODS], key[PODS];
 #pragma unroll
-  for (int k = 0; k < PODS; ++k) slot[k] = ns[k] < C.NS ? C.slot_of(ns[k]) : kHashEmpty;
+    for (int k = 0; k < PODS; ++k) {
+      s[k] = (ns[k] * 0x9E3779B1u) >> C.hash_shift;
+      key[k] = lds_u32(C.key_base + s[k] * 4u);
+    }
+#pragma unroll
+    for (int k = 0; k < PODS; ++k) {
+      uint32_t kk = key[k];
+      if (ns[k] < C.NS && kk == kHashEmpty) {  // claim-once: first namespace to arrive owns the slot
+        kk = atoms_cas_u32(C.key_base + s[k] * 4u, kHashEmpty, ns[k]);
+        if (kk == kHashEmpty) kk = ns[k];
+      }
+      slot[k] = (ns[k] < C.NS && kk == ns[k]) ? s[k] : kHashEmpty;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < PODS; ++k) slot[k] = ns[k] < C.NS ? ns[k] : kHashEmpty;
+  }
   // phase 1: every low-word atomic of the group is in flight before any result is consumed
 #pragma unroll
   for (int k = 0; k < PODS; ++k) {

@@ -46,7 +46,10 @@ def main():
     cases = [  # (NS, R, dist, s, grouped)
         (10_000, 3, 1, 1.1, 0), (10_000, 3, 0, 0, 0), (10_000, 3, 1, 1.1, 1), (10_000, 2, 0, 0, 0),
         (100, 3, 1, 1.1, 0), (1_000_000, 3, 1, 1.1, 0), (1_000_000, 3, 0, 0, 0), (10_000, 3, 1, 1.5, 0),
+        (125_000, 3, 1, 1.1, 0), (500_000, 3, 1, 1.1, 0), (20_000, 3, 1, 1.1, 0), (10_000, 4, 1, 1.1, 0), (10_000, 1, 1, 1.1, 0),
     ]
+    if args.cases != "all":
+        cases = [c for c in cases if str(c[0]) in args.cases.split(",")]
     for NS, R, dist, s, grouped in cases:
         a, b = Q.scramble_params(NS)
         cdf = Q.zipf_cdf(NS, s) if dist else None
