@@ -46,7 +46,7 @@ EXPORTS = [
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
     "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
     "bgc_nsmap_intern", "bgc_nsmap_lookup", "bgc_nsmap_size", "bgc_nsmap_name", "bgc_flatten_pods",
-    "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev",
+    "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev", "bgc_admit_greedy", "bgc_admit_greedy_dev",
 ]
 
 
@@ -83,6 +83,8 @@ lib.bgc_usage_get.argtypes = [_P, _P]
 lib.bgc_usage_set.argtypes = [_P, _P]
 lib.bgc_quota_eval.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_quota_eval_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_admit_greedy.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_admit_greedy_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_synth_pods_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64, _Z, _P, _P, _P]
 lib.bgc_synth_policy_dev.argtypes = [_P, C.c_uint64, C.c_uint64, _Z, _P, _P]
 lib.bgc_checksum_u8_dev.argtypes = [_P, _P, C.c_uint64, _Z, C.POINTER(C.c_uint64)]
@@ -240,6 +242,26 @@ class Engine:
         ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
         self._ck(lib.bgc_quota_eval_dev(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask),
                                         d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
+
+    # -- K3 (row N1): sequential admission inside the batch; updates the usage table
+    def admit_greedy(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None) -> np.ndarray:
+        n = ns_id.shape[0]
+        _check_np(ns_id, np.uint32, name="ns_id")
+        for r, c in enumerate(req):
+            _check_np(c, np.int64, n, f"req[{r}]")
+        if req_mask is not None:
+            _check_np(req_mask, np.uint8, n, "req_mask")
+        if len(req) != self.R:
+            raise ValueError(f"expected {self.R} request columns")
+        ptrs = (C.c_void_p * len(req))(*[c.ctypes.data for c in req])
+        verdict = np.empty(n, np.uint8)
+        self._ck(lib.bgc_admit_greedy(self._h, _np_ptr(ns_id), ptrs, _np_ptr(req_mask), n, _np_ptr(verdict)))
+        return verdict
+
+    def admit_greedy_dev(self, d_ns_id, d_req: list, d_req_mask, d_verdict, n: int | None = None):
+        ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
+        self._ck(lib.bgc_admit_greedy_dev(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask),
+                                          d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
 
     # -- raw-pointer variants (host pinned buffers, slices of larger allocations)
     def usage_reduce_ptr(self, ns_ptr: int, req_ptrs: list, n: int, flags: int = 0, used_out_ptr: int = 0):

@@ -13,6 +13,8 @@
 
 #include "../../include/bgc.h"
 #include "../../include/bgc_synth.h"
+#include <cub/device/device_radix_sort.cuh>
+
 #include "bgc_kernels.cuh"
 
 using namespace bgc;
@@ -65,6 +67,13 @@ struct bgc_ctx {
   std::vector<cudaEvent_t> ev_pool;
   size_t ev_next = 0;
   unsigned long long* d_scratch = nullptr;  // 256 x u64
+  // greedy admission (row N1): grouping buffers, grown on demand
+  uint32_t *g_keys = nullptr, *g_keys_sorted = nullptr, *g_idx = nullptr, *g_order = nullptr, *g_seg = nullptr;
+  void* g_temp = nullptr;
+  long long* g_req[kMaxR] = {nullptr, nullptr, nullptr, nullptr};  // request columns in grouped order
+  uint8_t* g_mask = nullptr;
+  int g_R = 0;
+  size_t g_cap = 0, g_temp_bytes = 0, g_seg_cap = 0;
   // latency path: small host batches are read by the kernel straight over PCIe (zero-copy) from
   // the caller's pinned buffers, or from this pinned, device-mapped staging area
   uint8_t* zc_host = nullptr;
@@ -458,6 +467,9 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   cudaFree(ctx->d_hard_mask);
   cudaFree(ctx->d_table_tmp);
   cudaFree(ctx->d_scratch);
+  cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order);
+  cudaFree(ctx->g_seg); cudaFree(ctx->g_temp); cudaFree(ctx->g_mask);
+  for (auto q : ctx->g_req) cudaFree(q);
   cudaFreeHost(ctx->zc_host);
   cudaStreamDestroy(ctx->own_stream);
   cudaStreamDestroy(ctx->h2d_stream);
@@ -813,6 +825,181 @@ int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* re
   return finish_timings(ctx, sp);
 }
 
+}  // extern "C"
+
+// ---------------------------------------------------------------- K3 (row N1): greedy in-batch admission
+namespace {
+
+template <int R>
+int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const long long* const* req_in, const uint8_t* mask_in, size_t n,
+                uint8_t* verdict) {
+  // permute the request columns into grouped order once, in parallel
+  ReqCols<R> src, cols;
+  ReqColsOut<R> dst;
+  for (int r = 0; r < R; ++r) {
+    src.p[r] = req_in[r];
+    dst.p[r] = ctx->g_req[r];
+    cols.p[r] = ctx->g_req[r];
+  }
+  const int gg = grid_for(n, 256, ctx->sm_count * 16);
+  if (mask_in) k_greedy_gather<R, true><<<gg, 256, 0, st>>>(ctx->g_order, src, mask_in, n, dst, ctx->g_mask);
+  else k_greedy_gather<R, false><<<gg, 256, 0, st>>>(ctx->g_order, src, mask_in, n, dst, ctx->g_mask);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  const uint8_t* mask = mask_in ? ctx->g_mask : nullptr;
+  int grid = ctx->sm_count * 8;
+  const int warps_per_block = 256 / 32;
+  if ((size_t)grid * warps_per_block > ctx->NS) grid = (int)((ctx->NS + warps_per_block - 1) / warps_per_block);
+  // short segments: one warp per namespace; long ones (Zipf heads): one 1024-thread CTA per namespace
+  int team_grid = ctx->sm_count;
+  if ((uint32_t)team_grid > ctx->NS) team_grid = (int)ctx->NS;
+  const size_t ring = (size_t)kGreedyDepth * R * kGreedyTeam * 8;
+  if (mask) {
+    CU(cudaFuncSetAttribute(k3_admit_greedy_team<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
+    k3_admit_greedy<R, true><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows, ctx->d_hard_mask,
+                                                   ctx->NS, ctx->compute_mask, verdict, kGreedyTeamMin);
+    k3_admit_greedy_team<R, true><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows,
+                                                                       ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+  } else {
+    CU(cudaFuncSetAttribute(k3_admit_greedy_team<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
+    k3_admit_greedy<R, false><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows, ctx->d_hard_mask,
+                                                    ctx->NS, ctx->compute_mask, verdict, kGreedyTeamMin);
+    k3_admit_greedy_team<R, false><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows,
+                                                                        ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+  }
+  ctx->tm.launches += 2;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+int ensure_greedy_buffers(bgc_ctx* ctx, size_t n, int end_bit) {
+  if (n > ctx->g_cap || ctx->R > ctx->g_R) {
+    CU(cudaDeviceSynchronize());
+    cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order); cudaFree(ctx->g_mask);
+    for (auto& q : ctx->g_req) { cudaFree(q); q = nullptr; }
+    ctx->g_keys = ctx->g_keys_sorted = ctx->g_idx = ctx->g_order = nullptr;
+    ctx->g_mask = nullptr;
+    if (n < ctx->g_cap) n = ctx->g_cap;
+    ctx->g_cap = 0;
+    ctx->g_R = 0;
+    CU(cudaMalloc(&ctx->g_keys, n * 4));
+    CU(cudaMalloc(&ctx->g_keys_sorted, n * 4));
+    CU(cudaMalloc(&ctx->g_idx, n * 4));
+    CU(cudaMalloc(&ctx->g_order, n * 4));
+    CU(cudaMalloc(&ctx->g_mask, n));
+    for (int r = 0; r < ctx->R; ++r) CU(cudaMalloc(&ctx->g_req[r], n * 8));
+    ctx->g_cap = n;
+    ctx->g_R = ctx->R;
+  }
+  if ((size_t)ctx->NS + 2 > ctx->g_seg_cap) {
+    CU(cudaDeviceSynchronize());
+    cudaFree(ctx->g_seg); ctx->g_seg = nullptr; ctx->g_seg_cap = 0;
+    CU(cudaMalloc(&ctx->g_seg, ((size_t)ctx->NS + 2) * 4));
+    ctx->g_seg_cap = (size_t)ctx->NS + 2;
+  }
+  size_t need = 0;
+  CU(cub::DeviceRadixSort::SortPairs(nullptr, need, ctx->g_keys, ctx->g_keys_sorted, ctx->g_idx, ctx->g_order,
+                                     (long long)n, 0, end_bit));
+  if (need > ctx->g_temp_bytes) {
+    CU(cudaDeviceSynchronize());
+    cudaFree(ctx->g_temp); ctx->g_temp = nullptr; ctx->g_temp_bytes = 0;
+    CU(cudaMalloc(&ctx->g_temp, need));
+    ctx->g_temp_bytes = need;
+  }
+  return BGC_OK;
+}
+
+}  // namespace
+
+extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
+                                    const uint8_t* d_req_mask, size_t n, uint8_t* d_verdict) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(n == 0 || (d_ns_id && d_req && d_verdict), "null column pointer");
+  NEED(n < (size_t(1) << 31), "greedy admission handles fewer than 2^31 pods per call");
+  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  for (int r = 0; r < ctx->R && n; ++r) {
+    NEED(d_req[r], "null request column");
+    cols[r] = reinterpret_cast<const long long*>(d_req[r]);
+  }
+  if (n == 0) return BGC_OK;
+  CU(cudaSetDevice(ctx->device));
+  int end_bit = 1;
+  while ((1ull << end_bit) <= (unsigned long long)ctx->NS) ++end_bit;  // keys are 0..NS
+  int rc = ensure_greedy_buffers(ctx, n, end_bit);
+  if (rc) return rc;
+  cudaStream_t st = ctx->stream;
+  const int g1 = grid_for(n, 256, ctx->sm_count * 8);
+  k_greedy_keys<<<g1, 256, 0, st>>>(d_ns_id, n, ctx->NS, ctx->g_keys, ctx->g_idx);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  size_t tb = ctx->g_temp_bytes;
+  CU(cub::DeviceRadixSort::SortPairs(ctx->g_temp, tb, ctx->g_keys, ctx->g_keys_sorted, ctx->g_idx, ctx->g_order,
+                                     (long long)n, 0, end_bit, st));  // stable: arrival order kept inside a namespace
+  const int g2 = grid_for((size_t)ctx->NS + 2, 256, ctx->sm_count * 4);
+  k_greedy_segments<<<g2, 256, 0, st>>>(ctx->g_keys_sorted, n, ctx->NS, ctx->g_seg);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  k_greedy_bad_ns<<<ctx->sm_count, 256, 0, st>>>(ctx->g_order, ctx->g_seg, ctx->NS, d_verdict);
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  ctx->head_stale = true;
+  switch (ctx->R) {
+    case 1: return launch_k3_r<1>(ctx, st, cols, d_req_mask, n, d_verdict);
+    case 2: return launch_k3_r<2>(ctx, st, cols, d_req_mask, n, d_verdict);
+    case 3: return launch_k3_r<3>(ctx, st, cols, d_req_mask, n, d_verdict);
+    default: return launch_k3_r<4>(ctx, st, cols, d_req_mask, n, d_verdict);
+  }
+}
+
+extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
+                                const uint8_t* req_mask, size_t n, uint8_t* verdict) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(n == 0 || (ns_id && req && verdict), "null column pointer");
+  const int R = ctx->R;
+  for (int r = 0; r < R && n; ++r) NEED(req[r], "null request column");
+  if (n == 0) return BGC_OK;
+  CU(cudaSetDevice(ctx->device));
+  if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
+  // the whole batch must be resident for the grouping pass: one-shot buffers, released on return
+  uint32_t* d_ns = nullptr;
+  long long* d_req[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  uint8_t *d_mask = nullptr, *d_v = nullptr;
+  auto cleanup = [&] {
+    cudaFree(d_ns); cudaFree(d_mask); cudaFree(d_v);
+    for (auto p : d_req) cudaFree(p);
+  };
+  cudaStream_t keep = ctx->stream;
+  ctx->stream = ctx->own_stream;
+  int rc = BGC_OK;
+  cudaError_t e = cudaMalloc(&d_ns, n * 4);
+  for (int r = 0; r < R && e == cudaSuccess; ++r) e = cudaMalloc(&d_req[r], n * 8);
+  if (e == cudaSuccess && req_mask) e = cudaMalloc(&d_mask, n);
+  if (e == cudaSuccess) e = cudaMalloc(&d_v, n);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_ns, ns_id, n * 4, cudaMemcpyHostToDevice, ctx->own_stream);
+  for (int r = 0; r < R && e == cudaSuccess; ++r)
+    e = cudaMemcpyAsync(d_req[r], req[r], n * 8, cudaMemcpyHostToDevice, ctx->own_stream);
+  if (e == cudaSuccess && req_mask) e = cudaMemcpyAsync(d_mask, req_mask, n, cudaMemcpyHostToDevice, ctx->own_stream);
+  if (e != cudaSuccess) {
+    rc = fail(ctx, e == cudaErrorMemoryAllocation ? BGC_E_OOM : BGC_E_CUDA, "greedy staging: %s", cudaGetErrorString(e));
+  } else {
+    const int64_t* cols[kMaxR];
+    for (int r = 0; r < kMaxR; ++r) cols[r] = reinterpret_cast<const int64_t*>(d_req[r]);
+    rc = bgc_admit_greedy_dev(ctx, d_ns, cols, d_mask, n, d_v);
+    if (rc == BGC_OK) {
+      e = cudaMemcpyAsync(verdict, d_v, n, cudaMemcpyDeviceToHost, ctx->own_stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->own_stream);
+      if (e != cudaSuccess) rc = fail(ctx, BGC_E_CUDA, "greedy copy-out: %s", cudaGetErrorString(e));
+    }
+  }
+  cudaStreamSynchronize(ctx->own_stream);
+  ctx->stream = keep;
+  cleanup();
+  return rc;
+}
+
+extern "C" {
 // ---------------------------------------------------------------- synthetic inputs / checksums
 int bgc_synth_pods_dev(bgc_ctx* ctx, const bgc_synth_params* p, uint64_t first, size_t count,
                        uint32_t* d_ns_id, int64_t* const* d_req, uint8_t* d_req_mask) {

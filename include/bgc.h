@@ -153,6 +153,17 @@ int bgc_quota_eval(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *re
 int bgc_quota_eval_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
                        const uint8_t *d_req_mask, size_t n, uint8_t *d_verdict);
 
+/* ---- row N1: K3 admit_greedy — sequential admission inside one batch -----------
+ * No reference function; this is what kube-apiserver does one pod at a time against the
+ * ResourceQuota the reference writes (src/controller.rs:89-110): per namespace, in arrival order, a
+ * pod is admitted iff its verdict (same encoding and rules as bgc_quota_eval) against the CURRENT
+ * usage is 0, and only admitted pods add their requests to the usage table, which is updated in
+ * place.  Order-dependent, so the checker is the literal loop.  n < 2^31. */
+int bgc_admit_greedy(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *req,
+                     const uint8_t *req_mask, size_t n, uint8_t *verdict);
+int bgc_admit_greedy_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
+                         const uint8_t *d_req_mask, size_t n, uint8_t *d_verdict);
+
 /* ---- allocation-free usage reduction ---------------------------------------------------------
  * No counterpart in the reference.  For callers that cannot allocate device memory when they
  * call (all of HBM already handed to their own pool, or a latency-critical handler that must not

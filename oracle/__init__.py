@@ -162,6 +162,17 @@ def quota_eval(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask, th
     return verdict
 
 
+def admit_greedy(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask):
+    """Returns (verdict, used_after); `used` is not modified."""
+    R = len(req)
+    n = ns_id.shape[0]
+    verdict = np.empty(n, np.uint8)
+    u = np.ascontiguousarray(used, dtype=np.int64).copy()
+    lib().quota_ref_admit_greedy(_p(ns_id), _ptrs(req), _p(req_mask), C.c_size_t(n), C.c_uint32(NS), C.c_uint32(R), _p(u),
+                                 _p(np.ascontiguousarray(hard)), _p(hard_mask), C.c_uint8(compute_mask), _p(verdict))
+    return verdict, u
+
+
 def gen_params(seed, set_, NS, dist, grouped, n_total, a, b, cdf, kinds):
     p = GenParams()
     p.seed, p.set, p.ns_count, p.dist, p.grouped, p.n_total = seed, set_, NS, dist, int(grouped), n_total

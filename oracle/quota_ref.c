@@ -84,6 +84,20 @@ void quota_ref_quota_eval(const uint32_t *ns_id, const int64_t *const *req,
                           hard, hard_mask, compute_mask);
 }
 
+void quota_ref_admit_greedy(const uint32_t *ns_id, const int64_t *const *req,
+                            const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
+                            int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
+                            uint8_t compute_mask, uint8_t *verdict) {
+  for (size_t j = 0; j < n; ++j) {
+    const uint32_t ns = ns_id[j];
+    const uint8_t v = eval_one(ns, req, req_mask ? req_mask[j] : 0xFF, j, NS, R, used, hard, hard_mask, compute_mask);
+    verdict[j] = v;
+    if (v == 0) /* admitted: it now holds quota */
+      for (uint32_t r = 0; r < R; ++r)
+        used[(size_t)r * NS + ns] = (int64_t)((uint64_t)used[(size_t)r * NS + ns] + (uint64_t)req[r][j]);
+  }
+}
+
 /* ------------------------------------------------------------------ generator spec */
 static inline uint64_t sm64(uint64_t x) {
   x += 0x9E3779B97F4A7C15ull;

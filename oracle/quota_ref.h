@@ -41,6 +41,15 @@ void quota_ref_quota_eval(const uint32_t *ns_id, const int64_t *const *req,
                           const int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
                           uint8_t compute_mask, uint8_t *verdict, int threads);
 
+/* N1: Kubernetes-faithful sequential admission inside one batch.  Pods are taken
+ * in arrival order; pod j is admitted iff its verdict — computed exactly like quota_ref_quota_eval
+ * but against the CURRENT usage of its namespace — is 0, and only admitted pods add their requests
+ * (all R columns, wrapping i64 like A3) to `used`, which is updated in place.  The literal loop. */
+void quota_ref_admit_greedy(const uint32_t *ns_id, const int64_t *const *req,
+                            const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
+                            int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
+                            uint8_t compute_mask, uint8_t *verdict);
+
 /* ---- synthetic generator spec ---- */
 enum { GEN_KIND_GPU = 0, GEN_KIND_CPU_MILLI = 1, GEN_KIND_MEM_BYTES = 2, GEN_KIND_MIG = 3 };
 enum { GEN_DIST_UNIFORM = 0, GEN_DIST_ZIPF_CDF = 1 };

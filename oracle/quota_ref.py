@@ -48,6 +48,36 @@ def quota_eval(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask) ->
     return out
 
 
+def admit_greedy(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask):
+    """N1, pure-Python statement (small cases only): arrival order, only admitted pods consume."""
+    R = len(req)
+    used = [[int(x) for x in row] for row in used]
+    out = np.zeros(ns_id.shape[0], np.uint8)
+    wrap = lambda x: ((x + (1 << 63)) & _M64) - (1 << 63)
+    for j in range(ns_id.shape[0]):
+        ns = int(ns_id[j])
+        if ns >= NS:
+            out[j] = VERDICT_BAD_NS
+            continue
+        rm = 0xFF if req_mask is None else int(req_mask[j])
+        missing = exceeded = 0
+        for r in range(R):
+            if not (int(hard_mask[ns]) >> r) & 1:
+                continue
+            if not (rm >> r) & 1:
+                if (compute_mask >> r) & 1:
+                    missing |= 1 << r
+                continue
+            q = int(req[r][j])
+            if q > 0 and used[r][ns] + q > int(hard[r][ns]):
+                exceeded |= 1 << r
+        out[j] = (missing << 4) | exceeded
+        if out[j] == 0:
+            for r in range(R):
+                used[r][ns] = wrap(used[r][ns] + int(req[r][j]))
+    return out, np.array(used, dtype=np.int64)
+
+
 # ---- generator spec, numpy restatement (cross-checks gen_ref_* in quota_ref.c) ----
 def _sm64(x: np.ndarray) -> np.ndarray:
     x = (x + np.uint64(0x9E3779B97F4A7C15))

@@ -1,0 +1,112 @@
+"""GPU parity tests for K3 admit_greedy: Kubernetes-faithful sequential
+admission inside a batch.  Order-dependent, so the checker is the oracle's literal loop
+(oracle/quota_ref.c::quota_ref_admit_greedy); bit-exact verdicts and final usage."""
+import numpy as np
+import pytest
+
+from oracle import quota_ref as Q
+from workloads import make_hard, KINDS, UNITS, SEEDS
+
+pytestmark = pytest.mark.gpu
+
+
+def _cm(units):
+    return sum(1 << r for r, u in enumerate(units) if u != 0)
+
+
+@pytest.mark.parametrize("R", [1, 2, 3, 4])
+@pytest.mark.parametrize("with_mask", [False, True])
+@pytest.mark.parametrize("n,NS", [(1, 1), (31, 2), (32, 2), (33, 2), (1000, 7), (50_000, 300), (200_003, 10_000), (160_001, 3), (32768, 1), (32769, 1)])
+def test_greedy_vs_literal_loop(engine, oracle, R, with_mask, n, NS):
+    rng = np.random.default_rng(R * 7 + n)
+    ns = rng.integers(0, NS, n, dtype=np.uint32)
+    req = [rng.integers(0, 1 << 30, n, dtype=np.int64) for _ in range(R)]
+    for r in range(R):
+        req[r][::9] = 0
+        req[r][3::41] = -rng.integers(1, 1000, req[r][3::41].shape[0])     # negative requests reduce usage when admitted
+    if n > 100:
+        ns[5] = NS
+        ns[n // 3] = 0xFFFFFFFF
+    mask = rng.integers(0, 256, n, dtype=np.uint8) | np.uint8(0b0110 if n > 40 else 0) if with_mask else None
+    if with_mask and n > 40:
+        mask[::17] &= np.uint8(0xF9)                                        # some pods omit cpu / memory
+    used0 = oracle.usage_reduce(ns[: n // 4 + 1], [c[: n // 4 + 1] for c in req], NS)
+    hard, hm = make_hard(used0 * 4 + 1000, 3)
+    hm[::6] = rng.integers(0, 1 << R, hm[::6].shape[0], dtype=np.uint8)
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(used0)
+    want_v, want_u = oracle.admit_greedy(ns, req, mask, NS, used0, hard, hm, _cm(UNITS[R]))
+    got_v = engine.admit_greedy(ns, req, mask)
+    assert np.array_equal(got_v, want_v)
+    assert np.array_equal(engine.usage_get(), want_u)
+    if n <= 1000:  # the pure-Python statement agrees too
+        pv, pu = Q.admit_greedy(ns, req, mask, NS, used0, hard, hm, _cm(UNITS[R]))
+        assert np.array_equal(pv, want_v) and np.array_equal(pu, want_u)
+
+
+def test_greedy_differs_from_snapshot_and_is_order_dependent(engine, oracle):
+    """Two pods that each fit alone but not together: snapshot semantics (K2) admits both,
+    sequential semantics admits the first only; swapping them changes who wins."""
+    hard = np.array([[10]], np.int64)
+    engine.quota_table_set(hard, np.array([1], np.uint8), [0])
+    ns = np.zeros(2, np.uint32)
+    req = [np.array([6, 5], np.int64)]
+    assert engine.quota_eval(ns, req).tolist() == [0, 0]
+    assert engine.admit_greedy(ns, req).tolist() == [0, 1]
+    assert engine.usage_get().tolist() == [[6]]
+    engine.usage_set(np.zeros((1, 1), np.int64))
+    assert engine.admit_greedy(ns, [np.array([5, 6], np.int64)]).tolist() == [0, 1]
+    assert engine.usage_get().tolist() == [[5]]
+    # a later, smaller pod still gets in after a rejection
+    engine.usage_set(np.zeros((1, 1), np.int64))
+    assert engine.admit_greedy(np.zeros(4, np.uint32), [np.array([6, 5, 4, 1], np.int64)]).tolist() == [0, 1, 0, 1]
+
+
+@pytest.mark.parametrize("dist", [0, 1])
+def test_greedy_generated_workload_device_pointers(bgc, engine, oracle, dist):
+    import torch
+    R, NS, n = 3, 10_000, 2_000_003
+    a, b = Q.scramble_params(NS)
+    cdf = Q.zipf_cdf(NS, 1.1)
+    run = oracle.gen_fill(oracle.gen_params(SEEDS["C3"], 0, NS, dist, 0, n, a, b, cdf if dist else None, KINDS[R]), 0, n, threads=8)
+    cand = oracle.gen_fill(oracle.gen_params(SEEDS["C3"], 1, NS, dist, 0, n, a, b, cdf if dist else None, KINDS[R]), 0, n, want_mask=True, threads=8)
+    used0 = oracle.usage_reduce(run[0], run[1], NS, threads=8)
+    hard, hm = make_hard(used0, SEEDS["C3"])
+    hard = hard + (hard // 8)               # leave some room so that admissions and rejections interleave
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(used0)
+    want_v, want_u = oracle.admit_greedy(cand[0], cand[1], cand[2], NS, used0, hard, hm, 6)
+    d_ns = torch.from_numpy(cand[0].view(np.int32)).cuda()
+    d_req = [torch.from_numpy(c).cuda() for c in cand[1]]
+    d_mask = torch.from_numpy(cand[2]).cuda()
+    d_v = torch.empty(n, dtype=torch.uint8, device="cuda")
+    engine.use_torch_stream()
+    engine.admit_greedy_dev(d_ns, d_req, d_mask, d_v)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_v.cpu().numpy(), want_v)
+    assert np.array_equal(engine.usage_get(), want_u)
+    adm = np.mean(want_v == 0)
+    assert 0.02 < adm < 0.98, adm
+    # K2 right after sees the updated usage (headroom table is rebuilt)
+    v2 = engine.quota_eval(cand[0][:1000], [c[:1000] for c in cand[1]], cand[2][:1000])
+    assert np.array_equal(v2, oracle.quota_eval(cand[0][:1000], [c[:1000] for c in cand[1]], cand[2][:1000], NS, want_u, hard, hm, 6))
+
+
+@pytest.mark.parametrize("R", [1, 3, 4])
+@pytest.mark.parametrize("n,NS", [(300_000, 2), (70_000, 1), (100_000, 40)])
+def test_greedy_monotone_fast_path_long_segments(engine, oracle, R, n, NS):
+    """Non-negative requests only: every tile takes the strike-out fast path, in the warp kernel
+    (short segments) and in the CTA-wide kernel (segments >= 32768 pods)."""
+    rng = np.random.default_rng(R + n)
+    ns = rng.integers(0, NS, n, dtype=np.uint32)
+    req = [rng.choice(np.array([0, 1, 2, 4, 8, 250, 1000, 1 << 20, 1 << 32], np.int64), n) for _ in range(R)]
+    mask = rng.integers(0, 256, n, dtype=np.uint8) | np.uint8(0b0110)
+    mask[::29] &= np.uint8(0xFD)
+    used0 = oracle.usage_reduce(ns[: n // 8], [c[: n // 8] for c in req], NS)
+    hard, hm = make_hard(used0 * 3, 11)
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(used0)
+    want_v, want_u = oracle.admit_greedy(ns, req, mask, NS, used0, hard, hm, _cm(UNITS[R]))
+    assert np.array_equal(engine.admit_greedy(ns, req, mask), want_v)
+    assert np.array_equal(engine.usage_get(), want_u)
+    assert 0.01 < np.mean(want_v == 0) < 0.99

@@ -185,3 +185,25 @@ def test_checksum_is_additive_and_position_keyed(oracle):
     w = v.copy(); w[[1, 2]] = w[[2, 1]]
     if v[1] != v[2]:
         assert oracle.checksum_u8(w, 100) != whole
+
+
+@pytest.mark.parametrize("R", [1, 2, 3, 4])
+def test_greedy_oracle_c_vs_python(oracle, R):
+    rng = np.random.default_rng(50 + R)
+    n, NS = 4000, 30
+    ns = rng.integers(0, NS + 2, n, dtype=np.uint32)
+    req = [rng.integers(-3, 1 << 20, n, dtype=np.int64) for _ in range(R)]
+    mask = rng.integers(0, 256, n, dtype=np.uint8)
+    used0 = oracle.usage_reduce(ns[:500], [c[:500] for c in req], NS)
+    hard, hm = make_hard(used0 * 3, R)
+    cm = 6 & ((1 << R) - 1)
+    a = oracle.admit_greedy(ns, req, mask, NS, used0, hard, hm, cm)
+    b = Q.admit_greedy(ns, req, mask, NS, used0, hard, hm, cm)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    # with unlimited quota the greedy pass admits everything and ends at used0 + usage of the batch
+    big = np.full_like(hard, 2**62)
+    v, u = oracle.admit_greedy(ns, req, None, NS, used0, big, hm, cm)
+    ok = ns < NS
+    assert (v[ok] == 0).all() and (v[~ok] == 0xFF).all()
+    with np.errstate(over="ignore"):
+        assert np.array_equal(u, used0 + oracle.usage_reduce(ns, req, NS))
