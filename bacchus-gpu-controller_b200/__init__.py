@@ -47,6 +47,8 @@ EXPORTS = [
     "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
     "bgc_nsmap_intern", "bgc_nsmap_lookup", "bgc_nsmap_size", "bgc_nsmap_name", "bgc_flatten_pods",
     "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev", "bgc_admit_greedy", "bgc_admit_greedy_dev",
+    "bgc_sheet_infer_header", "bgc_sheet_parse_csv", "bgc_sheet_destroy", "bgc_sheet_row_count", "bgc_sheet_skipped_rows",
+    "bgc_sheet_get_row", "bgc_sheet_match", "bgc_sheet_row_quota",
 ]
 
 
@@ -309,4 +311,4 @@ def version() -> str:
     return lib.bgc_version().decode()
 
 
-from . import admission, pods, shard  # noqa: E402,F401
+from . import admission, pods, shard, sheet  # noqa: E402,F401

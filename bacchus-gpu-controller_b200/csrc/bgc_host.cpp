@@ -68,6 +68,105 @@ void json_escape(std::string& out, std::string_view s) {
 
 }  // namespace
 
+// ------------------------------------------------------------------------------ row N2 helpers
+struct SheetRowOwned {
+  std::string name, department, id_username, gpu_server, authorized;
+  int64_t gpu_request = 0, cpu_request = 0, memory_request = 0, storage_request = 0, mig_request = 0;
+};
+
+struct bgc_sheet {
+  std::vector<SheetRowOwned> rows;
+  size_t skipped = 0;
+};
+
+namespace {
+
+// CSV records as the rust `csv` crate reads them with default settings (what the reference uses,
+// src/synchronizer.rs:146): ',' delimiter, '"' quoting with "" as an escaped quote, \n / \r\n / \r
+// record terminators, no trimming, empty lines skipped.  (csv 1.2 behaviour restated from its
+// documentation — unpinned; a leading UTF-8 BOM is dropped.)
+std::vector<std::vector<std::string>> csv_records(std::string_view text) {
+  std::vector<std::vector<std::string>> out;
+  if (text.size() >= 3 && (unsigned char)text[0] == 0xEF && (unsigned char)text[1] == 0xBB && (unsigned char)text[2] == 0xBF)
+    text.remove_prefix(3);
+  std::vector<std::string> rec;
+  std::string field;
+  bool in_quotes = false, field_started = false, any = false;
+  auto end_field = [&] { rec.push_back(field); field.clear(); field_started = false; };
+  auto end_record = [&] {
+    if (any || !rec.empty() || field_started) { end_field(); out.push_back(rec); }
+    rec.clear(); any = false;
+  };
+  for (size_t i = 0; i < text.size(); ++i) {
+    const char c = text[i];
+    if (in_quotes) {
+      if (c == '"') {
+        if (i + 1 < text.size() && text[i + 1] == '"') { field.push_back('"'); ++i; }
+        else in_quotes = false;
+      } else field.push_back(c);
+      continue;
+    }
+    if (c == '"' && !field_started) { in_quotes = true; field_started = true; any = true; }
+    else if (c == ',') { end_field(); any = true; }
+    else if (c == '\n' || c == '\r') {
+      if (c == '\r' && i + 1 < text.size() && text[i + 1] == '\n') ++i;
+      end_record();
+    } else { field.push_back(c); field_started = true; any = true; }
+  }
+  end_record();
+  return out;
+}
+
+// i64 from a CSV field the way serde's integer visitor over csv does: str::parse::<i64>()
+bool parse_i64_strict(const std::string& s, int64_t* out) {
+  if (s.empty()) return false;
+  size_t i = 0;
+  bool neg = false;
+  if (s[0] == '+' || s[0] == '-') { neg = s[0] == '-'; i = 1; }
+  if (i == s.size()) return false;
+  unsigned long long v = 0;
+  const unsigned long long lim = neg ? 9223372036854775808ull : 9223372036854775807ull;
+  for (; i < s.size(); ++i) {
+    if (s[i] < '0' || s[i] > '9') return false;
+    const unsigned d = (unsigned)(s[i] - '0');
+    if (v > (lim - d) / 10) return false;
+    v = v * 10 + d;
+  }
+  *out = neg ? (int64_t)(0 - v) : (int64_t)v;
+  return true;
+}
+
+bool contains(std::string_view hay, std::string_view needle) { return hay.find(needle) != std::string_view::npos; }
+
+// str::trim(): Unicode White_Space at both ends
+std::string_view trim_unicode(std::string_view s) {
+  auto ws_len_front = [](std::string_view t) -> size_t {
+    if (t.empty()) return 0;
+    const unsigned char c = (unsigned char)t[0];
+    if (c == ' ' || (c >= 0x09 && c <= 0x0D)) return 1;
+    if (t.size() >= 2 && c == 0xC2 && ((unsigned char)t[1] == 0x85 || (unsigned char)t[1] == 0xA0)) return 2;
+    if (t.size() >= 3) {
+      const unsigned char d = (unsigned char)t[1], e = (unsigned char)t[2];
+      if (c == 0xE1 && d == 0x9A && e == 0x80) return 3;                                  // U+1680
+      if (c == 0xE2 && d == 0x80 && ((e >= 0x80 && e <= 0x8A) || e == 0xA8 || e == 0xA9 || e == 0xAF)) return 3;
+      if (c == 0xE2 && d == 0x81 && e == 0x9F) return 3;                                  // U+205F
+      if (c == 0xE3 && d == 0x80 && e == 0x80) return 3;                                  // U+3000
+    }
+    return 0;
+  };
+  for (size_t k; (k = ws_len_front(s)) != 0;) s.remove_prefix(k);
+  for (bool again = true; again && !s.empty();) {
+    again = false;
+    for (size_t k = 1; k <= 3 && k <= s.size(); ++k) {
+      const std::string_view tail = s.substr(s.size() - k);
+      if (ws_len_front(tail) == k) { s.remove_suffix(k); again = true; break; }
+    }
+  }
+  return s;
+}
+
+}  // namespace
+
 struct bgc_nsmap {
   std::unordered_map<std::string, uint32_t> ids;
   std::vector<std::string> names;
@@ -359,6 +458,134 @@ int bgc_flatten_pods(const bgc_pod_spec* pods, size_t n, const char* const* quot
     ++w;
   }
   *n_out = w;
+  return BGC_OK;
+}
+
+// ------------------------------------------------------------------------------ row N2
+const char* bgc_sheet_infer_header(const char* header) {
+  if (!header) return nullptr;
+  const std::string_view h(header);
+  // first match wins, in the reference's order (src/synchronizer.rs:99-137)
+  if (h == "타임스탬프") return "timestamp";
+  if (h == "이름") return "name";
+  if (h == "소속") return "department";
+  if (contains(h, "SNUCSE ID")) return "id_username";
+  if (contains(h, "사용할 서버")) return "gpu_server";
+  if (contains(h, "GPU 개수")) return "gpu_request";
+  if (contains(h, "vCPU 개수")) return "cpu_request";
+  if (contains(h, "메모리")) return "memory_request";
+  if (contains(h, "스토리지")) return "storage_request";
+  if (contains(h, "MiG 개수")) return "mig_request";
+  if (contains(h, "요청 사유")) return "description";
+  if (contains(h, "승인")) return "authorized";
+  if (contains(h, "이메일")) return "email";
+  return nullptr;
+}
+
+bgc_sheet* bgc_sheet_parse_csv(const char* content, size_t len, char* err, size_t err_len) {
+  if (err && err_len) err[0] = 0;
+  if (!content) return nullptr;
+  auto recs = csv_records(std::string_view(content, len));
+  auto sheet = new (std::nothrow) bgc_sheet;
+  if (!sheet) return nullptr;
+  if (recs.empty()) return sheet;
+  // header row → canonical names (src/synchronizer.rs:149-154)
+  std::vector<std::string> names;
+  for (const auto& h : recs[0]) {
+    const char* n = bgc_sheet_infer_header(h.c_str());
+    if (!n) {
+      if (err && err_len) snprintf(err, err_len, "unknown header: \"%s\"", h.c_str());  // :139-142
+      delete sheet;
+      return nullptr;
+    }
+    names.emplace_back(n);
+  }
+  auto col = [&](const char* want) -> long {
+    long found = -1;
+    for (size_t i = 0; i < names.size(); ++i)
+      if (names[i] == want) { if (found >= 0) return -2; found = (long)i; }  // duplicate field → serde error per row
+    return found;
+  };
+  const long c_name = col("name"), c_dep = col("department"), c_id = col("id_username"), c_srv = col("gpu_server"),
+             c_gpu = col("gpu_request"), c_cpu = col("cpu_request"), c_mem = col("memory_request"),
+             c_sto = col("storage_request"), c_mig = col("mig_request"), c_auth = col("authorized");
+  const long need[] = {c_name, c_dep, c_id, c_srv, c_gpu, c_cpu, c_mem, c_sto, c_mig, c_auth};
+  bool schema_ok = true;
+  for (long c : need) schema_ok = schema_ok && c >= 0;
+  for (size_t r = 1; r < recs.size(); ++r) {
+    const auto& f = recs[r];
+    SheetRowOwned row;
+    // the csv reader is not flexible: a record whose length differs from the header is an error
+    bool ok = schema_ok && f.size() == names.size();
+    ok = ok && parse_i64_strict(f[c_gpu], &row.gpu_request) && parse_i64_strict(f[c_cpu], &row.cpu_request) &&
+         parse_i64_strict(f[c_mem], &row.memory_request) && parse_i64_strict(f[c_sto], &row.storage_request) &&
+         parse_i64_strict(f[c_mig], &row.mig_request);
+    if (!ok) { ++sheet->skipped; continue; }  // "row parsing error. skipping" :160-163
+    row.name = f[c_name]; row.department = f[c_dep]; row.id_username = f[c_id];
+    row.gpu_server = f[c_srv]; row.authorized = f[c_auth];
+    sheet->rows.push_back(std::move(row));
+  }
+  return sheet;
+}
+
+void bgc_sheet_destroy(bgc_sheet* s) { delete s; }
+size_t bgc_sheet_row_count(const bgc_sheet* s) { return s ? s->rows.size() : 0; }
+size_t bgc_sheet_skipped_rows(const bgc_sheet* s) { return s ? s->skipped : 0; }
+
+int bgc_sheet_get_row(const bgc_sheet* s, size_t i, bgc_sheet_row* out) {
+  if (!s || !out || i >= s->rows.size()) return BGC_E_BADARG;
+  const SheetRowOwned& r = s->rows[i];
+  out->name = r.name.c_str(); out->department = r.department.c_str(); out->id_username = r.id_username.c_str();
+  out->gpu_server = r.gpu_server.c_str(); out->authorized = r.authorized.c_str();
+  out->gpu_request = r.gpu_request; out->cpu_request = r.cpu_request; out->memory_request = r.memory_request;
+  out->storage_request = r.storage_request; out->mig_request = r.mig_request;
+  return BGC_OK;
+}
+
+int bgc_sheet_match(const bgc_sheet* s, const char* server_name, const char* const* names, size_t n, long* row_index) {
+  if (!s || !server_name || (n && (!names || !row_index))) return BGC_E_BADARG;
+  // rows of this server, in sheet order (src/synchronizer.rs:208-213); "o" test at :227-231
+  std::vector<size_t> mine;
+  std::vector<char> authorised;
+  for (size_t i = 0; i < s->rows.size(); ++i) {
+    if (!contains(s->rows[i].gpu_server, server_name)) continue;
+    mine.push_back(i);
+    const std::string_view a = trim_unicode(s->rows[i].authorized);
+    // to_lowercase() == "o": the only strings that lower-case to "o" are "o" and "O"
+    authorised.push_back(a == "o" || a == "O");
+  }
+  for (size_t k = 0; k < n; ++k) {
+    row_index[k] = -1;
+    for (size_t j = mine.size(); j-- > 0;) {  // rows.iter().rev().find(..) :225
+      if (authorised[j] && s->rows[mine[j]].id_username == names[k]) { row_index[k] = (long)mine[j]; break; }
+    }
+  }
+  return BGC_OK;
+}
+
+int bgc_sheet_row_quota(const bgc_sheet_row* row, const char** keys, const char** quantities, int64_t* canonical,
+                        char* scratch, size_t scratch_len) {
+  if (!row || !keys || !quantities || !canonical || !scratch || scratch_len < 512) return BGC_E_BADARG;
+  // BTreeMap iteration order = byte order of the keys (src/synchronizer.rs:250)
+  struct Item { const char* key; int64_t v; bool gi; int64_t canon; };
+  const Item items[BGC_SHEET_KEYS] = {
+      {"limits.cpu", row->cpu_request, false, (int64_t)((uint64_t)row->cpu_request * 1000u)},             // :259-261
+      {"limits.memory", row->memory_request, true, (int64_t)((uint64_t)row->memory_request << 30)},       // :263-265
+      {"requests.cpu", row->cpu_request, false, (int64_t)((uint64_t)row->cpu_request * 1000u)},           // :251-253
+      {"requests.memory", row->memory_request, true, (int64_t)((uint64_t)row->memory_request << 30)},     // :255-257
+      {"requests.nvidia.com/gpu", row->gpu_request, false, row->gpu_request},                             // :267-269
+      {"requests.nvidia.com/mig-1g.10gb", row->mig_request, false, row->mig_request},                     // :275-277
+      {"requests.storage", row->storage_request, true, (int64_t)((uint64_t)row->storage_request << 30)},  // :271-273
+  };
+  size_t off = 0;
+  for (int k = 0; k < BGC_SHEET_KEYS; ++k) {
+    const int w = snprintf(scratch + off, scratch_len - off, items[k].gi ? "%lldGi" : "%lld", (long long)items[k].v);
+    if (w < 0 || off + (size_t)w + 1 > scratch_len) return BGC_E_BADARG;
+    keys[k] = items[k].key;
+    quantities[k] = scratch + off;
+    canonical[k] = items[k].canon;
+    off += (size_t)w + 1;
+  }
   return BGC_OK;
 }
 

@@ -133,6 +133,45 @@ int bgc_hard_from_sheet_row(int64_t cpu_request, int64_t memory_request_gi, int6
                             const char *const *quota_keys, uint32_t R, int64_t *hard_out,
                             uint8_t *unit_out);
 
+/* ---- row N2: the quota-table producer ------------------------------------------
+ * Batch form of the synchronizer's sheet logic, reference src/synchronizer.rs:63-169,208-281:
+ * the Google-Form CSV export is parsed with the reference's header heuristics, filtered by GPU
+ * server, and for every UserBootstrap name the LAST authorised matching row yields the seven `hard`
+ * quantities.  The result feeds bgc_quota_table_set. */
+typedef struct bgc_sheet bgc_sheet;
+
+typedef struct bgc_sheet_row { /* struct Row, src/synchronizer.rs:63-93 */
+  const char *name, *department, *id_username, *gpu_server, *authorized;
+  int64_t gpu_request, cpu_request, memory_request, storage_request, mig_request;
+} bgc_sheet_row;
+
+/* try_infer_header, src/synchronizer.rs:97-143: canonical field name for one header cell, or NULL
+ * for an unknown header (the reference fails the whole parse with CsvHeaderError). */
+const char *bgc_sheet_infer_header(const char *header);
+
+/* parse_csv, src/synchronizer.rs:145-169: returns NULL and a message in err on a header error;
+ * rows that fail to deserialise (missing column, non-integer request, wrong field count) are
+ * skipped, as the reference does with a warning. */
+bgc_sheet *bgc_sheet_parse_csv(const char *content, size_t len, char *err, size_t err_len);
+void bgc_sheet_destroy(bgc_sheet *s);
+size_t bgc_sheet_row_count(const bgc_sheet *s);
+size_t bgc_sheet_skipped_rows(const bgc_sheet *s);
+int bgc_sheet_get_row(const bgc_sheet *s, size_t i, bgc_sheet_row *out);
+
+/* src/synchronizer.rs:208-236: keep rows whose gpu_server CONTAINS server_name (not exact), then
+ * for each name take the last row with authorized.trim().to_lowercase() == "o" and
+ * id_username == name.  row_index[i] = index into the sheet, or -1 when there is no such row
+ * (the reference `continue`s: quota untouched). */
+int bgc_sheet_match(const bgc_sheet *s, const char *server_name, const char *const *names, size_t n,
+                    long *row_index);
+
+/* The seven (key, quantity string) pairs of src/synchronizer.rs:249-281 for one row, in BTreeMap
+ * (sorted-key) order as serde_json would emit them, and the same values in canonical units.
+ * keys[k], quantities[k] point into buffers owned by `scratch` (>= 512 bytes). */
+#define BGC_SHEET_KEYS 7
+int bgc_sheet_row_quota(const bgc_sheet_row *row, const char **keys, const char **quantities,
+                        int64_t *canonical, char *scratch, size_t scratch_len);
+
 #ifdef __cplusplus
 }
 #endif
