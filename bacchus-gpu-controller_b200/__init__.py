@@ -40,7 +40,7 @@ DIST_UNIFORM, DIST_ZIPF_CDF = 0, 1
 EXPORTS = [
     "bgc_ctx_create", "bgc_ctx_destroy", "bgc_last_error", "bgc_ctx_set_stream", "bgc_ctx_reset_stream", "bgc_ctx_sync",
     "bgc_timings_get", "bgc_policy_eval", "bgc_policy_eval_dev", "bgc_quota_table_set",
-    "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_quota_eval",
+    "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_usage_get_dev", "bgc_usage_set_dev", "bgc_quota_eval",
     "bgc_quota_eval_dev", "bgc_ctx_set_k1_variant", "bgc_last_k1_variant", "bgc_version",
     "bgc_synth_pods_dev", "bgc_synth_policy_dev", "bgc_checksum_u8_dev", "bgc_histogram_u8_dev",
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
@@ -83,6 +83,8 @@ lib.bgc_usage_reduce.argtypes = [_P, _P, _P, _Z, C.c_uint, _P]
 lib.bgc_usage_reduce_dev.argtypes = [_P, _P, _P, _Z, C.c_uint, _P]
 lib.bgc_usage_get.argtypes = [_P, _P]
 lib.bgc_usage_set.argtypes = [_P, _P]
+lib.bgc_usage_get_dev.argtypes = [_P, _P]
+lib.bgc_usage_set_dev.argtypes = [_P, _P]
 lib.bgc_quota_eval.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_quota_eval_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_admit_greedy.argtypes = [_P, _P, _P, _P, _Z, _P]
@@ -204,6 +206,12 @@ class Engine:
         if used.shape != (self.R, self.NS):
             raise ValueError("used must be [R][NS]")
         self._ck(lib.bgc_usage_set(self._h, _np_ptr(used)))
+
+    def usage_get_dev(self, d_used_out):
+        self._ck(lib.bgc_usage_get_dev(self._h, _dev_ptr(d_used_out)))
+
+    def usage_set_dev(self, d_used):
+        self._ck(lib.bgc_usage_set_dev(self._h, _dev_ptr(d_used)))
 
     # -- K1 (row A3)
     def usage_reduce(self, ns_id: np.ndarray, req: list, flags: int = 0, want_used: bool = True):

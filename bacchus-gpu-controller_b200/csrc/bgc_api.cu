@@ -663,6 +663,29 @@ int bgc_usage_set(bgc_ctx* ctx, const int64_t* used) {
   return BGC_OK;
 }
 
+// device-pointer forms, enqueued on the context's stream (row N5: the usage table is what the
+// index-sharded multi-GPU variant all-reduces between K1 and K2)
+int bgc_usage_get_dev(bgc_ctx* ctx, int64_t* d_used_out) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(d_used_out, "null output");
+  CU(cudaSetDevice(ctx->device));
+  return export_used(ctx, ctx->stream, reinterpret_cast<long long*>(d_used_out));
+}
+
+int bgc_usage_set_dev(bgc_ctx* ctx, const int64_t* d_used) {
+  if (!ctx) return BGC_E_BADARG;
+  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  NEED(d_used, "null input");
+  CU(cudaSetDevice(ctx->device));
+  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
+  k_rows_import_used<<<grid, 256, 0, ctx->stream>>>(ctx->rows, reinterpret_cast<const long long*>(d_used), ctx->NS, ctx->R);
+  ctx->head_stale = true;
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
 // ---------------------------------------------------------------- K1
 int bgc_usage_reduce_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req, size_t n,
                          unsigned flags, int64_t* d_used_out) {

@@ -175,6 +175,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--k1", type=int, default=0, help="force a K1 variant (BGC_K1_*)")
     ap.add_argument("--grouped", action="store_true", help="running set grouped by namespace (segmented path)")
+    ap.add_argument("--sharding", default="namespace", choices=["namespace", "index"],
+                    help="multi-GPU: independent namespace-hash shards (no collective, default) or pods sharded by index "
+                         "with one int64 all-reduce of the usage table per step (SURVEY.md §8(e)(b), row N5)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = max(args.warmup, 0)
@@ -208,7 +211,12 @@ def main():
         eng.set_k1_variant(args.k1)
 
     n, NS, R, dist_kind, zs, desc = wl
-    seed = SEED[args.workload] + 7919 * rank          # every rank owns an independent namespace shard
+    by_index = args.sharding == "index" and world > 1
+    # namespace sharding: every rank owns an independent namespace shard (own seed, no exchange);
+    # index sharding: all ranks see the same namespaces, rank r takes pods [r*n, (r+1)*n) of one global stream
+    seed = SEED[args.workload] + (0 if by_index else 7919 * rank)
+    first = rank * n if by_index else 0               # position of this rank's slice in the global stream
+    n_total = world * n if by_index else n
     a, b = Q.scramble_params(NS)
     cdf = Q.zipf_cdf(NS, zs) if dist_kind else None
     d_cdf = torch.from_numpy(cdf.view(np.int64)).cuda() if dist_kind else None
@@ -219,19 +227,30 @@ def main():
     run_ns, run_req = alloc_set()
     cand_ns, cand_req = alloc_set()
     d_verdict = torch.empty(n, dtype=torch.uint8, device=dev)
-    eng.synth_pods_dev(bgc.synth_params(seed, 0, NS, dist_kind, int(args.grouped), n, a, b, d_cdf, KINDS[R]), 0, n, run_ns, run_req)
-    eng.synth_pods_dev(bgc.synth_params(seed, 1, NS, dist_kind, 0, n, a, b, d_cdf, KINDS[R]), 0, n, cand_ns, cand_req)
+    eng.synth_pods_dev(bgc.synth_params(seed, 0, NS, dist_kind, int(args.grouped), n_total, a, b, d_cdf, KINDS[R]), first, n, run_ns, run_req)
+    eng.synth_pods_dev(bgc.synth_params(seed, 1, NS, dist_kind, 0, n_total, a, b, d_cdf, KINDS[R]), first, n, cand_ns, cand_req)
     # quota table: hard drawn from the running set's own usage so that about half the verdicts deny
     eng.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
     flags = bgc.REDUCE_GROUPED if args.grouped else 0
-    eng.usage_reduce_dev(run_ns, run_req, flags)
+    d_used = torch.empty(R * NS, dtype=torch.int64, device=dev)
+
+    def reduce_usage():
+        """K1 over this rank's running pods; with index sharding, plus the one exchange step: an int64
+        all-reduce (NCCL over NVLink/NVSwitch) of the R x NS usage table, written back for K2."""
+        eng.usage_reduce_dev(run_ns, run_req, flags)
+        if by_index:
+            eng.usage_get_dev(d_used)
+            dist.all_reduce(d_used, op=dist.ReduceOp.SUM)
+            eng.usage_set_dev(d_used)
+
+    reduce_usage()
     torch.cuda.synchronize()
     used0 = eng.usage_get()
     hard, hard_mask = make_hard(used0, seed)
     eng.quota_table_set(hard, hard_mask, UNITS[R])
 
     def step():
-        eng.usage_reduce_dev(run_ns, run_req, flags)
+        reduce_usage()
         eng.quota_eval_dev(cand_ns, cand_req, None, d_verdict)
 
     def barrier():
@@ -253,7 +272,7 @@ def main():
     t_all0.record()
     for k in range(args.steps):
         ev[k][0].record()
-        eng.usage_reduce_dev(run_ns, run_req, flags)
+        reduce_usage()
         ev[k][1].record()
         eng.quota_eval_dev(cand_ns, cand_req, None, d_verdict)
         ev[k][2].record()
@@ -277,19 +296,19 @@ def main():
     verified = None
     if rank == 0:
         cnt = min(n, 1 << 20)
-        p1 = oracle.gen_params(seed, 1, NS, dist_kind, 0, n, a, b, cdf, KINDS[R])
-        cns, creq, _ = oracle.gen_fill(p1, n - cnt, cnt, threads=8)
+        p1 = oracle.gen_params(seed, 1, NS, dist_kind, 0, n_total, a, b, cdf, KINDS[R])
+        cns, creq, _ = oracle.gen_fill(p1, first + n - cnt, cnt, threads=8)
         used_now = eng.usage_get()
         v = oracle.quota_eval(cns, creq, None, NS, used_now, hard, hard_mask, 0b110 & ((1 << R) - 1), threads=8)
         verified = bool(np.array_equal(used_now, used0)) and oracle.checksum_u8(v, n - cnt) == eng.checksum_u8_dev(d_verdict[n - cnt:], n - cnt)
-        if n <= (1 << 25):
-            p0 = oracle.gen_params(seed, 0, NS, dist_kind, int(args.grouped), n, a, b, cdf, KINDS[R])
-            rns, rreq, _ = oracle.gen_fill(p0, 0, n, threads=8)
+        if n_total <= (1 << 25):
+            p0 = oracle.gen_params(seed, 0, NS, dist_kind, int(args.grouped), n_total, a, b, cdf, KINDS[R])
+            rns, rreq, _ = oracle.gen_fill(p0, 0, n_total, threads=8)
             verified = verified and bool(np.array_equal(oracle.usage_reduce(rns, rreq, NS, threads=8), used_now))
 
     # ---- end to end through the host-pointer entry points (pinned host buffers)
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and not by_index:
         h_run_ns = torch.empty(n, dtype=torch.int32, pin_memory=True); h_run_ns.copy_(run_ns)
         h_run_req = [torch.empty(n, dtype=torch.int64, pin_memory=True) for _ in range(R)]
         h_cand_ns = torch.empty(n, dtype=torch.int32, pin_memory=True); h_cand_ns.copy_(cand_ns)
@@ -320,8 +339,8 @@ def main():
             dt = t.item()
         if rank == 0 and verified is not None:
             verified = verified and oracle.checksum_u8(v, n - cnt) == oracle.checksum_u8(h_verdict[n - cnt:].numpy(), n - cnt)
-        e2e = {"value": world * n * e2e_steps / dt, "unit": "pods/s", "h2d_bytes_per_step": 2 * n * (4 + 8 * R),
-               "d2h_bytes_per_step": n, "ms_per_step": dt / e2e_steps * 1e3, "host_memory": "pinned",
+        e2e = {"value": world * n * e2e_steps / dt, "unit": "pods/s", "h2d_bytes_per_step": world * 2 * n * (4 + 8 * R),
+               "d2h_bytes_per_step": world * n, "ms_per_step": dt / e2e_steps * 1e3, "host_memory": "pinned",
                "last_quota_eval_call": {"h2d_ms": tm["h2d_ns"] / 1e6, "kernel_ms": tm["kernel_ns"] / 1e6, "d2h_ms": tm["d2h_ns"] / 1e6}}
 
     # ---- CPU baseline beside it (rank 0, bounded sample, all host cores)
@@ -352,7 +371,8 @@ def main():
             "config": {"workload": desc, "pods_per_gpu": n, "namespaces_per_gpu": NS, "resources": R,
                        "step": "K1 usage_reduce(running set) + K2 quota_eval(candidate set)", "running_set": "grouped" if args.grouped else "arrival order",
                        "l2": f"inputs {(k1_bytes + k2_bytes) / 1e6:.0f} MB per step >> 126 MB L2 (no flush needed)" if k1_bytes > 4e8 else "inputs fit in L2: treat GB/s as cache bandwidth",
-                       "k1_variant": eng.last_k1_variant(), "sharding": "namespace-hash shards, independent per rank, no collective"},
+                       "k1_variant": eng.last_k1_variant(), "sharding": ("pods sharded by index, one NCCL int64 all-reduce of the %d-byte usage table per step" % (8 * R * NS)) if by_index
+                       else "namespace-hash shards, independent per rank, no collective"},
             "roofline": {"bound": "hbm", "kernel": "k1_usage_reduce", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak,
                          "traffic": None if args.grouped or args.k1 else ncu_traffic(args.workload, "k1_usage_reduce", n, WORKLOADS[args.workload][0]),

@@ -143,6 +143,10 @@ int bgc_usage_reduce_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *c
                          size_t n, unsigned flags, int64_t *d_used_out);
 int bgc_usage_get(bgc_ctx *ctx, int64_t *used_out /* host [R][NS] */);
 int bgc_usage_set(bgc_ctx *ctx, const int64_t *used /* host [R][NS] */);
+/* device [R][NS] forms on the context's stream — what the index-sharded multi-GPU variant
+ *  all-reduces between usage_reduce and quota_eval */
+int bgc_usage_get_dev(bgc_ctx *ctx, int64_t *d_used_out);
+int bgc_usage_set_dev(bgc_ctx *ctx, const int64_t *d_used);
 
 /* ---- row A4: K2 quota_eval — snapshot verdict per candidate pod ------------------------------
  * No reference function; semantic model = kube-apiserver ResourceQuota

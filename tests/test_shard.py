@@ -85,6 +85,56 @@ def _worker(rank, world, port, q):
     q.put((rank, ok))
 
 
+def _worker_index(rank, world, port, q):
+    """Row N5: pods sharded by index, one int64 all-reduce of the usage table, then local evaluation."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import importlib
+    import torch
+    import torch.distributed as dist
+    import oracle
+    from workloads import make_hard
+    bgc = importlib.import_module("bacchus-gpu-controller_b200")
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(6)
+    n, NS, R = 9_001, 150, 3
+    ns = rng.integers(0, NS, n, dtype=np.uint32)
+    req = [rng.integers(0, 1 << 33, n, dtype=np.int64) for _ in range(R)]
+    cns = rng.integers(0, NS, n, dtype=np.uint32)
+    creq = [rng.integers(0, 1 << 33, n, dtype=np.int64) for _ in range(R)]
+    used_all = oracle.usage_reduce(ns, req, NS)
+    hard, hm = make_hard(used_all, 8)
+    lo, hi = bgc.shard.index_slice(n, world, rank)
+    local = torch.from_numpy(oracle.usage_reduce(ns[lo:hi], [c[lo:hi] for c in req], NS))
+    bgc.shard.allreduce_usage(local)                               # the one exchange step
+    ok = bool(np.array_equal(local.numpy(), used_all))
+    v = oracle.quota_eval(cns[lo:hi], [c[lo:hi] for c in creq], None, NS, local.numpy(), hard, hm, 6)
+    want = oracle.quota_eval(cns, creq, None, NS, used_all, hard, hm, 6)
+    ok = ok and bool(np.array_equal(v, want[lo:hi]))
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, ok))
+
+
+def test_two_rank_gloo_index_sharding_with_one_allreduce():
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_index, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(60)
+    assert res == [(0, True), (1, True)]
+    import importlib
+    S = importlib.import_module("bacchus-gpu-controller_b200").shard
+    assert [S.index_slice(10, 3, r) for r in range(3)] == [(0, 4), (4, 8), (8, 10)]
+    assert S.index_slice(2, 4, 3) == (2, 2)
+
+
 def test_two_rank_gloo_shards_need_no_collective_on_the_data_path():
     import torch.multiprocessing as mp
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
