@@ -103,6 +103,32 @@ class ClockSampler:
         return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def bind_to_gpu_numa_node(device: int):
+    """Pin this rank's host threads to the NUMA node its GPU hangs off, BEFORE any pinned buffer is
+    allocated, so the e2e leg's host buffers are local to the GPU's PCIe root (with 8 ranks sharing
+    one socket's memory the copies otherwise contend).  Best effort; returns the node or None."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(device).pci_bus_id
+        dom = torch.cuda.get_device_properties(device).pci_domain_id
+        dev = torch.cuda.get_device_properties(device).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = []
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus += list(range(int(lo), int(hi or lo) + 1))
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return node
+    except Exception:
+        return None
+    return None
+
+
 def cpu_info():
     model = "unknown"
     try:
@@ -198,6 +224,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
     torch.cuda.set_device(local)
+    numa_node = bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -340,7 +367,7 @@ def main():
         if rank == 0 and verified is not None:
             verified = verified and oracle.checksum_u8(v, n - cnt) == oracle.checksum_u8(h_verdict[n - cnt:].numpy(), n - cnt)
         e2e = {"value": world * n * e2e_steps / dt, "unit": "pods/s", "h2d_bytes_per_step": world * 2 * n * (4 + 8 * R),
-               "d2h_bytes_per_step": world * n, "ms_per_step": dt / e2e_steps * 1e3, "host_memory": "pinned",
+               "d2h_bytes_per_step": world * n, "ms_per_step": dt / e2e_steps * 1e3, "host_memory": "pinned", "numa_node_rank0": numa_node,
                "last_quota_eval_call": {"h2d_ms": tm["h2d_ns"] / 1e6, "kernel_ms": tm["kernel_ns"] / 1e6, "d2h_ms": tm["d2h_ns"] / 1e6}}
 
     # ---- CPU baseline beside it (rank 0, bounded sample, all host cores)
