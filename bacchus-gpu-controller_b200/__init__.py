@@ -49,6 +49,8 @@ EXPORTS = [
     "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev", "bgc_admit_greedy", "bgc_admit_greedy_dev",
     "bgc_sheet_infer_header", "bgc_sheet_parse_csv", "bgc_sheet_destroy", "bgc_sheet_row_count", "bgc_sheet_skipped_rows",
     "bgc_sheet_get_row", "bgc_sheet_match", "bgc_sheet_row_quota",
+    "bgc_review_parse", "bgc_review_destroy", "bgc_review_has_request", "bgc_review_uid", "bgc_review_kind",
+    "bgc_review_request", "bgc_review_pod", "bgc_render_review_response",
 ]
 
 
@@ -319,4 +321,4 @@ def version() -> str:
     return lib.bgc_version().decode()
 
 
-from . import admission, pods, shard, sheet  # noqa: E402,F401
+from . import admission, pods, shard, sheet, review  # noqa: E402,F401

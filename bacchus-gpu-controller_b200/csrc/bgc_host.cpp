@@ -4,7 +4,9 @@
 // 312-386) become the (op, flags) columns K0 consumes.  Row A5: pod specs become the
 // (ns_id, req[r], req_mask) columns K1/K2 consume.  Plain C++17, no CUDA in this file; the only
 // device work is reached through the C ABI (bgc_policy_eval).
+#include <cstdio>
 #include <cstring>
+#include <new>
 #include <string>
 #include <string_view>
 #include <unordered_map>
@@ -611,6 +613,375 @@ int bgc_hard_from_sheet_row(int64_t cpu_request, int64_t memory_request_gi, int6
     }
   }
   return BGC_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------ row N4
+// A small order-preserving JSON DOM: enough for AdmissionReview documents.
+namespace {
+
+struct JVal {
+  enum Kind { Null, Bool, Num, Str, Arr, Obj } kind = Null;
+  bool b = false;
+  std::string s;  // string value, or the raw text of a number
+  std::vector<JVal> arr;
+  std::vector<std::pair<std::string, JVal>> obj;
+  const JVal* get(std::string_view key) const {
+    if (kind != Obj) return nullptr;
+    const JVal* hit = nullptr;
+    for (const auto& kv : obj)
+      if (kv.first == key) hit = &kv.second;  // serde_json keeps the last duplicate
+    return hit;
+  }
+  const JVal* get_obj(std::string_view key) const {
+    const JVal* v = get(key);
+    return v && v->kind == Obj ? v : nullptr;
+  }
+  const char* get_str(std::string_view key) const {
+    const JVal* v = get(key);
+    return v && v->kind == Str ? v->s.c_str() : nullptr;
+  }
+};
+
+struct JParser {
+  const char* p;
+  const char* end;
+  std::string err;
+  int depth = 0;
+  bool fail(const char* m) { if (err.empty()) err = m; return false; }
+  void ws() { while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) ++p; }
+  static void utf8(std::string& out, unsigned cp) {
+    if (cp < 0x80) out.push_back((char)cp);
+    else if (cp < 0x800) { out.push_back((char)(0xC0 | (cp >> 6))); out.push_back((char)(0x80 | (cp & 0x3F))); }
+    else if (cp < 0x10000) { out.push_back((char)(0xE0 | (cp >> 12))); out.push_back((char)(0x80 | ((cp >> 6) & 0x3F))); out.push_back((char)(0x80 | (cp & 0x3F))); }
+    else { out.push_back((char)(0xF0 | (cp >> 18))); out.push_back((char)(0x80 | ((cp >> 12) & 0x3F))); out.push_back((char)(0x80 | ((cp >> 6) & 0x3F))); out.push_back((char)(0x80 | (cp & 0x3F))); }
+  }
+  bool hex4(unsigned* v) {
+    if (end - p < 4) return fail("truncated \\u escape");
+    unsigned x = 0;
+    for (int i = 0; i < 4; ++i) {
+      const char c = p[i];
+      x <<= 4;
+      if (c >= '0' && c <= '9') x |= (unsigned)(c - '0');
+      else if (c >= 'a' && c <= 'f') x |= (unsigned)(c - 'a' + 10);
+      else if (c >= 'A' && c <= 'F') x |= (unsigned)(c - 'A' + 10);
+      else return fail("bad \\u escape");
+    }
+    p += 4;
+    *v = x;
+    return true;
+  }
+  bool str(std::string& out) {
+    if (p >= end || *p != '"') return fail("expected string");
+    ++p;
+    while (p < end && *p != '"') {
+      if ((unsigned char)*p < 0x20) return fail("control character in string");
+      if (*p == '\\') {
+        if (++p >= end) return fail("truncated escape");
+        switch (*p++) {
+          case '"': out.push_back('"'); break;
+          case '\\': out.push_back('\\'); break;
+          case '/': out.push_back('/'); break;
+          case 'b': out.push_back('\b'); break;
+          case 'f': out.push_back('\f'); break;
+          case 'n': out.push_back('\n'); break;
+          case 'r': out.push_back('\r'); break;
+          case 't': out.push_back('\t'); break;
+          case 'u': {
+            unsigned cp;
+            if (!hex4(&cp)) return false;
+            if (cp >= 0xD800 && cp < 0xDC00) {  // surrogate pair
+              unsigned lo;
+              if (end - p < 6 || p[0] != '\\' || p[1] != 'u') return fail("lone surrogate");
+              p += 2;
+              if (!hex4(&lo) || lo < 0xDC00 || lo > 0xDFFF) return fail("bad surrogate pair");
+              cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
+            } else if (cp >= 0xDC00 && cp < 0xE000) return fail("lone surrogate");
+            utf8(out, cp);
+            break;
+          }
+          default: return fail("bad escape");
+        }
+      } else if ((unsigned char)*p < 0x80) {
+        out.push_back(*p++);
+      } else {  // raw multi-byte sequence: must be well-formed UTF-8, as serde_json requires
+        const unsigned char c = (unsigned char)*p;
+        const int len = c >= 0xF0 ? 4 : c >= 0xE0 ? 3 : c >= 0xC2 ? 2 : 0;
+        if (!len || c > 0xF4 || end - p < len) return fail("invalid UTF-8 in string");
+        unsigned cp = c & (0xFF >> (len + 1));
+        for (int i = 1; i < len; ++i) {
+          const unsigned char d = (unsigned char)p[i];
+          if ((d & 0xC0) != 0x80) return fail("invalid UTF-8 in string");
+          cp = (cp << 6) | (d & 0x3F);
+        }
+        if ((len == 3 && (cp < 0x800 || (cp >= 0xD800 && cp < 0xE000))) || (len == 4 && (cp < 0x10000 || cp > 0x10FFFF)))
+          return fail("invalid UTF-8 in string");
+        out.append(p, (size_t)len);
+        p += len;
+      }
+    }
+    if (p >= end) return fail("unterminated string");
+    ++p;
+    return true;
+  }
+  bool value(JVal& v) {
+    if (++depth > 128) return fail("nesting too deep");
+    ws();
+    if (p >= end) return fail("unexpected end");
+    bool ok = true;
+    if (*p == '{') {
+      v.kind = JVal::Obj;
+      ++p; ws();
+      if (p < end && *p == '}') ++p;
+      else for (;;) {
+        ws();
+        std::string k;
+        if (!str(k)) { ok = false; break; }
+        ws();
+        if (p >= end || *p != ':') { ok = fail("expected ':'"); break; }
+        ++p;
+        v.obj.emplace_back(std::move(k), JVal());
+        if (!value(v.obj.back().second)) { ok = false; break; }
+        ws();
+        if (p < end && *p == ',') { ++p; continue; }
+        if (p < end && *p == '}') { ++p; break; }
+        ok = fail("expected ',' or '}'"); break;
+      }
+    } else if (*p == '[') {
+      v.kind = JVal::Arr;
+      ++p; ws();
+      if (p < end && *p == ']') ++p;
+      else for (;;) {
+        v.arr.emplace_back();
+        if (!value(v.arr.back())) { ok = false; break; }
+        ws();
+        if (p < end && *p == ',') { ++p; continue; }
+        if (p < end && *p == ']') { ++p; break; }
+        ok = fail("expected ',' or ']'"); break;
+      }
+    } else if (*p == '"') {
+      v.kind = JVal::Str;
+      ok = str(v.s);
+    } else if (end - p >= 4 && !std::strncmp(p, "true", 4)) { v.kind = JVal::Bool; v.b = true; p += 4; }
+    else if (end - p >= 5 && !std::strncmp(p, "false", 5)) { v.kind = JVal::Bool; v.b = false; p += 5; }
+    else if (end - p >= 4 && !std::strncmp(p, "null", 4)) { v.kind = JVal::Null; p += 4; }
+    else if (*p == '-' || (*p >= '0' && *p <= '9')) {
+      v.kind = JVal::Num;
+      const char* q = p;
+      if (*p == '-') ++p;
+      if (p >= end || *p < '0' || *p > '9') return fail("bad number");
+      while (p < end && ((*p >= '0' && *p <= '9') || *p == '.' || *p == 'e' || *p == 'E' || *p == '+' || *p == '-')) ++p;
+      v.s.assign(q, p);
+    } else ok = fail("unexpected character");
+    --depth;
+    return ok;
+  }
+};
+
+// DynamicObject::try_parse::<UserBootstrap>() approximated as in the Python mirror
+// (bacchus-gpu-controller_b200/admission.py::_parses_as_userbootstrap; crd.rs:19-42).
+bool parses_as_userbootstrap(const JVal& obj) {
+  const JVal* spec = obj.get_obj("spec");
+  if (!spec) return false;
+  auto opt_is = [&](const char* k, JVal::Kind kind) {
+    const JVal* v = spec->get(k);
+    return !v || v->kind == JVal::Null || v->kind == kind;
+  };
+  if (!opt_is("kube_username", JVal::Str) || !opt_is("quota", JVal::Obj) || !opt_is("role", JVal::Obj)) return false;
+  const JVal* rb = spec->get("rolebinding");
+  if (rb && rb->kind != JVal::Null) {
+    if (rb->kind != JVal::Obj) return false;
+    const JVal* rr = rb->get_obj("role_ref");
+    if (!rr || !rr->get_str("apiGroup") || !rr->get_str("kind") || !rr->get_str("name")) return false;
+    const JVal* subs = rb->get("subjects");
+    if (subs && subs->kind != JVal::Null && subs->kind != JVal::Arr) return false;
+  }
+  return true;
+}
+
+const char kB64[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+void base64(std::string& out, std::string_view in) {
+  size_t i = 0;
+  for (; i + 2 < in.size(); i += 3) {
+    const unsigned v = ((unsigned char)in[i] << 16) | ((unsigned char)in[i + 1] << 8) | (unsigned char)in[i + 2];
+    out.push_back(kB64[v >> 18]); out.push_back(kB64[(v >> 12) & 63]); out.push_back(kB64[(v >> 6) & 63]); out.push_back(kB64[v & 63]);
+  }
+  if (i + 1 == in.size()) {
+    const unsigned v = (unsigned char)in[i] << 16;
+    out.push_back(kB64[v >> 18]); out.push_back(kB64[(v >> 12) & 63]); out += "==";
+  } else if (i + 2 == in.size()) {
+    const unsigned v = ((unsigned char)in[i] << 16) | ((unsigned char)in[i + 1] << 8);
+    out.push_back(kB64[v >> 18]); out.push_back(kB64[(v >> 12) & 63]); out.push_back(kB64[(v >> 6) & 63]); out.push_back('=');
+  }
+}
+
+}  // namespace
+
+struct bgc_review {
+  JVal doc;
+  const JVal* request = nullptr;
+  std::vector<const char*> groups;
+  // pod view
+  std::vector<std::vector<const char*>> name_store, quant_store;
+  std::vector<bgc_container_spec> containers, init_containers;
+  bgc_resource_list overhead{};
+  bool has_overhead = false;
+  std::string ns;
+};
+
+extern "C" {
+
+bgc_review* bgc_review_parse(const char* json, size_t len, char* err, size_t err_len) {
+  if (err && err_len) err[0] = 0;
+  if (!json) return nullptr;
+  auto r = new (std::nothrow) bgc_review;
+  if (!r) return nullptr;
+  JParser ps{json, json + len, {}, 0};
+  bool ok = ps.value(r->doc);
+  if (ok) { ps.ws(); if (ps.p != ps.end) ok = ps.fail("trailing characters"); }
+  if (!ok || r->doc.kind != JVal::Obj) {
+    if (err && err_len) snprintf(err, err_len, "%s", ok ? "AdmissionReview must be a JSON object" : ps.err.c_str());
+    delete r;
+    return nullptr;
+  }
+  r->request = r->doc.get_obj("request");
+  return r;
+}
+
+void bgc_review_destroy(bgc_review* r) { delete r; }
+int bgc_review_has_request(const bgc_review* r) { return r && r->request ? 1 : 0; }
+
+const char* bgc_review_uid(const bgc_review* r) {
+  const char* u = r && r->request ? r->request->get_str("uid") : nullptr;
+  return u ? u : "";
+}
+
+const char* bgc_review_kind(const bgc_review* r) {
+  const JVal* k = r && r->request ? r->request->get_obj("kind") : nullptr;
+  const char* s = k ? k->get_str("kind") : nullptr;
+  return s ? s : "";
+}
+
+int bgc_review_request(const bgc_review* rc, bgc_admission_request* out) {
+  if (!rc || !out || !rc->request) return BGC_E_BADARG;
+  bgc_review* r = const_cast<bgc_review*>(rc);
+  const JVal& q = *r->request;
+  std::memset(out, 0, sizeof *out);
+  const JVal* ui = q.get_obj("userInfo");
+  out->username = ui ? ui->get_str("username") : nullptr;                     // src/admission.rs:248
+  const JVal* groups = ui ? ui->get("groups") : nullptr;
+  r->groups.clear();
+  if (groups && groups->kind == JVal::Arr) {                                  // :263-267
+    for (const auto& g : groups->arr)
+      if (g.kind == JVal::Str) r->groups.push_back(g.s.c_str());
+    static const char* const kNoGroups[1] = {nullptr};  // Some([]) is distinct from None
+    out->groups = r->groups.empty() ? kNoGroups : r->groups.data();
+    out->n_groups = r->groups.size();
+  }
+  const char* op = q.get_str("operation");                                    // :272
+  out->operation = !op ? BGC_OP_OTHER : !std::strcmp(op, "CREATE") ? BGC_OP_CREATE : !std::strcmp(op, "UPDATE") ? BGC_OP_UPDATE
+                   : !std::strcmp(op, "DELETE") ? BGC_OP_DELETE : BGC_OP_OTHER;
+  const JVal* obj = q.get("object");
+  if (obj && obj->kind == JVal::Obj) {                                        // :312
+    out->has_object = 1;
+    const JVal* meta = obj->get_obj("metadata");
+    out->name = meta ? meta->get_str("name") : nullptr;                       // :321
+    if (parses_as_userbootstrap(*obj)) {                                      // :341
+      out->parse_ok = 1;
+      const JVal* spec = obj->get_obj("spec");
+      out->spec_kube_username = spec->get_str("kube_username");               // :362-367
+      const JVal* quota = spec->get("quota");
+      out->has_quota = quota && quota->kind != JVal::Null;                    // :376
+      const JVal* rb = spec->get("rolebinding");
+      out->has_rolebinding = rb && rb->kind != JVal::Null;                    // :386
+    }
+  }
+  return BGC_OK;
+}
+
+static void fill_list(bgc_review* r, const JVal* m, bgc_resource_list* out) {
+  r->name_store.emplace_back();
+  r->quant_store.emplace_back();
+  auto& names = r->name_store.back();
+  auto& quants = r->quant_store.back();
+  if (m && m->kind == JVal::Obj)
+    for (const auto& kv : m->obj)
+      if (kv.second.kind == JVal::Str || kv.second.kind == JVal::Num) {  // quantities arrive as strings or bare numbers
+        names.push_back(kv.first.c_str());
+        quants.push_back(kv.second.s.c_str());
+      }
+  out->names = names.data();
+  out->quantities = quants.data();
+  out->n = names.size();
+}
+
+static void fill_containers(bgc_review* r, const JVal* list, std::vector<bgc_container_spec>& out) {
+  out.clear();
+  if (!list || list->kind != JVal::Arr) return;
+  for (const auto& c : list->arr) {
+    bgc_container_spec cs{};
+    const JVal* res = c.get_obj("resources");
+    fill_list(r, res ? res->get("requests") : nullptr, &cs.requests);
+    fill_list(r, res ? res->get("limits") : nullptr, &cs.limits);
+    out.push_back(cs);
+  }
+}
+
+int bgc_review_pod(const bgc_review* rc, bgc_pod_spec* out) {
+  if (!rc || !out || !rc->request) return BGC_E_BADARG;
+  bgc_review* r = const_cast<bgc_review*>(rc);
+  const JVal* obj = r->request->get_obj("object");
+  if (!obj) return BGC_E_BADARG;
+  r->name_store.clear(); r->quant_store.clear();
+  // the stores must not reallocate while pointers into them are handed out
+  r->name_store.reserve(4096); r->quant_store.reserve(4096);
+  const JVal* spec = obj->get_obj("spec");
+  const JVal* meta = obj->get_obj("metadata");
+  const char* ns = r->request->get_str("namespace");
+  if (!ns && meta) ns = meta->get_str("namespace");
+  r->ns = ns ? ns : "default";
+  fill_containers(r, spec ? spec->get("containers") : nullptr, r->containers);
+  fill_containers(r, spec ? spec->get("initContainers") : nullptr, r->init_containers);
+  const JVal* oh = spec ? spec->get("overhead") : nullptr;
+  r->has_overhead = oh && oh->kind == JVal::Obj;
+  if (r->has_overhead) fill_list(r, oh, &r->overhead);
+  const JVal* status = obj->get_obj("status");
+  const char* phase = status ? status->get_str("phase") : nullptr;
+  out->ns = r->ns.c_str();
+  out->phase = !phase ? BGC_PHASE_PENDING : !std::strcmp(phase, "Running") ? BGC_PHASE_RUNNING : !std::strcmp(phase, "Succeeded") ? BGC_PHASE_SUCCEEDED
+               : !std::strcmp(phase, "Failed") ? BGC_PHASE_FAILED : !std::strcmp(phase, "Pending") ? BGC_PHASE_PENDING : BGC_PHASE_UNKNOWN;
+  out->containers = r->containers.data(); out->n_containers = r->containers.size();
+  out->init_containers = r->init_containers.data(); out->n_init_containers = r->init_containers.size();
+  out->overhead = r->has_overhead ? &r->overhead : nullptr;
+  return BGC_OK;
+}
+
+long bgc_render_review_response(const char* uid, const bgc_admission_response* resp, const char* message_override,
+                                const char* patch_json, char* buf, size_t cap) {
+  if (!resp || !buf) return BGC_E_BADARG;
+  std::string s = "{\"apiVersion\":\"admission.k8s.io/v1\",\"kind\":\"AdmissionReview\",\"response\":{\"uid\":";
+  const char* msg = message_override ? message_override : resp->message;
+  if (resp->klass == BGC_INVALID) {  // AdmissionResponse::invalid: fresh response without the request's uid
+    json_escape(s, "");
+    s += ",\"allowed\":false,\"status\":{\"status\":\"Failure\",\"code\":400,\"message\":";
+    json_escape(s, msg ? msg : "");
+    s += ",\"reason\":\"InvalidRequest\"}";
+  } else {
+    json_escape(s, uid ? uid : "");
+    s += resp->allowed ? ",\"allowed\":true,\"status\":{" : ",\"allowed\":false,\"status\":{";
+    if (!resp->allowed) { s += "\"message\":"; json_escape(s, msg ? msg : ""); }
+    s += "}";
+    if (resp->allowed && patch_json && patch_json[0]) {  // with_patch, src/admission.rs:429
+      s += ",\"patch\":\"";
+      base64(s, patch_json);
+      s += "\",\"patchType\":\"JSONPatch\"";
+    }
+  }
+  s += "}}";
+  if (s.size() + 1 > cap) return BGC_E_BADARG;
+  std::memcpy(buf, s.c_str(), s.size() + 1);
+  return (long)s.size();
 }
 
 }  // extern "C"

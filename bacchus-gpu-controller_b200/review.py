@@ -1,0 +1,137 @@
+"""Row N4: AdmissionReview v1 JSON in and out — the batched form of the reference's `mutate_handler`
+(reference src/admission.rs:184-204): wire bytes → AdmissionRequest fields (C++ parser in libbgc) →
+flatten (row A2) → decision on the GPU (K0, row A1) → AdmissionReview response JSON with the
+reference's messages and base64 JSONPatch.  Byte-level parity with kube-core/serde_json is unpinned."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Sequence
+
+import numpy as np
+
+from . import lib, OK, BgcError, Engine
+from .admission import AdmissionConfig, _CRequest, _CResponse, _CConfig
+from .pods import _Pod
+
+lib.bgc_review_parse.restype = C.c_void_p
+lib.bgc_review_parse.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+lib.bgc_review_destroy.argtypes = [C.c_void_p]
+lib.bgc_review_has_request.argtypes = [C.c_void_p]
+lib.bgc_review_uid.restype = C.c_char_p
+lib.bgc_review_uid.argtypes = [C.c_void_p]
+lib.bgc_review_kind.restype = C.c_char_p
+lib.bgc_review_kind.argtypes = [C.c_void_p]
+lib.bgc_review_request.argtypes = [C.c_void_p, C.POINTER(_CRequest)]
+lib.bgc_review_pod.argtypes = [C.c_void_p, C.POINTER(_Pod)]
+lib.bgc_render_review_response.restype = C.c_long
+lib.bgc_render_review_response.argtypes = [C.c_char_p, C.POINTER(_CResponse), C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]
+lib.bgc_render_patch.argtypes = [C.POINTER(_CConfig), C.POINTER(_CRequest), C.c_uint8, C.c_char_p, C.c_size_t]
+
+
+class Review:
+    """One parsed AdmissionReview document (owns the strings the request view points into)."""
+
+    def __init__(self, body: bytes | str):
+        raw = body.encode() if isinstance(body, str) else body
+        err = C.create_string_buffer(256)
+        self._h = lib.bgc_review_parse(raw, len(raw), err, 256)
+        if not self._h:
+            raise ValueError(err.value.decode() or "malformed AdmissionReview")
+
+    @property
+    def has_request(self) -> bool:
+        return bool(lib.bgc_review_has_request(self._h))
+
+    @property
+    def uid(self) -> str:
+        return lib.bgc_review_uid(self._h).decode()
+
+    @property
+    def kind(self) -> str:
+        return lib.bgc_review_kind(self._h).decode()
+
+    def c_request(self) -> _CRequest:
+        r = _CRequest()
+        if lib.bgc_review_request(self._h, C.byref(r)) != OK:
+            raise BgcError(-1, "review has no request")
+        return r
+
+    def request_fields(self) -> dict:
+        r = self.c_request()
+        dec = lambda b: None if b is None else b.decode()
+        return dict(username=dec(r.username), groups=None if not r.groups else [r.groups[i].decode() for i in range(r.n_groups)],
+                    operation=r.operation, has_object=bool(r.has_object), name=dec(r.name), parse_ok=bool(r.parse_ok),
+                    spec_kube_username=dec(r.spec_kube_username), has_quota=bool(r.has_quota), has_rolebinding=bool(r.has_rolebinding))
+
+    def c_pod(self) -> _Pod:
+        p = _Pod()
+        if lib.bgc_review_pod(self._h, C.byref(p)) != OK:
+            raise BgcError(-1, "review carries no object")
+        return p
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.bgc_review_destroy(self._h)
+            self._h = None
+
+
+def _render(uid: str, resp: _CResponse, message_override, patch) -> str:
+    buf = C.create_string_buffer(8192)
+    n = lib.bgc_render_review_response(uid.encode(), C.byref(resp), None if message_override is None else message_override.encode(),
+                                       None if patch is None else patch, buf, 8192)
+    if n < 0:
+        raise BgcError(int(n), "bgc_render_review_response")
+    return buf.value.decode()
+
+
+def handle_reviews(engine: Engine, config: AdmissionConfig, bodies: Sequence[bytes | str]) -> list:
+    """Batched `mutate_handler`: one response JSON string per request body.  Reviews without a
+    `request` are answered `invalid` like src/admission.rs:189-197; everything else is flattened,
+    decided in one K0 launch, and rendered."""
+    reviews = [Review(b) for b in bodies]
+    live = [i for i, r in enumerate(reviews) if r.has_request]
+    creqs = (_CRequest * max(1, len(live)))()
+    for k, i in enumerate(live):
+        lib.bgc_review_request(reviews[i]._h, C.byref(creqs[k]))
+    cc, keep = config._c()
+    out = (_CResponse * max(1, len(live)))()
+    engine._ck(lib.bgc_mutate_batch(engine._h, C.byref(cc), creqs, C.c_size_t(len(live)), out))
+    res = [None] * len(reviews)
+    pbuf = C.create_string_buffer(4096)
+    for k, i in enumerate(live):
+        patch = None
+        if out[k].patch_mask:
+            n = lib.bgc_render_patch(C.byref(cc), C.byref(creqs[k]), out[k].patch_mask, pbuf, 4096)
+            if n < 0:
+                raise BgcError(int(n), "bgc_render_patch")
+            patch = pbuf.value
+        res[i] = _render(reviews[i].uid, out[k], None, patch)
+    for i, r in enumerate(reviews):
+        if res[i] is None:
+            bad = _CResponse(0, 3, 0, 0, None)
+            res[i] = _render("", bad, "invalid request: AdmissionReview carries no request", None)
+    return res
+
+
+def flatten_pod_reviews(bodies: Sequence[bytes | str], quota_keys: Sequence[str], nsmap, intern: bool = False):
+    """Pod-create AdmissionReviews → (ns_id, req[R], req_mask) columns through bgc_flatten_pods."""
+    from .pods import QUOTA_KEYS
+    reviews = [Review(b) for b in bodies]
+    n = len(reviews)
+    arr = (_Pod * max(1, n))()
+    for i, r in enumerate(reviews):
+        arr[i] = r.c_pod()
+    R = len(quota_keys)
+    keys = (C.c_char_p * R)(*[k.encode() for k in quota_keys])
+    unit = np.array([QUOTA_KEYS[k] for k in quota_keys], np.uint8)
+    ns_id = np.empty(n, np.uint32)
+    req = [np.empty(n, np.int64) for _ in range(R)]
+    mask = np.empty(n, np.uint8)
+    ptrs = (C.c_void_p * R)(*[c.ctypes.data for c in req])
+    n_out = C.c_size_t()
+    rc = lib.bgc_flatten_pods(arr, C.c_size_t(n), keys, C.c_void_p(unit.ctypes.data), C.c_uint32(R), nsmap._h, C.c_int(int(intern)),
+                              C.c_void_p(ns_id.ctypes.data), ptrs, C.c_void_p(mask.ctypes.data), C.byref(n_out))
+    if rc != OK:
+        raise BgcError(rc, "bgc_flatten_pods")
+    m = n_out.value
+    return ns_id[:m].copy(), [c[:m].copy() for c in req], mask[:m].copy(), unit

@@ -133,6 +133,36 @@ int bgc_hard_from_sheet_row(int64_t cpu_request, int64_t memory_request_gi, int6
                             const char *const *quota_keys, uint32_t R, int64_t *hard_out,
                             uint8_t *unit_out);
 
+/* ---- row N4: AdmissionReview v1 JSON in and out ---------------------------------
+ * What `mutate_handler` does around `mutate` (src/admission.rs:184-204): the axum `Json` extractor
+ * turns the body into AdmissionReview<DynamicObject>, `try_into()` yields the AdmissionRequest (a
+ * review without `request` becomes an `invalid` response, :189-197), and `into_review()` wraps the
+ * response.  Byte-level parity with kube-core 0.84 / serde_json is unpinned:
+ * field order and the Status shape below are restated from memory. */
+typedef struct bgc_review bgc_review;
+
+/* NULL + message on malformed JSON (the reference answers 4xx from the extractor). */
+bgc_review *bgc_review_parse(const char *json, size_t len, char *err, size_t err_len);
+void bgc_review_destroy(bgc_review *r);
+/* 1 when the document carries a `request` object (AdmissionReview::try_into succeeds) */
+int bgc_review_has_request(const bgc_review *r);
+const char *bgc_review_uid(const bgc_review *r);       /* request.uid or "" */
+/* request.kind.kind, e.g. "UserBootstrap" or "Pod" ("" when absent) */
+const char *bgc_review_kind(const bgc_review *r);
+/* the fields mutate() reads; string pointers stay valid until bgc_review_destroy */
+int bgc_review_request(const bgc_review *r, bgc_admission_request *out);
+/* request.object as a pod spec for bgc_flatten_pods (namespace from request.namespace or
+ * object.metadata.namespace); pointers valid until bgc_review_destroy */
+int bgc_review_pod(const bgc_review *r, bgc_pod_spec *out);
+
+/* AdmissionReview response text for one decision.  patch_json = bgc_render_patch output or NULL.
+ * allow   → {"uid","allowed":true,"status":{}} (+ "patch": base64, "patchType":"JSONPatch")
+ * deny    → allowed:false, status.message = the reference's literal
+ * invalid → uid "", allowed:false, status {"status":"Failure","code":400,"message",...,"reason":"InvalidRequest"}
+ * Returns the length written or BGC_E_BADARG when the buffer is too small. */
+long bgc_render_review_response(const char *uid, const bgc_admission_response *resp, const char *message_override,
+                                const char *patch_json, char *buf, size_t cap);
+
 /* ---- row N2: the quota-table producer ------------------------------------------
  * Batch form of the synchronizer's sheet logic, reference src/synchronizer.rs:63-169,208-281:
  * the Google-Form CSV export is parsed with the reference's header heuristics, filtered by GPU

@@ -1,0 +1,93 @@
+"""Row N4: AdmissionReview JSON in/out.  CPU tests cover the C++ parser against Python's json module
+and the Python mirror; the GPU test runs wire bytes → K0 → response JSON against the oracle."""
+import base64
+import json
+
+import numpy as np
+import pytest
+
+from oracle import policy_ref as P
+
+
+def _reviews():
+    cfg = P.Config()
+    out = []
+    for op in range(4):
+        for fl in range(1024):
+            r = P.request_from_bits(op, fl, cfg)
+            if r is not None:
+                out.append({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview", "request": r})
+    return out
+
+
+def test_parser_extracts_the_fields_mutate_reads(bgc):
+    A, Rv = bgc.admission, bgc.review
+    for rv in _reviews():
+        for text in (json.dumps(rv), json.dumps(rv, indent=2, ensure_ascii=True)):
+            got = Rv.Review(text).request_fields()
+            want = A.AdmissionRequest.from_review(rv["request"])
+            assert got["username"] == want.username and got["groups"] == (None if want.groups is None else list(want.groups))
+            assert got["operation"] == A.OPERATIONS[want.operation]
+            assert (got["has_object"], got["name"], got["parse_ok"]) == (want.has_object, want.name, want.parse_ok)
+            assert (got["spec_kube_username"], got["has_quota"], got["has_rolebinding"]) == (want.spec_kube_username, want.has_quota, want.has_rolebinding)
+
+
+def test_parser_json_details(bgc):
+    Rv = bgc.review
+    body = r'{"request":{"uid":"é😀-\"q\"","operation":"CREATE","kind":{"kind":"UserBootstrap"},"userInfo":{"username":"oidc:알리스","groups":[]},"object":{"metadata":{"name":"알리스"},"spec":{"kube_username":null,"quota":null}}},"extra":[1,2.5e3,true,null]}'
+    r = Rv.Review(body)
+    assert r.uid == 'é😀-"q"' and r.kind == "UserBootstrap"
+    f = r.request_fields()
+    assert f["username"] == "oidc:알리스" and f["groups"] == [] and f["name"] == "알리스" and f["parse_ok"] and not f["has_quota"]
+    assert not Rv.Review('{"apiVersion":"admission.k8s.io/v1"}').has_request
+    for bad in ["", "{", '{"a":}', '{"a":1,}', "[1,2", '{"a":"\\x"}', b'{"a":"\xff"}', b'{"a":"\xed\xa0\x80"}', b'{"a":"\xc0\xaf"}', '{"a":"\\ud800"}', "nul", '{"a":1} x', '"str"']:
+        with pytest.raises(ValueError):
+            Rv.Review(bad)
+
+
+def test_pod_review_flattening_equals_dict_flattening(bgc):
+    import sys, os
+    sys.path.insert(0, os.path.dirname(__file__))
+    from workloads import C1_KEYS, c1_namespaces, c1_pods
+    nss = c1_namespaces()
+    pods = c1_pods(500, nss, running=False)
+    m = bgc.pods.NamespaceMap()
+    for ns in nss:
+        m.intern(ns["name"])
+    bodies = [json.dumps({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview",
+                          "request": {"uid": f"u{i}", "operation": "CREATE", "kind": {"kind": "Pod"}, "namespace": p["metadata"]["namespace"], "object": p}})
+              for i, p in enumerate(pods)]
+    a = bgc.review.flatten_pod_reviews(bodies, C1_KEYS, m)
+    b = bgc.pods.flatten_pods(pods, C1_KEYS, m, intern=False)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
+    for x, y in zip(a[1], b[1]):
+        assert np.array_equal(x, y)
+
+
+@pytest.mark.gpu
+def test_wire_bytes_to_response_json(bgc, engine):
+    cfg_py, cfg = P.Config(), bgc.admission.AdmissionConfig()
+    reviews = _reviews()
+    bodies = [json.dumps(rv) for rv in reviews] + ['{"apiVersion":"admission.k8s.io/v1","kind":"AdmissionReview"}']
+    outs = bgc.review.handle_reviews(engine, cfg, bodies)
+    assert len(outs) == len(bodies)
+    for rv, text in zip(reviews, outs):
+        doc = json.loads(text)
+        assert doc["apiVersion"] == "admission.k8s.io/v1" and doc["kind"] == "AdmissionReview"
+        resp = doc["response"]
+        d = P.mutate(rv["request"], cfg_py)
+        assert resp["allowed"] == (d.klass in (P.ALLOW, P.ALLOW_PATCH))
+        if d.klass == P.INVALID:
+            assert resp["uid"] == "" and resp["status"]["code"] == 400 and resp["status"]["reason"] == "InvalidRequest"
+            if d.reason != 8:
+                assert resp["status"]["message"] == d.message
+        else:
+            assert resp["uid"] == rv["request"]["uid"]
+            if d.klass == P.DENY:
+                assert resp["status"]["message"] == d.message
+        if d.patch_mask:
+            assert resp["patchType"] == "JSONPatch" and json.loads(base64.b64decode(resp["patch"])) == d.patches
+        else:
+            assert "patch" not in resp
+    last = json.loads(outs[-1])["response"]
+    assert last["allowed"] is False and last["status"]["reason"] == "InvalidRequest"
