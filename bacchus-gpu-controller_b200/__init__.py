@@ -51,6 +51,7 @@ EXPORTS = [
     "bgc_sheet_get_row", "bgc_sheet_match", "bgc_sheet_row_quota",
     "bgc_review_parse", "bgc_review_destroy", "bgc_review_has_request", "bgc_review_uid", "bgc_review_kind",
     "bgc_review_request", "bgc_review_pod", "bgc_render_review_response",
+    "bgc_reconcile_plan", "bgc_plan_destroy", "bgc_plan_count", "bgc_plan_item", "bgc_plan_requeue_seconds",
 ]
 
 
@@ -321,4 +322,4 @@ def version() -> str:
     return lib.bgc_version().decode()
 
 
-from . import admission, pods, shard, sheet, review  # noqa: E402,F401
+from . import admission, pods, shard, sheet, review, reconcile  # noqa: E402,F401

@@ -985,3 +985,129 @@ long bgc_render_review_response(const char* uid, const bgc_admission_response* r
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------ row N3
+// Reconcile plan: the objects `reconcile()` server-side-applies for one UserBootstrap
+// (reference src/controller.rs:50-155), as (path, body) pairs in the reference's order.
+namespace {
+
+void jdump(std::string& out, const JVal& v) {
+  switch (v.kind) {
+    case JVal::Null: out += "null"; break;
+    case JVal::Bool: out += v.b ? "true" : "false"; break;
+    case JVal::Num: out += v.s; break;
+    case JVal::Str: json_escape(out, v.s); break;
+    case JVal::Arr:
+      out.push_back('[');
+      for (size_t i = 0; i < v.arr.size(); ++i) { if (i) out.push_back(','); jdump(out, v.arr[i]); }
+      out.push_back(']');
+      break;
+    case JVal::Obj:
+      out.push_back('{');
+      for (size_t i = 0; i < v.obj.size(); ++i) {
+        if (i) out.push_back(',');
+        json_escape(out, v.obj[i].first);
+        out.push_back(':');
+        jdump(out, v.obj[i].second);
+      }
+      out.push_back('}');
+      break;
+  }
+}
+
+}  // namespace
+
+struct bgc_plan_item_s { std::string kind, ns, name, path, body; bool namespaced; };
+struct bgc_plan { std::vector<bgc_plan_item_s> items; };
+
+extern "C" {
+
+bgc_plan* bgc_reconcile_plan(const char* ub_json, size_t len, char* err, size_t err_len) {
+  if (err && err_len) err[0] = 0;
+  auto say = [&](const char* m) -> bgc_plan* { if (err && err_len) snprintf(err, err_len, "%s", m); return nullptr; };
+  if (!ub_json) return say("null document");
+  JVal doc;
+  JParser ps{ub_json, ub_json + len, {}, 0};
+  bool ok = ps.value(doc);
+  if (ok) { ps.ws(); ok = ps.p == ps.end; }
+  if (!ok || doc.kind != JVal::Obj) return say(ps.err.empty() ? "UserBootstrap must be a JSON object" : ps.err.c_str());
+  const JVal* meta = doc.get_obj("metadata");
+  const char* ub_name = meta ? meta->get_str("name") : nullptr;
+  const char* ub_uid = meta ? meta->get_str("uid") : nullptr;
+  // controller_owner_ref(&()).unwrap() at src/controller.rs:52 needs both name and uid
+  if (!ub_name || !ub_uid) return say("missing object key: .metadata.name / .metadata.uid (no controller owner reference)");
+  std::string name(ub_name);
+  for (auto& c : name)
+    if (c >= 'A' && c <= 'Z') c = (char)(c - 'A' + 'a');  // .to_lowercase() :63 (object names are ASCII)
+  std::string oref = "{\"apiVersion\":\"bacchus.io/v1\",\"blockOwnerDeletion\":true,\"controller\":true,\"kind\":\"UserBootstrap\",\"name\":";
+  json_escape(oref, ub_name);
+  oref += ",\"uid\":";
+  json_escape(oref, ub_uid);
+  oref += "}";
+  std::string qname;
+  json_escape(qname, name);
+  const std::string metadata = "{\"name\":" + qname + ",\"ownerReferences\":[" + oref + "]}";
+  const std::string params = "?fieldManager=bacchus-gpu-controller.bacchus.io&force=true";  // PatchParams::apply(PATCH_MANAGER).force() :67
+  auto plan = new (std::nothrow) bgc_plan;
+  if (!plan) return say("out of memory");
+  // Namespace :69-87
+  plan->items.push_back({"Namespace", "", name, "/api/v1/namespaces/" + name + params,
+                         "{\"apiVersion\":\"v1\",\"kind\":\"Namespace\",\"metadata\":" + metadata + "}", false});
+  const JVal* spec = doc.get_obj("spec");
+  const JVal* quota = spec ? spec->get("quota") : nullptr;
+  if (quota && quota->kind != JVal::Null) {  // ResourceQuota only if spec.quota is Some :89-110
+    std::string body = "{\"apiVersion\":\"v1\",\"kind\":\"ResourceQuota\",\"metadata\":" + metadata + ",\"spec\":";
+    jdump(body, *quota);
+    body += "}";
+    plan->items.push_back({"ResourceQuota", name, name, "/api/v1/namespaces/" + name + "/resourcequotas/" + name + params, body, true});
+  }
+  const JVal* role = spec ? spec->get("role") : nullptr;
+  if (role && role->kind == JVal::Obj) {  // Role if Some, owner reference overwritten :112-124
+    std::string body = "{\"apiVersion\":\"rbac.authorization.k8s.io/v1\",\"kind\":\"Role\",\"metadata\":{";
+    bool first = true;
+    if (const JVal* rmeta = role->get_obj("metadata"))
+      for (const auto& kv : rmeta->obj) {
+        if (kv.first == "ownerReferences") continue;
+        if (!first) body.push_back(',');
+        json_escape(body, kv.first); body.push_back(':'); jdump(body, kv.second);
+        first = false;
+      }
+    if (!first) body.push_back(',');
+    body += "\"ownerReferences\":[" + oref + "]}";
+    if (const JVal* rules = role->get("rules")) { body += ",\"rules\":"; jdump(body, *rules); }
+    body += "}";
+    plan->items.push_back({"Role", name, name, "/apis/rbac.authorization.k8s.io/v1/namespaces/" + name + "/roles/" + name + params, body, true});
+  }
+  const JVal* rb = spec ? spec->get("rolebinding") : nullptr;
+  const JVal* status = doc.get_obj("status");
+  const JVal* synced = status ? status->get("synchronized_with_sheet") : nullptr;
+  // RoleBinding only once the sheet synchroniser has vouched for the user :126-152
+  if (rb && rb->kind == JVal::Obj && synced && synced->kind == JVal::Bool && synced->b) {
+    std::string body = "{\"apiVersion\":\"rbac.authorization.k8s.io/v1\",\"kind\":\"RoleBinding\",\"metadata\":" + metadata + ",\"roleRef\":";
+    if (const JVal* rr = rb->get("role_ref")) jdump(body, *rr); else body += "null";
+    const JVal* subs = rb->get("subjects");
+    if (subs && subs->kind != JVal::Null) { body += ",\"subjects\":"; jdump(body, *subs); }
+    body += "}";
+    plan->items.push_back({"RoleBinding", name, name, "/apis/rbac.authorization.k8s.io/v1/namespaces/" + name + "/rolebindings/" + name + params, body, true});
+  }
+  return plan;
+}
+
+void bgc_plan_destroy(bgc_plan* p) { delete p; }
+size_t bgc_plan_count(const bgc_plan* p) { return p ? p->items.size() : 0; }
+
+int bgc_plan_item(const bgc_plan* p, size_t i, const char** kind, const char** ns, const char** name, const char** path,
+                  const char** body) {
+  if (!p || i >= p->items.size()) return BGC_E_BADARG;
+  const auto& it = p->items[i];
+  if (kind) *kind = it.kind.c_str();
+  if (ns) *ns = it.namespaced ? it.ns.c_str() : nullptr;
+  if (name) *name = it.name.c_str();
+  if (path) *path = it.path.c_str();
+  if (body) *body = it.body.c_str();
+  return BGC_OK;
+}
+
+int bgc_plan_requeue_seconds(int failed) { return failed ? 3 : 30; }  // src/controller.rs:154,174
+
+}  // extern "C"

@@ -163,6 +163,24 @@ int bgc_review_pod(const bgc_review *r, bgc_pod_spec *out);
 long bgc_render_review_response(const char *uid, const bgc_admission_response *resp, const char *message_override,
                                 const char *patch_json, char *buf, size_t cap);
 
+/* ---- row N3: reconcile plan ------------------------------------------------------
+ * The objects `reconcile()` server-side-applies for one UserBootstrap (src/controller.rs:50-155),
+ * as request path + body pairs in the reference's order: Namespace (name lower-cased, :55-63),
+ * ResourceQuota only if spec.quota is set (:89-110), Role if set (:112-124, owner reference
+ * overwritten), RoleBinding only if set AND status.synchronized_with_sheet (:126-152); every object
+ * carries the controller owner reference (:52); paths carry PatchParams::apply(PATCH_MANAGER).force()
+ * (:22,:67).  Wire format only — nothing is sent.  Field order of the bodies is unpinned. */
+typedef struct bgc_plan bgc_plan;
+/* NULL + message for malformed JSON or a missing metadata.name / metadata.uid */
+bgc_plan *bgc_reconcile_plan(const char *userbootstrap_json, size_t len, char *err, size_t err_len);
+void bgc_plan_destroy(bgc_plan *p);
+size_t bgc_plan_count(const bgc_plan *p);
+/* ns is NULL for the cluster-scoped Namespace object; pointers valid until bgc_plan_destroy */
+int bgc_plan_item(const bgc_plan *p, size_t i, const char **kind, const char **ns, const char **name,
+                  const char **path, const char **body);
+/* Action::requeue: 30 s after success (:154), 3 s after an error (:174) */
+int bgc_plan_requeue_seconds(int failed);
+
 /* ---- row N2: the quota-table producer ------------------------------------------
  * Batch form of the synchronizer's sheet logic, reference src/synchronizer.rs:63-169,208-281:
  * the Google-Form CSV export is parsed with the reference's header heuristics, filtered by GPU
