@@ -30,7 +30,7 @@ OK, E_BADARG, E_CUDA, E_OOM, E_STATE = 0, -1, -2, -3, -4
 MAX_R = 4
 UNIT_COUNT, UNIT_MILLI, UNIT_BYTES = 0, 1, 2
 REDUCE_GROUPED, REDUCE_ACCUMULATE = 1, 2
-K1_AUTO, K1_GLOBAL, K1_SMEM_DIRECT, K1_SMEM_HASH = 0, 1, 2, 3
+K1_AUTO, K1_GLOBAL, K1_SMEM_DIRECT, K1_SMEM_HASH, K1_CLUSTER8, K1_CLUSTER16 = 0, 1, 2, 3, 4, 5
 VERDICT_BAD_NS = 0xFF
 ALLOW, ALLOW_PATCH, DENY, INVALID = 0, 1, 2, 3
 GEN_GPU, GEN_CPU_MILLI, GEN_MEM_BYTES, GEN_MIG = 0, 1, 2, 3

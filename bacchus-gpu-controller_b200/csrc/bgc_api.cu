@@ -202,6 +202,39 @@ int launch_k1_scatter(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const l
   }
 }
 
+// cluster-distributed table: CSIZE SMs share one direct-indexed table over distributed shared memory
+template <int R, bool VEC, int CSIZE>
+int launch_k1_cluster(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req, size_t n) {
+  ReqCols<R> cols;
+  for (int r = 0; r < R; ++r) cols.p[r] = req[r];
+  auto kern = k1_scatter_cluster<R, VEC, CSIZE>;
+  const uint32_t cap = (ctx->NS + CSIZE - 1) / CSIZE;
+  const size_t smem = k1_slot_bytes(ctx, R) * cap;
+  CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (CSIZE > 8) CU(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(1024);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = CSIZE;
+  attr.val.clusterDim.y = 1;
+  attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  int clusters = 0;
+  cfg.gridDim = dim3(CSIZE);
+  CU(cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg));
+  if (clusters < 1) return fail(ctx, BGC_E_CUDA, "no room for a %d-CTA cluster with %zu B of shared memory", CSIZE, smem);
+  cfg.gridDim = dim3((unsigned)(clusters * CSIZE));
+  CU(cudaLaunchKernelEx(&cfg, kern, ns, cols, n, ctx->rows, ctx->NS, cap, ctx->wide_mask));
+  ctx->head_stale = true;
+  ctx->tm.launches++;
+  CU(cudaGetLastError());
+  return BGC_OK;
+}
+
 template <int R>
 int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
                 size_t n, unsigned flags) {
@@ -220,6 +253,17 @@ int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long lo
   if (variant == BGC_K1_SMEM_HASH) {
     cap = 1;
     while ((size_t)cap * 2 * (k1_slot_bytes(ctx, R) + 4) <= kSmemBudget) cap *= 2;
+  }
+  if (variant == BGC_K1_CLUSTER8 || variant == BGC_K1_CLUSTER16) {
+    const int cs = variant == BGC_K1_CLUSTER8 ? 8 : 16;
+    if ((size_t)((ctx->NS + cs - 1) / cs) * k1_slot_bytes(ctx, R) > kSmemBudget)
+      return fail(ctx, BGC_E_BADARG, "namespace table does not fit a %d-CTA cluster", cs);
+    if (cs == 8) {
+      ctx->last_k1 = "scatter_cluster8_dsmem";
+      return vec ? launch_k1_cluster<R, true, 8>(ctx, st, ns, req, n) : launch_k1_cluster<R, false, 8>(ctx, st, ns, req, n);
+    }
+    ctx->last_k1 = "scatter_cluster16_dsmem";
+    return vec ? launch_k1_cluster<R, true, 16>(ctx, st, ns, req, n) : launch_k1_cluster<R, false, 16>(ctx, st, ns, req, n);
   }
   switch (variant) {
     case BGC_K1_GLOBAL:
@@ -509,7 +553,7 @@ int bgc_timings_get(bgc_ctx* ctx, bgc_timings* out) {
 
 int bgc_ctx_set_k1_variant(bgc_ctx* ctx, int variant) {
   if (!ctx) return BGC_E_BADARG;
-  NEED((variant & 0xFF) >= BGC_K1_AUTO && (variant & 0xFF) <= BGC_K1_SMEM_HASH, "unknown K1 variant");
+  NEED((variant & 0xFF) >= BGC_K1_AUTO && (variant & 0xFF) <= BGC_K1_CLUSTER16, "unknown K1 variant");
   ctx->k1_forced = variant & 0xFF;
   ctx->k1_shape = (variant >> 8) & 0xFF;  // bits 8..15: scatter launch shape (development knob)
   return BGC_OK;

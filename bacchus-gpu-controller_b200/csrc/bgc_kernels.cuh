@@ -216,6 +216,14 @@ static __global__ void k_rows_import_used(QuotaRow* rows, const long long* __res
 // modulo 2^64 under any interleaving.
 enum { SINK_GLOBAL = 0, SINK_DIRECT = 1, SINK_HASH = 2 };
 
+// slot hash of the claim-once table (murmur3 finaliser): namespace ids handed out by affine maps
+// collide systematically under a bare multiplicative hash
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+  return x;
+}
+__device__ __forceinline__ uint32_t slot_hash(uint32_t x, uint32_t shift) { return mix32(x) >> shift; }
+
 constexpr int kK1Tile = 128;            // pods per warp iteration
 constexpr uint32_t kHashEmpty = 0xFFFFFFFFu;
 
@@ -257,7 +265,7 @@ struct K1Sink {
       for (int r = 0; r < R; ++r)
         if (v[r]) smem_add(r, ns, ns, v[r]);
     } else {
-      const uint32_t s = (ns * 0x9E3779B1u) >> hash_shift;
+      const uint32_t s = slot_hash(ns, hash_shift);
       uint32_t k = s_key[s];
       if (k == kHashEmpty) {
         k = atomicCAS(&s_key[s], kHashEmpty, ns);
@@ -440,7 +448,7 @@ struct ScatterCtx {
   // slot of a namespace in the CTA-private table, or kHashEmpty when it has none (hash sink, cold)
   __device__ __forceinline__ uint32_t slot_of(uint32_t ns) const {
     if (SINK == SINK_DIRECT) return ns;
-    const uint32_t s = (ns * 0x9E3779B1u) >> hash_shift;
+    const uint32_t s = slot_hash(ns, hash_shift);
     const uint32_t kaddr = key_base + s * 4u;
     uint32_t k = lds_u32(kaddr);
     if (k == kHashEmpty) {
@@ -457,21 +465,38 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
   uint32_t slot[PODS];
   uint32_t old[R][PODS];
   if (SINK == SINK_HASH) {
-    // all key probes of the group are issued before any is examined (independent LDS in flight)
-    uint32_t s[PODS], key[PODS];
+    // Two candidate slots per namespace (top and bottom bits of one mixed word): with a single
+    // slot, two HOT namespaces landing on the same slot send the loser's millions of pods to one
+    // global address.  All key probes of the group are issued before any is examined.
+    uint32_t s1[PODS], s2[PODS], k1[PODS], k2[PODS];
 #pragma unroll
     for (int k = 0; k < PODS; ++k) {
-      s[k] = (ns[k] * 0x9E3779B1u) >> C.hash_shift;
-      key[k] = lds_u32(C.key_base + s[k] * 4u);
+      const uint32_t h = mix32(ns[k]);
+      s1[k] = h >> C.hash_shift;
+      s2[k] = h & (C.cap - 1u);
+      k1[k] = lds_u32(C.key_base + s1[k] * 4u);
+      k2[k] = lds_u32(C.key_base + s2[k] * 4u);
     }
 #pragma unroll
     for (int k = 0; k < PODS; ++k) {
-      uint32_t kk = key[k];
-      if (ns[k] < C.NS && kk == kHashEmpty) {  // claim-once: first namespace to arrive owns the slot
-        kk = atoms_cas_u32(C.key_base + s[k] * 4u, kHashEmpty, ns[k]);
-        if (kk == kHashEmpty) kk = ns[k];
+      uint32_t got = kHashEmpty;
+      if (ns[k] < C.NS) {
+        if (k1[k] == ns[k]) got = s1[k];
+        else if (k2[k] == ns[k]) got = s2[k];
+        else {
+          if (k1[k] == kHashEmpty) {  // claim-once: first namespace to arrive owns the slot
+            const uint32_t o = atoms_cas_u32(C.key_base + s1[k] * 4u, kHashEmpty, ns[k]);
+            if (o == kHashEmpty || o == ns[k]) got = s1[k];
+          }
+          if (got == kHashEmpty && k2[k] == kHashEmpty && s2[k] != s1[k]) {
+            // a namespace never holds two slots: only one thread per namespace can reach this CAS
+            // with s1 refused, because s1's refusal is permanent once its owner is somebody else
+            const uint32_t o = atoms_cas_u32(C.key_base + s2[k] * 4u, kHashEmpty, ns[k]);
+            if (o == kHashEmpty || o == ns[k]) got = s2[k];
+          }
+        }
       }
-      slot[k] = (ns[k] < C.NS && kk == ns[k]) ? s[k] : kHashEmpty;
+      slot[k] = got;
     }
   } else {
 #pragma unroll
@@ -576,6 +601,121 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRo
       const uint32_t ns = (SINK == SINK_HASH) ? k1_smem[words + sl] : sl;
       red_add_i64(&rows[ns].w[2 * r], (long long)v);
     }
+  }
+}
+
+// ------------------------------------------------------------------ K1, cluster-distributed table
+// Between ~14k and ~230k namespaces a CTA-private table no longer fits one SM, and the hash sink
+// pays a global red (L2 atomic, ~230 G/s chip-wide) for every cold namespace.  Thread-block
+// clusters give CSIZE neighbouring SMs one table between them: CTA `ns % CSIZE` of the cluster owns
+// namespace ns, and every CTA scatters its own slice of pods into whichever SM owns the slot with
+// shared::cluster atomics over distributed shared memory — no misses, no global traffic until the
+// single flush at the end.
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t cta_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ uint32_t atomc_add_u32(uint32_t caddr, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.shared::cluster.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(caddr), "r"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ void redc_add_u32(uint32_t caddr, uint32_t v) {
+  asm volatile("red.shared::cluster.add.u32 [%0], %1;" ::"r"(caddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+
+template <int R, int PODS, int CSIZE>
+__device__ __forceinline__ void scatter_pods_cluster(QuotaRow* rows, uint32_t NS, uint32_t wide_mask, uint32_t sbase,
+                                                     uint32_t cap, const uint32_t (&hi_slot)[R], const uint32_t (&ns)[PODS],
+                                                     const long long (&q)[R][PODS]) {
+  constexpr uint32_t kLog = CSIZE == 16 ? 4 : CSIZE == 8 ? 3 : CSIZE == 4 ? 2 : 1;
+  uint32_t base[PODS];   // shared::cluster address of slot 0 column 0 in the owning CTA
+  uint32_t local[PODS];
+  uint32_t old[R][PODS];
+#pragma unroll
+  for (int k = 0; k < PODS; ++k) {
+    local[k] = ns[k] >> kLog;
+    base[k] = mapa_u32(sbase, ns[k] & (CSIZE - 1));
+  }
+#pragma unroll
+  for (int k = 0; k < PODS; ++k) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t lo = (uint32_t)(unsigned long long)q[r][k];
+      old[r][k] = 0;
+      if (ns[k] < NS && lo) old[r][k] = atomc_add_u32(base[k] + ((uint32_t)r * cap + local[k]) * 4u, lo);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < PODS; ++k) {
+    if (ns[k] >= NS) continue;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const unsigned long long v = (unsigned long long)q[r][k];
+      const uint32_t lo = (uint32_t)v;
+      const uint32_t hi = (uint32_t)(v >> 32) + (uint32_t)(old[r][k] + lo < old[r][k]);
+      if (hi) {
+        if ((wide_mask >> r) & 1u) redc_add_u32(base[k] + ((R + hi_slot[r]) * cap + local[k]) * 4u, hi);
+        else red_add_i64(&rows[ns[k]].w[2 * r], (long long)((unsigned long long)hi << 32));
+      }
+    }
+  }
+}
+
+// cap = slots per CTA (>= ceil(NS / CSIZE)); launched with cluster dimension CSIZE
+template <int R, bool VEC, int CSIZE>
+__global__ void __launch_bounds__(1024, 1)
+k1_scatter_cluster(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRow* rows, uint32_t NS,
+                   uint32_t cap, uint32_t wide_mask) {
+  extern __shared__ __align__(16) uint32_t k1_smem[];
+  constexpr int THREADS = 1024;
+  constexpr uint32_t kLog = CSIZE == 16 ? 4 : CSIZE == 8 ? 3 : CSIZE == 4 ? 2 : 1;
+  const uint32_t nwide = __popc(wide_mask & ((1u << R) - 1u));
+  const uint32_t words = (R + nwide) * cap;
+  for (uint32_t i = threadIdx.x; i < words; i += THREADS) k1_smem[i] = 0;
+  uint32_t hi_slot[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) hi_slot[r] = __popc(wide_mask & ((1u << r) - 1u));
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(k1_smem);
+  cluster_sync_all();  // every table of the cluster is zeroed before anyone scatters into it
+
+  const size_t groups = VEC ? n / 4 : 0;
+  const size_t stride = (size_t)gridDim.x * THREADS;
+  for (size_t g = (size_t)blockIdx.x * THREADS + threadIdx.x; g < groups; g += stride) {
+    uint32_t ns[4];
+    long long q[R][4];
+    const size_t base = g * 4;
+    const uint4 v = ldg_nc_u32x4(ns_id + base);
+    ns[0] = v.x; ns[1] = v.y; ns[2] = v.z; ns[3] = v.w;
+#pragma unroll
+    for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
+    scatter_pods_cluster<R, 4, CSIZE>(rows, NS, wide_mask, sbase, cap, hi_slot, ns, q);
+  }
+  for (size_t i = groups * 4 + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
+    uint32_t ns[1] = {ns_id[i]};
+    long long q[R][1];
+#pragma unroll
+    for (int r = 0; r < R; ++r) q[r][0] = req.p[r][i];
+    scatter_pods_cluster<R, 1, CSIZE>(rows, NS, wide_mask, sbase, cap, hi_slot, ns, q);
+  }
+
+  cluster_sync_all();  // all remote atomics into this CTA's table have landed
+  const uint32_t me = cluster_ctarank();
+  for (uint32_t i = threadIdx.x; i < R * cap; i += THREADS) {
+    const uint32_t r = i / cap, sl = i - r * cap;
+    const uint32_t hi = ((wide_mask >> r) & 1u) ? k1_smem[(R + hi_slot[r]) * cap + sl] : 0u;
+    const unsigned long long v = ((unsigned long long)hi << 32) | k1_smem[i];
+    const uint32_t ns = (sl << kLog) | me;
+    if (v && ns < NS) red_add_i64(&rows[ns].w[2 * r], (long long)v);
   }
 }
 

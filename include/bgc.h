@@ -190,7 +190,7 @@ int bgc_usage_reduce_static_dev(const uint32_t *d_ns_id, const int64_t *const *d
 
 /* ---- tuning / introspection ---------------------------------------------------------------- */
 /* K1 kernel choice: 0 = automatic; otherwise force BGC_K1_* (tests exercise every variant) */
-enum { BGC_K1_AUTO = 0, BGC_K1_GLOBAL = 1, BGC_K1_SMEM_DIRECT = 2, BGC_K1_SMEM_HASH = 3 };
+enum { BGC_K1_AUTO = 0, BGC_K1_GLOBAL = 1, BGC_K1_SMEM_DIRECT = 2, BGC_K1_SMEM_HASH = 3, BGC_K1_CLUSTER8 = 4, BGC_K1_CLUSTER16 = 5 };
 int bgc_ctx_set_k1_variant(bgc_ctx *ctx, int variant);
 /* name of the K1 variant the last bgc_usage_reduce* launched */
 const char *bgc_last_k1_variant(const bgc_ctx *ctx);

@@ -295,3 +295,32 @@ def test_c3_scale_properties(engine, oracle, dist):
     assert acc == whole
     hist = engine.histogram_u8_dev(d_v)
     assert int(hist.sum()) == n and hist[0] > 0 and hist[1:8].sum() > 0
+
+
+@pytest.mark.parametrize("R", [1, 2, 3, 4])
+@pytest.mark.parametrize("variant,NS", [(4, 1), (4, 9), (4, 1000), (4, 70_000), (5, 17), (5, 70_000), (5, 150_000)])
+def test_k1_cluster_distributed_table(bgc, engine, oracle, R, variant, NS):
+    """K1 with the table spread over a thread-block cluster's shared memory (DSMEM atomics)."""
+    rng = np.random.default_rng(R * 31 + NS + variant)
+    for n in (1, 4099, 300_007):
+        ns = rng.integers(0, NS, n, dtype=np.uint32)
+        req = [rng.integers(-2**63, 2**63 - 1, n, dtype=np.int64) for _ in range(R)]
+        if n > 50:
+            ns[3] = NS
+            ns[n // 2] = 0xFFFFFFFF
+            req[0][::3] = rng.integers(0, 9, req[0][::3].shape[0])
+        want = oracle.usage_reduce(ns, req, NS, threads=4)
+        engine.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
+        engine.set_k1_variant(variant)
+        got = engine.usage_reduce(ns, req)
+        assert np.array_equal(got, want), (engine.last_k1_variant(), n)
+    assert "cluster" in engine.last_k1_variant()
+
+
+def test_k1_cluster_rejects_tables_that_do_not_fit(bgc, engine):
+    R, NS = 3, 2_000_000
+    engine.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
+    engine.set_k1_variant(bgc.K1_CLUSTER16)
+    with pytest.raises(bgc.BgcError) as e:
+        engine.usage_reduce(np.zeros(8, np.uint32), [np.zeros(8, np.int64)] * R)
+    assert e.value.code == bgc.E_BADARG

@@ -42,11 +42,11 @@ def main():
     n = args.pods
     eng = bgc.Engine(0)
     eng.use_torch_stream()
-    names = {0: "auto", 1: "global_red", 2: "smem_direct", 3: "smem_hash"}
+    names = {0: "auto", 1: "global_red", 2: "smem_direct", 3: "smem_hash", 4: "cluster8", 5: "cluster16"}
     cases = [  # (NS, R, dist, s, grouped)
         (10_000, 3, 1, 1.1, 0), (10_000, 3, 0, 0, 0), (10_000, 3, 1, 1.1, 1), (10_000, 2, 0, 0, 0),
         (100, 3, 1, 1.1, 0), (1_000_000, 3, 1, 1.1, 0), (1_000_000, 3, 0, 0, 0), (10_000, 3, 1, 1.5, 0),
-        (125_000, 3, 1, 1.1, 0), (500_000, 3, 1, 1.1, 0), (20_000, 3, 1, 1.1, 0), (10_000, 4, 1, 1.1, 0), (10_000, 1, 1, 1.1, 0),
+        (125_000, 3, 1, 1.1, 0), (500_000, 3, 1, 1.1, 0), (20_000, 3, 1, 1.1, 0), (50_000, 3, 0, 0, 0), (125_000, 3, 0, 0, 0), (200_000, 3, 1, 1.1, 0), (10_000, 4, 1, 1.1, 0), (10_000, 1, 1, 1.1, 0),
     ]
     if args.cases != "all":
         cases = [c for c in cases if str(c[0]) in args.cases.split(",")]
@@ -59,7 +59,7 @@ def main():
         eng.synth_pods_dev(bgc.synth_params(0xB2000003, 0, NS, dist, grouped, n, a, b, d_cdf, KINDS[R]), 0, n, ns, req)
         eng.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
         ref = None
-        todo = [1, 2, 3] if grouped else [1] + [v | (sh << 8) for v in (2, 3) for sh in (0, 1, 2, 3)]
+        todo = [1, 2, 3] if grouped else [1] + [v | (sh << 8) for v in (2, 3) for sh in (0, 1)] + [4, 5]
         if not grouped and (dist and NS > 100):
             todo = todo[1:]          # global reds on a Zipf head take tens of ms: measured once, skip
         for variant in todo:
@@ -68,7 +68,7 @@ def main():
             try:
                 ms = timeit(lambda: eng.usage_reduce_dev(ns, req, flags))
             except Exception as e:  # noqa: BLE001
-                print(json.dumps({"case": [NS, R, dist, s, grouped], "variant": names[variant], "error": str(e)}), flush=True)
+                print(json.dumps({"case": [NS, R, dist, s, grouped], "variant": names.get(variant & 0xFF), "error": str(e)[:80]}), flush=True)
                 continue
             used = eng.usage_get()
             if ref is None:
