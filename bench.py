@@ -34,8 +34,9 @@ WORKLOADS = {
     "c3": (100_000_000, 10_000, 3, 1, 1.1, "C3: 1e8 pods, Zipf(1.1) over 1e4 namespaces, R=3 (gpu,cpu,memory), arrival order"),
     "c2": (1_048_576, 10_000, 2, 0, 0.0, "C2: 2^20 pods x 1e4 namespaces, uniform, R=2 (gpu,cpu)"),
     "c5": (125_000_000, 125_000, 3, 1, 1.1, "C5 shard: 1.25e8 pods x 1.25e5 namespaces per GPU (1e9 x 1e6 over 8), Zipf(1.1), R=3"),
+    "c5full": (1_000_000_000, 1_000_000, 3, 1, 1.1, "C5 on one GPU: 1e9 pods x 1e6 namespaces, Zipf(1.1), R=3 (the 1-GPU reference point; 57 GB of inputs)"),
 }
-SEED = {"c3": 0xB2000003, "c2": 0xB2000002, "c5": 0xB2000005}
+SEED = {"c3": 0xB2000003, "c2": 0xB2000002, "c5": 0xB2000005, "c5full": 0xB2000005}
 
 
 def ncu_traffic(workload: str, kernel: str, n: int, default_n: int):
@@ -201,6 +202,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--k1", type=int, default=0, help="force a K1 variant (BGC_K1_*)")
     ap.add_argument("--grouped", action="store_true", help="running set grouped by namespace (segmented path)")
+    ap.add_argument("--verify-full", action="store_true",
+                    help="after timing, stream the whole running set through the CPU oracle in chunks and compare the full usage table")
     ap.add_argument("--sharding", default="namespace", choices=["namespace", "index"],
                     help="multi-GPU: independent namespace-hash shards (no collective, default) or pods sharded by index "
                          "with one int64 all-reduce of the usage table per step (SURVEY.md §8(e)(b), row N5)")
@@ -321,6 +324,7 @@ def main():
     import oracle
     oracle.build()
     verified = None
+    verified_full = False
     if rank == 0:
         cnt = min(n, 1 << 20)
         p1 = oracle.gen_params(seed, 1, NS, dist_kind, 0, n_total, a, b, cdf, KINDS[R])
@@ -328,10 +332,17 @@ def main():
         used_now = eng.usage_get()
         v = oracle.quota_eval(cns, creq, None, NS, used_now, hard, hard_mask, 0b110 & ((1 << R) - 1), threads=8)
         verified = bool(np.array_equal(used_now, used0)) and oracle.checksum_u8(v, n - cnt) == eng.checksum_u8_dev(d_verdict[n - cnt:], n - cnt)
-        if n_total <= (1 << 25):
+        if n_total <= (1 << 25) or args.verify_full:
+            # the oracle regenerates the same counter-based stream in chunks (no 28 GB host buffer)
             p0 = oracle.gen_params(seed, 0, NS, dist_kind, int(args.grouped), n_total, a, b, cdf, KINDS[R])
-            rns, rreq, _ = oracle.gen_fill(p0, 0, n_total, threads=8)
-            verified = verified and bool(np.array_equal(oracle.usage_reduce(rns, rreq, NS, threads=8), used_now))
+            acc = np.zeros((R, NS), np.int64)
+            cores_v = os.cpu_count() or 1
+            for lo in range(0, n_total, 1 << 24):
+                rns, rreq, _ = oracle.gen_fill(p0, lo, min(1 << 24, n_total - lo), threads=cores_v)
+                with np.errstate(over="ignore"):
+                    acc += oracle.usage_reduce(rns, rreq, NS, threads=cores_v)
+            verified = verified and bool(np.array_equal(acc, used_now))
+            verified_full = True
 
     # ---- end to end through the host-pointer entry points (pinned host buffers)
     e2e = None
@@ -408,6 +419,9 @@ def main():
                          "k2": {"ms": k2_ms, "achieved": k2_bytes / (k2_ms * 1e-3) / 1e9, "frac": k2_bytes / (k2_ms * 1e-3) / 1e9 / peak,
                                 "algorithmic_bytes_per_pod": 4 + 8 * R + 1}},
             "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches), "verified_vs_oracle": verified,
+            "verified_scope": ("full usage table (oracle streamed over all %d running pods) + verdict checksum of the last 2^20 candidates" % n_total) if verified_full
+                              else "usage table stable across steps + verdict checksum of the last 2^20 candidates vs oracle",
+            "crossover": {"see": "profiles/r01_crossover_c4.md", "gpu_wins_from_pinned_host_above_pods": 65536, "from_pageable_host": "never (measured up to 4194304)"},
         }
         print(json.dumps(line), flush=True)
     if world > 1:
