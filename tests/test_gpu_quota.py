@@ -324,3 +324,39 @@ def test_k1_cluster_rejects_tables_that_do_not_fit(bgc, engine):
     with pytest.raises(bgc.BgcError) as e:
         engine.usage_reduce(np.zeros(8, np.uint32), [np.zeros(8, np.int64)] * R)
     assert e.value.code == bgc.E_BADARG
+
+
+def test_two_contexts_in_two_threads_do_not_interfere(bgc, oracle):
+    """One bgc_ctx per thread (the reference handler is stateless per request, admission.rs:145-147):
+    two engines driven concurrently from two host threads must each produce their own exact result."""
+    import threading
+    R, NS, n = 3, 4000, 1_500_000
+    rng = np.random.default_rng(99)
+    cases = []
+    for t in range(2):
+        ns = rng.integers(0, NS, n, dtype=np.uint32)
+        req = [rng.integers(0, 1 << 34, n, dtype=np.int64) for _ in range(R)]
+        used = oracle.usage_reduce(ns, req, NS, threads=4)
+        hard, hm = make_hard(used, 40 + t)
+        cases.append((ns, req, used, hard, hm, oracle.quota_eval(ns, req, None, NS, used, hard, hm, 6, threads=4)))
+    errors = []
+
+    def work(t):
+        try:
+            ns, req, used, hard, hm, want = cases[t]
+            eng = bgc.Engine(0)
+            eng.quota_table_set(hard, hm, UNITS[R])
+            for _ in range(5):
+                assert np.array_equal(eng.usage_reduce(ns, req), used)
+                assert np.array_equal(eng.quota_eval(ns, req), want)
+                assert np.array_equal(eng.quota_eval(ns[:1000], [c[:1000] for c in req]), want[:1000])   # latency path
+            eng.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append((t, repr(e)))
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(2)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
