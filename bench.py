@@ -69,7 +69,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.device}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.device}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -288,15 +288,20 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # clocks are sampled from just before the warm-up to just after the timed region: the timed
+    # region alone (K steps of ~1 ms) is shorter than nvidia-smi's sampling period
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    t_w = time.perf_counter()
     for _ in range(max(args.warmup, 3)):
+        step()
+    while time.perf_counter() - t_w < 0.5:      # keep the GPU under the same load for a few samples
         step()
     barrier()
     launches0 = eng.timings()["launches"]
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.25)
     barrier()
     t_all0 = torch.cuda.Event(enable_timing=True); t_all1 = torch.cuda.Event(enable_timing=True)
     t_all0.record()
