@@ -46,9 +46,9 @@ struct bgc_ctx {
   cudaStream_t own_stream = nullptr, stream = nullptr, h2d_stream = nullptr, d2h_stream = nullptr;
   std::string err;
   // quota table
-  QuotaRow* rows = nullptr;
+  long long* d_used = nullptr;       // [R][NS]; K1 accumulates here
+  long long* d_hard = nullptr;       // [R][NS]
   uint8_t* d_hard_mask = nullptr;
-  long long* d_table_tmp = nullptr;  // [R][NS] staging for import/export
   uint32_t NS = 0;
   int R = 0;
   uint32_t compute_mask = 0;
@@ -168,7 +168,7 @@ int launch_k1_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
   size_t chunk_tiles = tiles / ((size_t)grid * warps_per_block * 4);
   if (chunk_tiles < 1) chunk_tiles = 1;
   if (chunk_tiles > 32) chunk_tiles = 32;
-  kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->rows, ctx->NS, cap, (uint32_t)chunk_tiles, ctx->wide_mask);
+  kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->d_used, ctx->NS, cap, (uint32_t)chunk_tiles, ctx->wide_mask);
   ctx->head_stale = true;
   ctx->tm.launches++;
   CU(cudaGetLastError());
@@ -188,7 +188,7 @@ int launch_k1_scatter(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const l
     int grid = ctx->sm_count;
     if ((size_t)grid * threads > groups) grid = (int)((groups + threads - 1) / threads);
     if (grid < 1) grid = 1;
-    kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->rows, ctx->NS, cap, ctx->wide_mask);
+    kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->d_used, ctx->NS, cap, ctx->wide_mask);
     ctx->head_stale = true;
     ctx->tm.launches++;
     CU(cudaGetLastError());
@@ -228,7 +228,7 @@ int launch_k1_cluster(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const l
   CU(cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg));
   if (clusters < 1) return fail(ctx, BGC_E_CUDA, "no room for a %d-CTA cluster with %zu B of shared memory", CSIZE, smem);
   cfg.gridDim = dim3((unsigned)(clusters * CSIZE));
-  CU(cudaLaunchKernelEx(&cfg, kern, ns, cols, n, ctx->rows, ctx->NS, cap, ctx->wide_mask));
+  CU(cudaLaunchKernelEx(&cfg, kern, ns, cols, n, ctx->d_used, ctx->NS, cap, ctx->wide_mask));
   ctx->head_stale = true;
   ctx->tm.launches++;
   CU(cudaGetLastError());
@@ -313,7 +313,7 @@ int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
   }
   if (ctx->head_stale) {  // usage or limits changed since the compact table was built
     const int g = grid_for((size_t)ctx->NS * 4, 256, ctx->sm_count * 4);
-    k_build_headroom<<<g, 256, 0, st>>>(ctx->rows, ctx->d_hard_mask, ctx->head, ctx->NS, R);
+    k_build_headroom<<<g, 256, 0, st>>>(ctx->d_used, ctx->d_hard, ctx->d_hard_mask, ctx->head, ctx->NS, R);
     ctx->tm.launches++;
     CU(cudaGetLastError());
     ctx->head_stale = false;
@@ -350,18 +350,13 @@ int launch_k2(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long
 
 int clear_used(bgc_ctx* ctx, cudaStream_t st) {
   ctx->head_stale = true;
-  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
-  k_rows_clear_used<<<grid, 256, 0, st>>>(ctx->rows, ctx->NS, ctx->R);
-  ctx->tm.launches++;
-  CU(cudaGetLastError());
+  CU(cudaMemsetAsync(ctx->d_used, 0, (size_t)ctx->NS * ctx->R * 8, st));
   return BGC_OK;
 }
 
+// the usage table already has the [R][NS] layout of the ABI: a plain device-to-device copy
 int export_used(bgc_ctx* ctx, cudaStream_t st, long long* d_out) {
-  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
-  k_rows_export_used<<<grid, 256, 0, st>>>(ctx->rows, d_out, ctx->NS, ctx->R);
-  ctx->tm.launches++;
-  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(d_out, ctx->d_used, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyDeviceToDevice, st));
   return BGC_OK;
 }
 
@@ -506,10 +501,10 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
     if (s.free_ev) cudaEventDestroy(s.free_ev);
   }
   for (auto e : ctx->ev_pool) cudaEventDestroy(e);
-  cudaFree(ctx->rows);
+  cudaFree(ctx->d_used);
+  cudaFree(ctx->d_hard);
   cudaFree(ctx->head);
   cudaFree(ctx->d_hard_mask);
-  cudaFree(ctx->d_table_tmp);
   cudaFree(ctx->d_scratch);
   cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order);
   cudaFree(ctx->g_seg); cudaFree(ctx->g_temp); cudaFree(ctx->g_mask);
@@ -648,15 +643,15 @@ int bgc_quota_table_set(bgc_ctx* ctx, uint32_t ns_count, uint32_t R, const int64
   CU(cudaSetDevice(ctx->device));
   CU(cudaDeviceSynchronize());
   if (ns_count != ctx->NS || (int)R != ctx->R) {
-    cudaFree(ctx->rows); ctx->rows = nullptr;
+    cudaFree(ctx->d_used); ctx->d_used = nullptr;
+    cudaFree(ctx->d_hard); ctx->d_hard = nullptr;
     cudaFree(ctx->head); ctx->head = nullptr;
     cudaFree(ctx->d_hard_mask); ctx->d_hard_mask = nullptr;
-    cudaFree(ctx->d_table_tmp); ctx->d_table_tmp = nullptr;
     ctx->NS = 0; ctx->R = 0;
-    CU(cudaMalloc(&ctx->rows, (size_t)ns_count * sizeof(QuotaRow)));
+    CU(cudaMalloc(&ctx->d_used, (size_t)ns_count * R * 8));
+    CU(cudaMalloc(&ctx->d_hard, (size_t)ns_count * R * 8));
     CU(cudaMalloc(&ctx->head, (size_t)ns_count * sizeof(HeadRow)));
     CU(cudaMalloc(&ctx->d_hard_mask, ns_count));
-    CU(cudaMalloc(&ctx->d_table_tmp, (size_t)ns_count * R * 8));
   }
   ctx->NS = ns_count;
   ctx->R = (int)R;
@@ -668,41 +663,32 @@ int bgc_quota_table_set(bgc_ctx* ctx, uint32_t ns_count, uint32_t R, const int64
     if (unit[r] != BGC_UNIT_COUNT) ctx->compute_mask |= 1u << r;
     if (unit[r] == BGC_UNIT_BYTES) ctx->wide_mask |= 1u << r;
   }
-  CU(cudaMemcpyAsync(ctx->d_table_tmp, hard, (size_t)ns_count * R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
+  CU(cudaMemcpyAsync(ctx->d_hard, hard, (size_t)ns_count * R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
   CU(cudaMemcpyAsync(ctx->d_hard_mask, hard_mask, ns_count, cudaMemcpyHostToDevice, ctx->own_stream));
-  const int grid = grid_for((size_t)ns_count * 8, 256, ctx->sm_count * 4);
-  k_rows_set_hard<<<grid, 256, 0, ctx->own_stream>>>(ctx->rows, ctx->d_table_tmp, ctx->d_hard_mask, ns_count, (int)R);
-  ctx->tm.launches++;
-  CU(cudaGetLastError());
+  CU(cudaMemsetAsync(ctx->d_used, 0, (size_t)ns_count * R * 8, ctx->own_stream));
   CU(cudaStreamSynchronize(ctx->own_stream));
   return BGC_OK;
 }
 
 int bgc_usage_get(bgc_ctx* ctx, int64_t* used_out) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(used_out, "null output");
   CU(cudaSetDevice(ctx->device));
   CU(cudaStreamSynchronize(ctx->stream));
-  int rc = export_used(ctx, ctx->own_stream, ctx->d_table_tmp);
-  if (rc) return rc;
-  CU(cudaMemcpyAsync(used_out, ctx->d_table_tmp, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyDeviceToHost, ctx->own_stream));
+  CU(cudaMemcpyAsync(used_out, ctx->d_used, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyDeviceToHost, ctx->own_stream));
   CU(cudaStreamSynchronize(ctx->own_stream));
   return BGC_OK;
 }
 
 int bgc_usage_set(bgc_ctx* ctx, const int64_t* used) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(used, "null input");
   CU(cudaSetDevice(ctx->device));
   CU(cudaStreamSynchronize(ctx->stream));
-  CU(cudaMemcpyAsync(ctx->d_table_tmp, used, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
-  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
-  k_rows_import_used<<<grid, 256, 0, ctx->own_stream>>>(ctx->rows, ctx->d_table_tmp, ctx->NS, ctx->R);
+  CU(cudaMemcpyAsync(ctx->d_used, used, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
   ctx->head_stale = true;
-  ctx->tm.launches++;
-  CU(cudaGetLastError());
   CU(cudaStreamSynchronize(ctx->own_stream));
   return BGC_OK;
 }
@@ -711,7 +697,7 @@ int bgc_usage_set(bgc_ctx* ctx, const int64_t* used) {
 // index-sharded multi-GPU variant all-reduces between K1 and K2)
 int bgc_usage_get_dev(bgc_ctx* ctx, int64_t* d_used_out) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(d_used_out, "null output");
   CU(cudaSetDevice(ctx->device));
   return export_used(ctx, ctx->stream, reinterpret_cast<long long*>(d_used_out));
@@ -719,14 +705,11 @@ int bgc_usage_get_dev(bgc_ctx* ctx, int64_t* d_used_out) {
 
 int bgc_usage_set_dev(bgc_ctx* ctx, const int64_t* d_used) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(d_used, "null input");
   CU(cudaSetDevice(ctx->device));
-  const int grid = grid_for((size_t)ctx->NS * ctx->R, 256, ctx->sm_count * 4);
-  k_rows_import_used<<<grid, 256, 0, ctx->stream>>>(ctx->rows, reinterpret_cast<const long long*>(d_used), ctx->NS, ctx->R);
+  CU(cudaMemcpyAsync(ctx->d_used, d_used, (size_t)ctx->NS * ctx->R * 8, cudaMemcpyDeviceToDevice, ctx->stream));
   ctx->head_stale = true;
-  ctx->tm.launches++;
-  CU(cudaGetLastError());
   return BGC_OK;
 }
 
@@ -734,7 +717,7 @@ int bgc_usage_set_dev(bgc_ctx* ctx, const int64_t* d_used) {
 int bgc_usage_reduce_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req, size_t n,
                          unsigned flags, int64_t* d_used_out) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (d_ns_id && d_req), "null column pointer");
   const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
   for (int r = 0; r < ctx->R && n; ++r) {
@@ -752,7 +735,7 @@ int bgc_usage_reduce_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* c
 int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req, size_t n,
                      unsigned flags, int64_t* used_out) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (ns_id && req), "null column pointer");
   const int R = ctx->R;
   for (int r = 0; r < R && n; ++r) NEED(req[r], "null request column");
@@ -796,9 +779,8 @@ int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
   if (used_out) {
     cudaEvent_t e = next_event(ctx), f = next_event(ctx);
     if (!f) return fail(ctx, BGC_E_CUDA, "event pool exhausted");
-    if ((rc = export_used(ctx, ctx->own_stream, ctx->d_table_tmp))) return rc;
     CU(cudaEventRecord(e, ctx->own_stream));
-    CU(cudaMemcpyAsync(used_out, ctx->d_table_tmp, (size_t)ctx->NS * R * 8, cudaMemcpyDeviceToHost, ctx->own_stream));
+    CU(cudaMemcpyAsync(used_out, ctx->d_used, (size_t)ctx->NS * R * 8, cudaMemcpyDeviceToHost, ctx->own_stream));
     CU(cudaEventRecord(f, ctx->own_stream));
     sp.d2h.push_back(e); sp.d2h.push_back(f);
   }
@@ -810,7 +792,7 @@ int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
 int bgc_quota_eval_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
                        const uint8_t* d_req_mask, size_t n, uint8_t* d_verdict) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (d_ns_id && d_req && d_verdict), "null column pointer");
   const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
   for (int r = 0; r < ctx->R && n; ++r) {
@@ -824,7 +806,7 @@ int bgc_quota_eval_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* con
 int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
                    const uint8_t* req_mask, size_t n, uint8_t* verdict) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (ns_id && req && verdict), "null column pointer");
   const int R = ctx->R;
   for (int r = 0; r < R && n; ++r) NEED(req[r], "null request column");
@@ -923,15 +905,15 @@ int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const long long* const* req_in, c
   const size_t ring = (size_t)kGreedyDepth * R * kGreedyTeam * 8;
   if (mask) {
     CU(cudaFuncSetAttribute(k3_admit_greedy_team<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
-    k3_admit_greedy<R, true><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows, ctx->d_hard_mask,
+    k3_admit_greedy<R, true><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
                                                    ctx->NS, ctx->compute_mask, verdict, kGreedyTeamMin);
-    k3_admit_greedy_team<R, true><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows,
+    k3_admit_greedy_team<R, true><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard,
                                                                        ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
   } else {
     CU(cudaFuncSetAttribute(k3_admit_greedy_team<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
-    k3_admit_greedy<R, false><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows, ctx->d_hard_mask,
+    k3_admit_greedy<R, false><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
                                                     ctx->NS, ctx->compute_mask, verdict, kGreedyTeamMin);
-    k3_admit_greedy_team<R, false><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->rows,
+    k3_admit_greedy_team<R, false><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard,
                                                                         ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
   }
   ctx->tm.launches += 2;
@@ -981,7 +963,7 @@ int ensure_greedy_buffers(bgc_ctx* ctx, size_t n, int end_bit) {
 extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
                                     const uint8_t* d_req_mask, size_t n, uint8_t* d_verdict) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (d_ns_id && d_req && d_verdict), "null column pointer");
   NEED(n < (size_t(1) << 31), "greedy admission handles fewer than 2^31 pods per call");
   const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
@@ -1022,7 +1004,7 @@ extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const
 extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
                                 const uint8_t* req_mask, size_t n, uint8_t* verdict) {
   if (!ctx) return BGC_E_BADARG;
-  if (!ctx->rows) return fail(ctx, BGC_E_STATE, "quota table not set");
+  if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (ns_id && req && verdict), "null column pointer");
   const int R = ctx->R;
   for (int r = 0; r < R && n; ++r) NEED(req[r], "null request column");

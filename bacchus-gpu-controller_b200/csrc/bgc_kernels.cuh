@@ -16,12 +16,12 @@ namespace bgc {
 constexpr int kMaxR = 4;
 constexpr uint32_t kBadNs = 0xFFFFFFFFu;
 
-// One namespace's quota state, one 64-byte line: w[2r] = used[r], w[2r+1] = hard[r]
-// (w[7] = hard_mask for R <= 3).  K1 accumulates into it; K2 reads the compact HeadRow derived
-// from it (see k_build_headroom).
-struct __align__(64) QuotaRow {
-  long long w[8];
-};
+// Quota state: two [R][NS] int64 tables, `used` (K1 accumulates into it with global reds; the L2
+// atomic rate does not depend on the layout, see tools/micro/red_bench.cu) and `hard`, plus
+// hard_mask[NS].  K2 reads the compact per-namespace HeadRow derived from them (k_build_headroom).
+__device__ __forceinline__ long long* used_at(long long* used, uint32_t NS, int r, uint32_t ns) {
+  return used + (size_t)r * NS + ns;
+}
 
 template <int R>
 struct ReqCols {
@@ -46,7 +46,7 @@ __device__ __forceinline__ void ldg_nc_i64x4(const long long* p, long long (&v)[
                : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
                : "l"(p));
 }
-// 256-bit gather of half a QuotaRow; table lines are re-used, so let them allocate in L1/L2
+// 256-bit gather of one HeadRow; table lines are re-used, so let them allocate in L1/L2
 __device__ __forceinline__ void ldg_row_half(const long long* p, long long (&v)[4]) {
   asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];"
                : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
@@ -151,52 +151,6 @@ k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flag
   }
 }
 
-// ------------------------------------------------------------------ quota table maintenance
-// grid-stride over NS*R
-static __global__ void k_rows_set_hard(QuotaRow* rows, const long long* __restrict__ hard,
-                                const uint8_t* __restrict__ hard_mask, uint32_t NS, int R) {
-  const size_t total = (size_t)NS * 8;
-  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (size_t)gridDim.x * blockDim.x) {
-    const uint32_t ns = (uint32_t)(t >> 3), k = (uint32_t)(t & 7);
-    const int r = k >> 1;
-    long long v = 0;
-    if ((k & 1) && r < R) v = hard[(size_t)r * NS + ns];
-    if (k == 7 && R <= 3) v = hard_mask[ns];
-    rows[ns].w[k] = v;
-  }
-}
-static __global__ void k_rows_clear_used(QuotaRow* rows, uint32_t NS, int R) {
-  const size_t total = (size_t)NS * R;
-  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (size_t)gridDim.x * blockDim.x) {
-    const uint32_t ns = (uint32_t)(t / R);
-    const int r = (int)(t % R);
-    rows[ns].w[2 * r] = 0;
-  }
-}
-// used_out[r][ns] <- rows ; or rows <- used_in (set)
-static __global__ void k_rows_export_used(const QuotaRow* __restrict__ rows, long long* used_out,
-                                   uint32_t NS, int R) {
-  const size_t total = (size_t)NS * R;
-  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (size_t)gridDim.x * blockDim.x) {
-    const int r = (int)(t / NS);
-    const uint32_t ns = (uint32_t)(t % NS);
-    used_out[t] = rows[ns].w[2 * r];
-  }
-}
-static __global__ void k_rows_import_used(QuotaRow* rows, const long long* __restrict__ used_in,
-                                   uint32_t NS, int R) {
-  const size_t total = (size_t)NS * R;
-  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (size_t)gridDim.x * blockDim.x) {
-    const int r = (int)(t / NS);
-    const uint32_t ns = (uint32_t)(t % NS);
-    rows[ns].w[2 * r] = used_in[t];
-  }
-}
-
 // ------------------------------------------------------------------ K1 usage_reduce
 // One warp owns a contiguous chunk of pods and walks it in tiles of 128 (4 consecutive pods per
 // lane, so every warp-level load is a fully coalesced 512 B / 1 KB request).  Runs of equal
@@ -206,7 +160,7 @@ static __global__ void k_rows_import_used(QuotaRow* rows, const long long* __res
 //   3. across tiles with a carry held by lane 0,
 // so pods grouped by namespace cost ~R atomics per 4096 pods, while fully shuffled input
 // degenerates to R updates per pod.  Updates go to one of three sinks:
-//   SINK_GLOBAL : red.global.add.u64 straight into the QuotaRow table (L2 atomics);
+//   SINK_GLOBAL : red.global.add.u64 straight into the global usage table (L2 atomics);
 //   SINK_DIRECT : CTA-private shared-memory table indexed by ns (NS*R*8 B must fit), flushed once;
 //   SINK_HASH   : CTA-private shared-memory table of S claim-once slots (hot namespaces claim
 //                 a slot first), cold namespaces fall through to global reds.
@@ -229,7 +183,7 @@ constexpr uint32_t kHashEmpty = 0xFFFFFFFFu;
 
 template <int R, int SINK>
 struct K1Sink {
-  QuotaRow* rows;
+  long long* used;
   uint32_t NS;
   uint32_t* s_lo;   // [R][cap]      low words of every column
   uint32_t* s_hi;   // [nwide][cap]  high words of the wide columns only
@@ -250,7 +204,7 @@ struct K1Sink {
     }
     if (hi) {
       if ((wide_mask >> r) & 1u) atomicAdd(&s_hi[hi_slot(r) * cap + idx], hi);
-      else red_add_i64(&rows[ns].w[2 * r], (long long)((unsigned long long)hi << 32));
+      else red_add_i64(used_at(used, NS, r, ns), (long long)((unsigned long long)hi << 32));
     }
   }
 
@@ -259,7 +213,7 @@ struct K1Sink {
     if (SINK == SINK_GLOBAL) {
 #pragma unroll
       for (int r = 0; r < R; ++r)
-        if (v[r]) red_add_i64(&rows[ns].w[2 * r], v[r]);
+        if (v[r]) red_add_i64(used_at(used, NS, r, ns), v[r]);
     } else if (SINK == SINK_DIRECT) {
 #pragma unroll
       for (int r = 0; r < R; ++r)
@@ -278,7 +232,7 @@ struct K1Sink {
       } else {
 #pragma unroll
         for (int r = 0; r < R; ++r)
-          if (v[r]) red_add_i64(&rows[ns].w[2 * r], v[r]);
+          if (v[r]) red_add_i64(used_at(used, NS, r, ns), v[r]);
       }
     }
   }
@@ -286,12 +240,12 @@ struct K1Sink {
 
 template <int R, int SINK, bool VEC>
 __global__ void __launch_bounds__(SINK == SINK_GLOBAL ? 512 : 1024, 1)
-k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRow* rows,
+k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long long* used,
                 uint32_t NS, uint32_t cap, uint32_t chunk_tiles, uint32_t wide_mask) {
   extern __shared__ __align__(16) uint32_t k1_smem[];
   K1Sink<R, SINK> sink;
   const uint32_t nwide = __popc(wide_mask & ((1u << R) - 1u));
-  sink.rows = rows;
+  sink.used = used;
   sink.NS = NS;
   sink.cap = cap;
   sink.wide_mask = wide_mask;
@@ -405,7 +359,7 @@ k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, Qu
       const unsigned long long v = ((unsigned long long)hi << 32) | sink.s_lo[i];
       if (v) {
         const uint32_t ns = (SINK == SINK_HASH) ? sink.s_key[s] : s;
-        red_add_i64(&rows[ns].w[2 * r], (long long)v);
+        red_add_i64(used_at(used, NS, r, ns), (long long)v);
       }
     }
   }
@@ -439,7 +393,7 @@ __device__ __forceinline__ uint32_t atoms_cas_u32(uint32_t saddr, uint32_t cmp, 
 
 template <int R, int SINK>
 struct ScatterCtx {
-  QuotaRow* rows;
+  long long* used;
   uint32_t NS, cap, wide_mask, hash_shift;
   uint32_t lo_base[R];  // shared-window byte address of column r's low words
   uint32_t hi_base[R];  // ... of its high words (wide columns only)
@@ -520,14 +474,14 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
     for (int r = 0; r < R; ++r) {
       const unsigned long long v = (unsigned long long)q[r][k];
       if (slot[k] == kHashEmpty) {  // cold namespace of the hash sink: straight to the global table
-        if (v) red_add_i64(&C.rows[ns[k]].w[2 * r], (long long)v);
+        if (v) red_add_i64(used_at(C.used, C.NS, r, ns[k]), (long long)v);
         continue;
       }
       const uint32_t lo = (uint32_t)v;
       const uint32_t hi = (uint32_t)(v >> 32) + (uint32_t)(old[r][k] + lo < old[r][k]);
       if (hi) {
         if ((C.wide_mask >> r) & 1u) reds_add_u32(C.hi_base[r] + slot[k] * 4u, hi);
-        else red_add_i64(&C.rows[ns[k]].w[2 * r], (long long)((unsigned long long)hi << 32));
+        else red_add_i64(used_at(C.used, C.NS, r, ns[k]), (long long)((unsigned long long)hi << 32));
       }
     }
   }
@@ -535,7 +489,7 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
 
 template <int R, int SINK, bool VEC, int THREADS, int U>
 __global__ void __launch_bounds__(THREADS, 1)
-k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRow* rows, uint32_t NS,
+k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long long* used, uint32_t NS,
            uint32_t cap, uint32_t wide_mask) {
   extern __shared__ __align__(16) uint32_t k1_smem[];
   const uint32_t nwide = __popc(wide_mask & ((1u << R) - 1u));
@@ -544,7 +498,7 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRo
   if (SINK == SINK_HASH)
     for (uint32_t i = threadIdx.x; i < cap; i += THREADS) k1_smem[words + i] = kHashEmpty;
   ScatterCtx<R, SINK> C;
-  C.rows = rows; C.NS = NS; C.cap = cap; C.wide_mask = wide_mask;
+  C.used = used; C.NS = NS; C.cap = cap; C.wide_mask = wide_mask;
   C.hash_shift = 32 - (31 - __clz(cap | 1));
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(k1_smem);
 #pragma unroll
@@ -599,7 +553,7 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRo
     const unsigned long long v = ((unsigned long long)hi << 32) | k1_smem[i];
     if (v) {
       const uint32_t ns = (SINK == SINK_HASH) ? k1_smem[words + sl] : sl;
-      red_add_i64(&rows[ns].w[2 * r], (long long)v);
+      red_add_i64(used_at(used, NS, r, ns), (long long)v);
     }
   }
 }
@@ -634,7 +588,7 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
 }
 
 template <int R, int PODS, int CSIZE>
-__device__ __forceinline__ void scatter_pods_cluster(QuotaRow* rows, uint32_t NS, uint32_t wide_mask, uint32_t sbase,
+__device__ __forceinline__ void scatter_pods_cluster(long long* used, uint32_t NS, uint32_t wide_mask, uint32_t sbase,
                                                      uint32_t cap, const uint32_t (&hi_slot)[R], const uint32_t (&ns)[PODS],
                                                      const long long (&q)[R][PODS]) {
   constexpr uint32_t kLog = CSIZE == 16 ? 4 : CSIZE == 8 ? 3 : CSIZE == 4 ? 2 : 1;
@@ -665,7 +619,7 @@ __device__ __forceinline__ void scatter_pods_cluster(QuotaRow* rows, uint32_t NS
       const uint32_t hi = (uint32_t)(v >> 32) + (uint32_t)(old[r][k] + lo < old[r][k]);
       if (hi) {
         if ((wide_mask >> r) & 1u) redc_add_u32(base[k] + ((R + hi_slot[r]) * cap + local[k]) * 4u, hi);
-        else red_add_i64(&rows[ns[k]].w[2 * r], (long long)((unsigned long long)hi << 32));
+        else red_add_i64(used_at(used, NS, r, ns[k]), (long long)((unsigned long long)hi << 32));
       }
     }
   }
@@ -674,7 +628,7 @@ __device__ __forceinline__ void scatter_pods_cluster(QuotaRow* rows, uint32_t NS
 // cap = slots per CTA (>= ceil(NS / CSIZE)); launched with cluster dimension CSIZE
 template <int R, bool VEC, int CSIZE>
 __global__ void __launch_bounds__(1024, 1)
-k1_scatter_cluster(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, QuotaRow* rows, uint32_t NS,
+k1_scatter_cluster(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long long* used, uint32_t NS,
                    uint32_t cap, uint32_t wide_mask) {
   extern __shared__ __align__(16) uint32_t k1_smem[];
   constexpr int THREADS = 1024;
@@ -698,14 +652,14 @@ k1_scatter_cluster(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n,
     ns[0] = v.x; ns[1] = v.y; ns[2] = v.z; ns[3] = v.w;
 #pragma unroll
     for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
-    scatter_pods_cluster<R, 4, CSIZE>(rows, NS, wide_mask, sbase, cap, hi_slot, ns, q);
+    scatter_pods_cluster<R, 4, CSIZE>(used, NS, wide_mask, sbase, cap, hi_slot, ns, q);
   }
   for (size_t i = groups * 4 + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
     uint32_t ns[1] = {ns_id[i]};
     long long q[R][1];
 #pragma unroll
     for (int r = 0; r < R; ++r) q[r][0] = req.p[r][i];
-    scatter_pods_cluster<R, 1, CSIZE>(rows, NS, wide_mask, sbase, cap, hi_slot, ns, q);
+    scatter_pods_cluster<R, 1, CSIZE>(used, NS, wide_mask, sbase, cap, hi_slot, ns, q);
   }
 
   cluster_sync_all();  // all remote atomics into this CTA's table have landed
@@ -715,12 +669,12 @@ k1_scatter_cluster(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n,
     const uint32_t hi = ((wide_mask >> r) & 1u) ? k1_smem[(R + hi_slot[r]) * cap + sl] : 0u;
     const unsigned long long v = ((unsigned long long)hi << 32) | k1_smem[i];
     const uint32_t ns = (sl << kLog) | me;
-    if (v && ns < NS) red_add_i64(&rows[ns].w[2 * r], (long long)v);
+    if (v && ns < NS) red_add_i64(used_at(used, NS, r, ns), (long long)v);
   }
 }
 
 // ------------------------------------------------------------------ K2 quota_eval
-// K2 gathers one 32-byte sector per pod from a compact table derived from the QuotaRows:
+// K2 gathers one 32-byte sector per pod from a compact table derived from the usage and limit tables:
 // head[ns].h[r] = hard[r] - used[r], saturated to the i64 range, and for R <= 3 h[3] = hard_mask.
 // "exceeded" is the overflow-free comparison used + req > hard (as Kubernetes' arbitrary-precision
 // Quantity arithmetic would decide it), i.e. req > hard - used with the difference saturated.
@@ -734,13 +688,13 @@ __device__ __forceinline__ long long sat_sub_i64(long long a, long long b) {
   return d;
 }
 
-static __global__ void k_build_headroom(const QuotaRow* __restrict__ rows, const uint8_t* __restrict__ hard_mask,
-                                        HeadRow* head, uint32_t NS, int R) {
+static __global__ void k_build_headroom(const long long* __restrict__ used, const long long* __restrict__ hard,
+                                        const uint8_t* __restrict__ hard_mask, HeadRow* head, uint32_t NS, int R) {
   for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < (size_t)NS * 4;
        t += (size_t)gridDim.x * blockDim.x) {
     const uint32_t ns = (uint32_t)(t >> 2), r = (uint32_t)(t & 3);
     long long v = 0;
-    if ((int)r < R) v = sat_sub_i64(rows[ns].w[2 * r + 1], rows[ns].w[2 * r]);
+    if ((int)r < R) v = sat_sub_i64(hard[(size_t)r * NS + ns], used[(size_t)r * NS + ns]);
     else if (r == 3) v = hard_mask[ns];
     head[ns].h[r] = v;
   }
@@ -885,8 +839,9 @@ __device__ __forceinline__ uint32_t greedy_verdict(const GreedyPod<R>& p, const 
 template <int R, bool HAS_MASK>
 __global__ void __launch_bounds__(256)
 k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg, ReqCols<R> req,
-                const uint8_t* __restrict__ req_mask, QuotaRow* rows, const uint8_t* __restrict__ hard_mask,
-                uint32_t NS, uint32_t compute_mask, uint8_t* __restrict__ verdict, uint32_t team_min) {
+                const uint8_t* __restrict__ req_mask, long long* used, const long long* __restrict__ hard,
+                const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask,
+                uint8_t* __restrict__ verdict, uint32_t team_min) {
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t warps_total = gridDim.x * (blockDim.x >> 5);
   // heavy namespaces first would be ideal; a strided walk at least spreads neighbours over warps
@@ -896,10 +851,10 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
     long long S[R], H[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      S[r] = rows[ns].w[2 * r];
-      H[r] = rows[ns].w[2 * r + 1];
+      S[r] = used[(size_t)r * NS + ns];
+      H[r] = hard[(size_t)r * NS + ns];
     }
-    const uint32_t hm = (R <= 3) ? (uint32_t)rows[ns].w[7] : (uint32_t)hard_mask[ns];
+    const uint32_t hm = hard_mask[ns];
 
     // `req` / `req_mask` are the GROUPED columns (k_greedy_gather): tile t+1 is in flight while tile t is decided
     GreedyPod<R> p0;
@@ -1028,7 +983,7 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
     }
     if (lane == 0) {
 #pragma unroll
-      for (int r = 0; r < R; ++r) rows[ns].w[2 * r] = S[r];
+      for (int r = 0; r < R; ++r) used[(size_t)r * NS + ns] = S[r];
     }
   }
 }
@@ -1044,8 +999,9 @@ constexpr int kGreedyDepth = 4;  // tiles of requests in flight per CTA (ring of
 template <int R, bool HAS_MASK>
 __global__ void __launch_bounds__(kGreedyTeam, 1)
 k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg, ReqCols<R> req,
-                     const uint8_t* __restrict__ req_mask, QuotaRow* rows, const uint8_t* __restrict__ hard_mask,
-                     uint32_t NS, uint32_t compute_mask, uint8_t* __restrict__ verdict) {
+                     const uint8_t* __restrict__ req_mask, long long* used, const long long* __restrict__ hard,
+                     const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask,
+                     uint8_t* __restrict__ verdict) {
   extern __shared__ __align__(16) long long g_ring[];  // [kGreedyDepth][R][kGreedyTeam]
   __shared__ long long s_wtot[R][32];    // per-warp totals, then their exclusive prefix
   __shared__ long long s_total[R];
@@ -1060,10 +1016,10 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
     long long S[R], H[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      S[r] = rows[ns].w[2 * r];
-      H[r] = rows[ns].w[2 * r + 1];
+      S[r] = used[(size_t)r * NS + ns];
+      H[r] = hard[(size_t)r * NS + ns];
     }
-    const uint32_t hm = (R <= 3) ? (uint32_t)rows[ns].w[7] : (uint32_t)hard_mask[ns];
+    const uint32_t hm = hard_mask[ns];
     __syncthreads();  // previous namespace's shared state is no longer read
 
     // A single CTA walks this namespace, so its own loads are all the memory parallelism there is:
@@ -1266,7 +1222,7 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
     }
     if (tid == 0) {
 #pragma unroll
-      for (int r = 0; r < R; ++r) rows[ns].w[2 * r] = S[r];
+      for (int r = 0; r < R; ++r) used[(size_t)r * NS + ns] = S[r];
     }
   }
 }

@@ -10,7 +10,7 @@
 // creation, no library routine that allocates.
 //
 // How: the accumulation table the reduction kernel scatters into lives in a file-scope
-// `static __device__` array of fixed size (BGC_STATIC_MAX_NS namespaces x 64 B = 1 MiB), which
+// `static __device__` array of fixed size (BGC_STATIC_MAX_NS namespaces x 4 columns x 8 B = 512 KiB), which
 // every GPU that loads libbgc.so holds from module load until the process exits.  The caller
 // passes the inputs (pod columns) and the output (used[R][NS]) as device pointers, plus the stream
 // to run on.
@@ -40,14 +40,14 @@ namespace {
 constexpr int kMaxDevices = 64;
 constexpr size_t kStaticSmemBudget = 200 * 1024;
 
-// The scratch itself.  In HOST code the name `g_static_rows` is only a handle for the runtime
-// (a host-side shadow symbol), not a device address; kernels must be given the pointer obtained
-// from cudaGetSymbolAddress below.
-static __device__ __align__(256) QuotaRow g_static_rows[BGC_STATIC_MAX_NS];
+// The scratch itself: the [R][ns_count] usage table the kernel accumulates into.  In HOST code the
+// name `g_static_used` is only a handle for the runtime (a host-side shadow symbol), not a device
+// address; kernels must be given the pointer obtained from cudaGetSymbolAddress below.
+static __device__ __align__(256) long long g_static_used[(size_t)BGC_STATIC_MAX_NS * kMaxR];
 
 struct PerDevice {
   bool ready = false;
-  QuotaRow* rows = nullptr;  // device address of g_static_rows on this device
+  long long* used = nullptr;  // device address of g_static_used on this device
   int sm_count = 0;
 };
 PerDevice g_dev[kMaxDevices];
@@ -73,10 +73,10 @@ int say(char* errbuf, size_t cap, int code, const char* fmt, ...) {
 int setup_device(int dev, char* errbuf, size_t errbuf_len) {
   PerDevice& d = g_dev[dev];
   void* p = nullptr;
-  SCU(cudaGetSymbolAddress(&p, g_static_rows));
+  SCU(cudaGetSymbolAddress(&p, g_static_used));
   if (!p) return say(errbuf, errbuf_len, BGC_E_CUDA, "cudaGetSymbolAddress returned a null address");
   SCU(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
-  d.rows = static_cast<QuotaRow*>(p);
+  d.used = static_cast<long long*>(p);
   d.ready = true;
   return BGC_OK;
 }
@@ -105,7 +105,7 @@ int launch_reduce(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const
   size_t chunk_tiles = tiles / ((size_t)grid * wpb * 4);
   if (chunk_tiles < 1) chunk_tiles = 1;
   if (chunk_tiles > 32) chunk_tiles = 32;
-  kern<<<grid, threads, smem, st>>>(ns, cols, n, d.rows, NS, cap, (uint32_t)chunk_tiles, (1u << R) - 1u);
+  kern<<<grid, threads, smem, st>>>(ns, cols, n, d.used, NS, cap, (uint32_t)chunk_tiles, (1u << R) - 1u);
   SCU(cudaGetLastError());
   return BGC_OK;
 }
@@ -162,14 +162,8 @@ extern "C" int bgc_usage_reduce_static_dev(const uint32_t* d_ns_id, const int64_
   const PerDevice& d = g_dev[dev];
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
 
-  // the table keeps the previous call's sums: zero the used[] slots this call accumulates into
-  {
-    const size_t total = (size_t)ns_count * R;
-    int grid = (int)((total + 255) / 256);
-    if (grid > d.sm_count * 4) grid = d.sm_count * 4;
-    k_rows_clear_used<<<grid, 256, 0, st>>>(d.rows, ns_count, (int)R);
-    SCU(cudaGetLastError());
-  }
+  // the table keeps the previous call's sums: zero the [R][ns_count] slots this call accumulates into
+  SCU(cudaMemsetAsync(d.used, 0, (size_t)ns_count * R * 8, st));
   int rc = BGC_OK;
   if (n) {
     switch (R) {
@@ -180,12 +174,7 @@ extern "C" int bgc_usage_reduce_static_dev(const uint32_t* d_ns_id, const int64_
     }
     if (rc) return rc;
   }
-  {
-    const size_t total = (size_t)ns_count * R;
-    int grid = (int)((total + 255) / 256);
-    if (grid > d.sm_count * 4) grid = d.sm_count * 4;
-    k_rows_export_used<<<grid, 256, 0, st>>>(d.rows, reinterpret_cast<long long*>(d_used_out), ns_count, (int)R);
-    SCU(cudaGetLastError());
-  }
+  // the table already has the [R][ns_count] layout of the output
+  SCU(cudaMemcpyAsync(d_used_out, d.used, (size_t)ns_count * R * 8, cudaMemcpyDeviceToDevice, st));
   return BGC_OK;
 }

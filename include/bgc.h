@@ -173,7 +173,7 @@ int bgc_admit_greedy_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *c
  * call (all of HBM already handed to their own pool, or a latency-critical handler that must not
  * trigger cudaMalloc's device-wide synchronisation): the same result as bgc_usage_reduce_dev, but
  * without a bgc_ctx and without a single allocation — the accumulation table is a static device
- * array of BGC_STATIC_MAX_NS namespaces (1 MiB per GPU, held from library load to process exit).
+ * array of BGC_STATIC_MAX_NS namespaces (512 KiB per GPU, held from library load to process exit).
  *   - runs on the CURRENT device, on `cuda_stream`; inputs and d_used_out ([R][ns_count]) are
  *     device pointers owned by the caller;
  *   - ns_count > BGC_STATIC_MAX_NS or R outside 1..BGC_MAX_R → BGC_E_BADARG, message in errbuf
