@@ -27,11 +27,13 @@ if not os.path.exists(LIB_PATH):
 lib = C.CDLL(LIB_PATH)
 
 OK, E_BADARG, E_CUDA, E_OOM, E_STATE = 0, -1, -2, -3, -4
-MAX_R = 4
+MAX_R = 8
+MAX_R8 = 4
 UNIT_COUNT, UNIT_MILLI, UNIT_BYTES = 0, 1, 2
 REDUCE_GROUPED, REDUCE_ACCUMULATE = 1, 2
 K1_AUTO, K1_GLOBAL, K1_SMEM_DIRECT, K1_SMEM_HASH, K1_CLUSTER8, K1_CLUSTER16 = 0, 1, 2, 3, 4, 5
 VERDICT_BAD_NS = 0xFF
+VERDICT16_BAD_NS = 0xFFFF
 ALLOW, ALLOW_PATCH, DENY, INVALID = 0, 1, 2, 3
 GEN_GPU, GEN_CPU_MILLI, GEN_MEM_BYTES, GEN_MIG = 0, 1, 2, 3
 DIST_UNIFORM, DIST_ZIPF_CDF = 0, 1
@@ -40,7 +42,7 @@ DIST_UNIFORM, DIST_ZIPF_CDF = 0, 1
 EXPORTS = [
     "bgc_ctx_create", "bgc_ctx_destroy", "bgc_last_error", "bgc_ctx_set_stream", "bgc_ctx_reset_stream", "bgc_ctx_sync",
     "bgc_timings_get", "bgc_policy_eval", "bgc_policy_eval_dev", "bgc_quota_table_set",
-    "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_usage_get_dev", "bgc_usage_set_dev", "bgc_quota_eval",
+    "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_usage_get_dev", "bgc_usage_set_dev", "bgc_quota_eval", "bgc_quota_eval16", "bgc_quota_eval16_dev",
     "bgc_quota_eval_dev", "bgc_ctx_set_k1_variant", "bgc_last_k1_variant", "bgc_version",
     "bgc_synth_pods_dev", "bgc_synth_policy_dev", "bgc_checksum_u8_dev", "bgc_histogram_u8_dev",
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
@@ -90,6 +92,8 @@ lib.bgc_usage_get_dev.argtypes = [_P, _P]
 lib.bgc_usage_set_dev.argtypes = [_P, _P]
 lib.bgc_quota_eval.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_quota_eval_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_quota_eval16.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_quota_eval16_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_admit_greedy.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_admit_greedy_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_synth_pods_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64, _Z, _P, _P, _P]
@@ -237,7 +241,7 @@ class Engine:
                                           flags, _dev_ptr(d_used_out)))
 
     # -- K2 (row A4)
-    def quota_eval(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None) -> np.ndarray:
+    def quota_eval(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None, wide: bool = False) -> np.ndarray:
         n = ns_id.shape[0]
         _check_np(ns_id, np.uint32, name="ns_id")
         for r, c in enumerate(req):
@@ -247,14 +251,19 @@ class Engine:
         if len(req) != self.R:
             raise ValueError(f"expected {self.R} request columns")
         ptrs = (C.c_void_p * len(req))(*[c.ctypes.data for c in req])
-        verdict = np.empty(n, np.uint8)
-        self._ck(lib.bgc_quota_eval(self._h, _np_ptr(ns_id), ptrs, _np_ptr(req_mask), n, _np_ptr(verdict)))
+        if wide:      # u16 verdicts: missing << 8 | exceeded, any R <= 8
+            verdict = np.empty(n, np.uint16)
+            self._ck(lib.bgc_quota_eval16(self._h, _np_ptr(ns_id), ptrs, _np_ptr(req_mask), n, _np_ptr(verdict)))
+        else:
+            verdict = np.empty(n, np.uint8)
+            self._ck(lib.bgc_quota_eval(self._h, _np_ptr(ns_id), ptrs, _np_ptr(req_mask), n, _np_ptr(verdict)))
         return verdict
 
     def quota_eval_dev(self, d_ns_id, d_req: list, d_req_mask, d_verdict, n: int | None = None):
+        """d_verdict: uint8 tensor (R <= 4) or int16/uint16 tensor (u16 form, R <= 8)."""
         ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
-        self._ck(lib.bgc_quota_eval_dev(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask),
-                                        d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
+        fn = lib.bgc_quota_eval16_dev if d_verdict.element_size() == 2 else lib.bgc_quota_eval_dev
+        self._ck(fn(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask), d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
 
     # -- K3 (row N1): sequential admission inside the batch; updates the usage table
     def admit_greedy(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None) -> np.ndarray:

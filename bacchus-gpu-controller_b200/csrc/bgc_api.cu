@@ -25,11 +25,11 @@ constexpr size_t kChunkPods = size_t(4) << 20;      // host-pointer calls move 4
 constexpr size_t kSmemBudget = 224 * 1024;          // CTA-private K1 table budget (<= 227 KB opt-in)
 constexpr int kSlots = 2;
 constexpr size_t kZeroCopyMaxPods = 262144;         // host batches up to this size take the latency path
-constexpr size_t kZeroCopyBytes = kZeroCopyMaxPods * (4 + 8 * 4 + 1 + 1 + 2) + 16 * 256;
+constexpr size_t kZeroCopyBytes = kZeroCopyMaxPods * (4 + 8 * kMaxR + 1 + 2 + 2) + 16 * 256;
 
 struct Slot {
   uint32_t* ns = nullptr;
-  long long* req[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  long long* req[kMaxR] = {};
   uint8_t* mask = nullptr;
   uint8_t* out0 = nullptr;  // verdict / code
   uint8_t* out1 = nullptr;  // patch_mask
@@ -53,7 +53,7 @@ struct bgc_ctx {
   int R = 0;
   uint32_t compute_mask = 0;
   uint32_t wide_mask = 0;            // byte-valued columns: K1 keeps their high words in shared memory
-  HeadRow* head = nullptr;           // K2's compact table (hard - used, mask), rebuilt when stale
+  long long* head = nullptr;         // K2's compact table (hard - used, mask), rebuilt when stale
   bool head_stale = true;
   // K1
   int k1_forced = BGC_K1_AUTO;
@@ -70,7 +70,7 @@ struct bgc_ctx {
   // greedy admission (row N1): grouping buffers, grown on demand
   uint32_t *g_keys = nullptr, *g_keys_sorted = nullptr, *g_idx = nullptr, *g_order = nullptr, *g_seg = nullptr;
   void* g_temp = nullptr;
-  long long* g_req[kMaxR] = {nullptr, nullptr, nullptr, nullptr};  // request columns in grouped order
+  long long* g_req[kMaxR] = {};  // request columns in grouped order
   uint8_t* g_mask = nullptr;
   int g_R = 0;
   size_t g_cap = 0, g_temp_bytes = 0, g_seg_cap = 0;
@@ -182,7 +182,7 @@ int launch_k1_scatter(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const l
   ReqCols<R> cols;
   for (int r = 0; r < R; ++r) cols.p[r] = req[r];
   const size_t smem = k1_slot_bytes(ctx, R) * cap + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
-  const size_t groups = (n + 3) / 4;
+  const size_t groups = (n + 1) / 2;
   auto go = [&](auto kern, int threads) -> int {
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = ctx->sm_count;
@@ -194,12 +194,15 @@ int launch_k1_scatter(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const l
     CU(cudaGetLastError());
     return BGC_OK;
   };
-  switch (ctx->k1_shape) {
-    case 1: return go(k1_scatter<R, SINK, VEC, 512, 2>, 512);
-    case 2: return go(k1_scatter<R, SINK, VEC, 1024, 2>, 1024);
-    case 3: return go(k1_scatter<R, SINK, VEC, 512, 1>, 512);
-    default: return go(k1_scatter<R, SINK, VEC, 1024, 1>, 1024);
+  if constexpr (R <= 4) {
+    switch (ctx->k1_shape) {
+      case 1: return go(k1_scatter<R, SINK, VEC, 512, 2>, 512);
+      case 2: return go(k1_scatter<R, SINK, VEC, 1024, 2>, 1024);
+      case 3: return go(k1_scatter<R, SINK, VEC, 512, 1>, 512);
+      default: break;
+    }
   }
+  return go(k1_scatter<R, SINK, VEC, 1024, 1>, 1024);
 }
 
 // cluster-distributed table: CSIZE SMs share one direct-indexed table over distributed shared memory
@@ -276,18 +279,30 @@ int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long lo
         return vec ? launch_k1_scatter<R, SINK_DIRECT, true>(ctx, st, ns, req, n, cap)
                    : launch_k1_scatter<R, SINK_DIRECT, false>(ctx, st, ns, req, n, cap);
       }
+      if constexpr (R > 4) {  // the segmented kernel keeps its shared-memory sinks for R <= 4 only
+        ctx->last_k1 = "segmented_global_red";
+        return vec ? launch_k1_inst<R, SINK_GLOBAL, true>(ctx, st, ns, req, n, cap)
+                   : launch_k1_inst<R, SINK_GLOBAL, false>(ctx, st, ns, req, n, cap);
+      } else {
       ctx->last_k1 = "segmented_smem_direct";
       return vec ? launch_k1_inst<R, SINK_DIRECT, true>(ctx, st, ns, req, n, cap)
                  : launch_k1_inst<R, SINK_DIRECT, false>(ctx, st, ns, req, n, cap);
+      }
     default:
       if (!(flags & BGC_REDUCE_GROUPED)) {
         ctx->last_k1 = "scatter_smem_hash";
         return vec ? launch_k1_scatter<R, SINK_HASH, true>(ctx, st, ns, req, n, cap)
                    : launch_k1_scatter<R, SINK_HASH, false>(ctx, st, ns, req, n, cap);
       }
+      if constexpr (R > 4) {
+        ctx->last_k1 = "segmented_global_red";
+        return vec ? launch_k1_inst<R, SINK_GLOBAL, true>(ctx, st, ns, req, n, cap)
+                   : launch_k1_inst<R, SINK_GLOBAL, false>(ctx, st, ns, req, n, cap);
+      } else {
       ctx->last_k1 = "segmented_smem_hash";
       return vec ? launch_k1_inst<R, SINK_HASH, true>(ctx, st, ns, req, n, cap)
                  : launch_k1_inst<R, SINK_HASH, false>(ctx, st, ns, req, n, cap);
+      }
   }
 }
 
@@ -298,52 +313,62 @@ int launch_k1(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long
     case 1: return launch_k1_r<1>(ctx, st, ns, req, n, flags);
     case 2: return launch_k1_r<2>(ctx, st, ns, req, n, flags);
     case 3: return launch_k1_r<3>(ctx, st, ns, req, n, flags);
-    default: return launch_k1_r<4>(ctx, st, ns, req, n, flags);
+    case 4: return launch_k1_r<4>(ctx, st, ns, req, n, flags);
+    case 5: return launch_k1_r<5>(ctx, st, ns, req, n, flags);
+    case 6: return launch_k1_r<6>(ctx, st, ns, req, n, flags);
+    case 7: return launch_k1_r<7>(ctx, st, ns, req, n, flags);
+    default: return launch_k1_r<8>(ctx, st, ns, req, n, flags);
   }
 }
 
-template <int R, bool HAS_MASK>
+template <int R, bool HAS_MASK, typename VT>
 int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
-                   const uint8_t* mask, size_t n, uint8_t* verdict) {
+                   const uint8_t* mask, size_t n, VT* verdict) {
   ReqCols<R> cols;
-  bool vec = aligned(ns, 16) && aligned(verdict, 4) && (!HAS_MASK || aligned(mask, 4));
+  constexpr int PODS = R <= 4 ? 4 : 2;
+  bool vec = aligned(ns, 16) && aligned(verdict, 8) && (!HAS_MASK || aligned(mask, 4));
   for (int r = 0; r < R; ++r) {
     cols.p[r] = req[r];
     vec = vec && aligned(req[r], 32);
   }
   if (ctx->head_stale) {  // usage or limits changed since the compact table was built
-    const int g = grid_for((size_t)ctx->NS * 4, 256, ctx->sm_count * 4);
+    const int g = grid_for((size_t)ctx->NS * head_words(R), 256, ctx->sm_count * 4);
     k_build_headroom<<<g, 256, 0, st>>>(ctx->d_used, ctx->d_hard, ctx->d_hard_mask, ctx->head, ctx->NS, R);
     ctx->tm.launches++;
     CU(cudaGetLastError());
     ctx->head_stale = false;
   }
-  const int grid = grid_for((n + 3) / 4, kK2Threads, ctx->sm_count * 8);
+  const int grid = grid_for((n + PODS - 1) / PODS, kK2Threads, ctx->sm_count * 8);
   if (vec)
-    k2_quota_eval<R, HAS_MASK, true><<<grid, kK2Threads, 0, st>>>(
+    k2_quota_eval<R, HAS_MASK, true, VT><<<grid, kK2Threads, 0, st>>>(
         ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
   else
-    k2_quota_eval<R, HAS_MASK, false><<<grid, kK2Threads, 0, st>>>(
+    k2_quota_eval<R, HAS_MASK, false, VT><<<grid, kK2Threads, 0, st>>>(
         ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
   ctx->tm.launches++;
   CU(cudaGetLastError());
   return BGC_OK;
 }
 
+// VT = uint8_t: missing << 4 | exceeded (R <= 4);  VT = uint16_t: missing << 8 | exceeded (R <= 8)
+template <typename VT>
 int launch_k2(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long long* const* req,
-              const uint8_t* mask, size_t n, uint8_t* verdict) {
+              const uint8_t* mask, size_t n, VT* verdict) {
   if (n == 0) return BGC_OK;
-#define K2CASE(RR)                                                                   \
-  case RR:                                                                           \
-    return mask ? launch_k2_inst<RR, true>(ctx, st, ns, req, mask, n, verdict)       \
-                : launch_k2_inst<RR, false>(ctx, st, ns, req, mask, n, verdict);
-  switch (ctx->R) {
-    K2CASE(1)
-    K2CASE(2)
-    K2CASE(3)
-    default:
-      return mask ? launch_k2_inst<4, true>(ctx, st, ns, req, mask, n, verdict)
-                  : launch_k2_inst<4, false>(ctx, st, ns, req, mask, n, verdict);
+#define K2CASE(RR)                                                                       \
+  case RR:                                                                               \
+    return mask ? launch_k2_inst<RR, true, VT>(ctx, st, ns, req, mask, n, verdict)       \
+                : launch_k2_inst<RR, false, VT>(ctx, st, ns, req, mask, n, verdict);
+  if constexpr (sizeof(VT) == 1) {
+    switch (ctx->R) {
+      K2CASE(1) K2CASE(2) K2CASE(3) K2CASE(4)
+      default: return fail(ctx, BGC_E_BADARG, "u8 verdicts hold at most 4 resources: use bgc_quota_eval16 for R = %d", ctx->R);
+    }
+  } else {
+    switch (ctx->R) {
+      K2CASE(1) K2CASE(2) K2CASE(3) K2CASE(4) K2CASE(5) K2CASE(6) K2CASE(7) K2CASE(8)
+      default: return fail(ctx, BGC_E_BADARG, "R out of range");
+    }
   }
 #undef K2CASE
 }
@@ -387,7 +412,7 @@ int ensure_slots(bgc_ctx* ctx, size_t pods, int R) {
     CU(cudaMalloc(&s.ns, pods * 4));
     for (int r = 0; r < R; ++r) CU(cudaMalloc(&s.req[r], pods * 8));
     CU(cudaMalloc(&s.mask, pods));
-    CU(cudaMalloc(&s.out0, pods));
+    CU(cudaMalloc(&s.out0, pods * 2));
     CU(cudaMalloc(&s.out1, pods));
     CU(cudaMalloc(&s.flags, pods * 2));
     if (!s.h2d_done) {
@@ -650,7 +675,7 @@ int bgc_quota_table_set(bgc_ctx* ctx, uint32_t ns_count, uint32_t R, const int64
     ctx->NS = 0; ctx->R = 0;
     CU(cudaMalloc(&ctx->d_used, (size_t)ns_count * R * 8));
     CU(cudaMalloc(&ctx->d_hard, (size_t)ns_count * R * 8));
-    CU(cudaMalloc(&ctx->head, (size_t)ns_count * sizeof(HeadRow)));
+    CU(cudaMalloc(&ctx->head, (size_t)ns_count * head_words((int)R) * 8));
     CU(cudaMalloc(&ctx->d_hard_mask, ns_count));
   }
   ctx->NS = ns_count;
@@ -719,7 +744,7 @@ int bgc_usage_reduce_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* c
   if (!ctx) return BGC_E_BADARG;
   if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (d_ns_id && d_req), "null column pointer");
-  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  const long long* cols[kMaxR] = {};
   for (int r = 0; r < ctx->R && n; ++r) {
     NEED(d_req[r], "null request column");
     cols[r] = reinterpret_cast<const long long*>(d_req[r]);
@@ -789,12 +814,17 @@ int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
 }
 
 // ---------------------------------------------------------------- K2
-int bgc_quota_eval_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
-                       const uint8_t* d_req_mask, size_t n, uint8_t* d_verdict) {
+}  // extern "C"
+
+namespace {
+
+template <typename VT>
+int quota_eval_dev_impl(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
+                        const uint8_t* d_req_mask, size_t n, VT* d_verdict) {
   if (!ctx) return BGC_E_BADARG;
   if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (d_ns_id && d_req && d_verdict), "null column pointer");
-  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  const long long* cols[kMaxR] = {};
   for (int r = 0; r < ctx->R && n; ++r) {
     NEED(d_req[r], "null request column");
     cols[r] = reinterpret_cast<const long long*>(d_req[r]);
@@ -803,8 +833,9 @@ int bgc_quota_eval_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* con
   return launch_k2(ctx, ctx->stream, d_ns_id, cols, d_req_mask, n, d_verdict);
 }
 
-int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
-                   const uint8_t* req_mask, size_t n, uint8_t* verdict) {
+template <typename VT>
+int quota_eval_host_impl(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
+                         const uint8_t* req_mask, size_t n, VT* verdict) {
   if (!ctx) return BGC_E_BADARG;
   if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (ns_id && req && verdict), "null column pointer");
@@ -818,14 +849,14 @@ int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* re
   if (n <= ctx->zc_max_pods) {  // latency path: one launch, the kernel reads/writes host memory itself
     ZcCursor cur;
     uint8_t* bounce;
-    const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+    const long long* cols[kMaxR] = {};
     const uint32_t* z_ns = static_cast<const uint32_t*>(zc_in(ctx, cur, ns_id, n * 4));
     for (int r = 0; r < R; ++r) cols[r] = static_cast<const long long*>(zc_in(ctx, cur, req[r], n * 8));
     const uint8_t* z_mask = req_mask ? static_cast<const uint8_t*>(zc_in(ctx, cur, req_mask, n)) : nullptr;
-    uint8_t* z_v = static_cast<uint8_t*>(zc_out(ctx, cur, verdict, n, &bounce));
+    VT* z_v = static_cast<VT*>(zc_out(ctx, cur, verdict, n * sizeof(VT), &bounce));
     if ((rc = launch_k2(ctx, ctx->own_stream, z_ns, cols, z_mask, n, z_v))) return rc;
     CU(cudaStreamSynchronize(ctx->own_stream));
-    if (bounce) std::memcpy(verdict, bounce, n);
+    if (bounce) std::memcpy(verdict, bounce, n * sizeof(VT));
     return BGC_OK;
   }
   if ((rc = ensure_slots(ctx, n, R))) return rc;
@@ -855,14 +886,14 @@ int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* re
       CU(cudaStreamWaitEvent(ctx->own_stream, s.h2d_done, 0));
     }
     CU(cudaEventRecord(c, ctx->own_stream));
-    if ((rc = launch_k2(ctx, ctx->own_stream, s.ns, s.req, req_mask ? s.mask : nullptr, m, s.out0))) return rc;
+    if ((rc = launch_k2(ctx, ctx->own_stream, s.ns, s.req, req_mask ? s.mask : nullptr, m, reinterpret_cast<VT*>(s.out0)))) return rc;
     CU(cudaEventRecord(d, ctx->own_stream));
     if (!single) {
       CU(cudaEventRecord(s.k_done, ctx->own_stream));
       CU(cudaStreamWaitEvent(ds, s.k_done, 0));
     }
     CU(cudaEventRecord(e, ds));
-    CU(cudaMemcpyAsync(verdict + off, s.out0, m, cudaMemcpyDeviceToHost, ds));
+    CU(cudaMemcpyAsync(verdict + off, s.out0, m * sizeof(VT), cudaMemcpyDeviceToHost, ds));
     CU(cudaEventRecord(f, ds));
     if (!single) CU(cudaEventRecord(s.free_ev, ds));
     s.used = !single;
@@ -872,6 +903,27 @@ int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* re
   }
   CU(cudaStreamSynchronize(ds));
   return finish_timings(ctx, sp);
+}
+
+}  // namespace
+
+extern "C" {
+
+int bgc_quota_eval_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
+                       const uint8_t* d_req_mask, size_t n, uint8_t* d_verdict) {
+  return quota_eval_dev_impl<uint8_t>(ctx, d_ns_id, d_req, d_req_mask, n, d_verdict);
+}
+int bgc_quota_eval16_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
+                         const uint8_t* d_req_mask, size_t n, uint16_t* d_verdict) {
+  return quota_eval_dev_impl<uint16_t>(ctx, d_ns_id, d_req, d_req_mask, n, d_verdict);
+}
+int bgc_quota_eval(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req, const uint8_t* req_mask,
+                   size_t n, uint8_t* verdict) {
+  return quota_eval_host_impl<uint8_t>(ctx, ns_id, req, req_mask, n, verdict);
+}
+int bgc_quota_eval16(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req, const uint8_t* req_mask,
+                     size_t n, uint16_t* verdict) {
+  return quota_eval_host_impl<uint16_t>(ctx, ns_id, req, req_mask, n, verdict);
 }
 
 }  // extern "C"
@@ -966,7 +1018,8 @@ extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const
   if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (d_ns_id && d_req && d_verdict), "null column pointer");
   NEED(n < (size_t(1) << 31), "greedy admission handles fewer than 2^31 pods per call");
-  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  NEED(ctx->R <= kMaxR8, "greedy admission is built for R <= 4 (u8 verdicts)");
+  const long long* cols[kMaxR] = {};
   for (int r = 0; r < ctx->R && n; ++r) {
     NEED(d_req[r], "null request column");
     cols[r] = reinterpret_cast<const long long*>(d_req[r]);
@@ -1013,7 +1066,7 @@ extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   // the whole batch must be resident for the grouping pass: one-shot buffers, released on return
   uint32_t* d_ns = nullptr;
-  long long* d_req[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  long long* d_req[kMaxR] = {};
   uint8_t *d_mask = nullptr, *d_v = nullptr;
   auto cleanup = [&] {
     cudaFree(d_ns); cudaFree(d_mask); cudaFree(d_v);

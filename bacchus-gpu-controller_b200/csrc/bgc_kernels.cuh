@@ -13,7 +13,8 @@
 
 namespace bgc {
 
-constexpr int kMaxR = 4;
+constexpr int kMaxR = 8;   // u8 verdicts up to R = 4, u16 verdicts up to R = 8
+constexpr int kMaxR8 = 4;  // widest R of the u8 verdict encoding
 constexpr uint32_t kBadNs = 0xFFFFFFFFu;
 
 // Quota state: two [R][NS] int64 tables, `used` (K1 accumulates into it with global reds; the L2
@@ -52,6 +53,26 @@ __device__ __forceinline__ void ldg_row_half(const long long* p, long long (&v)[
                : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
                : "l"(p));
 }
+// PODS consecutive pods per thread: 4 (R <= 4: 128-bit ns + 256-bit request loads) or 2 (R > 4, to
+// stay inside 64 registers: 64-bit ns + 128-bit request loads)
+template <int PODS>
+__device__ __forceinline__ void ldg_ns(const uint32_t* p, uint32_t (&v)[PODS]) {
+  if constexpr (PODS == 4) {
+    const uint4 x = ldg_nc_u32x4(p);
+    v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+  } else {
+    asm("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v[0]), "=r"(v[1]) : "l"(p));
+  }
+}
+template <int PODS>
+__device__ __forceinline__ void ldg_req(const long long* p, long long (&v)[PODS]) {
+  if constexpr (PODS == 4) {
+    ldg_nc_i64x4(p, v);
+  } else {
+    asm("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(v[0]), "=l"(v[1]) : "l"(p));
+  }
+}
+
 // 256-bit streaming load / store of 8 words (one full 32-byte sector per thread)
 __device__ __forceinline__ void ldg_nc_u32x8(const void* p, uint32_t (&v)[8]) {
   asm("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -509,36 +530,35 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long lo
   C.key_base = sbase + words * 4u;
   __syncthreads();
 
-  const size_t groups = VEC ? n / 4 : 0;
+  constexpr int PODS = R <= 4 ? 4 : 2;
+  const size_t groups = VEC ? n / PODS : 0;
   const size_t stride = (size_t)gridDim.x * THREADS;
   size_t g = (size_t)blockIdx.x * THREADS + threadIdx.x;
-  // U groups per trip: all loads first (U*(1+R) independent 128/256-bit requests per thread)
+  // U groups per trip: all loads first (U*(1+R) independent vector requests per thread)
   for (; g + (U - 1) * stride < groups; g += U * stride) {
-    uint32_t ns[U][4];
-    long long q[U][R][4];
+    uint32_t ns[U][PODS];
+    long long q[U][R][PODS];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const size_t base = (g + u * stride) * 4;
-      const uint4 v = ldg_nc_u32x4(ns_id + base);
-      ns[u][0] = v.x; ns[u][1] = v.y; ns[u][2] = v.z; ns[u][3] = v.w;
+      const size_t base = (g + u * stride) * PODS;
+      ldg_ns<PODS>(ns_id + base, ns[u]);
 #pragma unroll
-      for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[u][r]);
+      for (int r = 0; r < R; ++r) ldg_req<PODS>(req.p[r] + base, q[u][r]);
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) scatter_pods<R, SINK, 4>(C, ns[u], q[u]);
+    for (int u = 0; u < U; ++u) scatter_pods<R, SINK, PODS>(C, ns[u], q[u]);
   }
   for (; g < groups; g += stride) {
-    uint32_t ns[4];
-    long long q[R][4];
-    const size_t base = g * 4;
-    const uint4 v = ldg_nc_u32x4(ns_id + base);
-    ns[0] = v.x; ns[1] = v.y; ns[2] = v.z; ns[3] = v.w;
+    uint32_t ns[PODS];
+    long long q[R][PODS];
+    const size_t base = g * PODS;
+    ldg_ns<PODS>(ns_id + base, ns);
 #pragma unroll
-    for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
-    scatter_pods<R, SINK, 4>(C, ns, q);
+    for (int r = 0; r < R; ++r) ldg_req<PODS>(req.p[r] + base, q[r]);
+    scatter_pods<R, SINK, PODS>(C, ns, q);
   }
   // scalar tail (and everything when the columns are not 16/32-byte aligned)
-  for (size_t i = groups * 4 + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
+  for (size_t i = groups * PODS + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
     uint32_t ns[1] = {ns_id[i]};
     long long q[R][1];
 #pragma unroll
@@ -642,19 +662,19 @@ k1_scatter_cluster(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n,
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(k1_smem);
   cluster_sync_all();  // every table of the cluster is zeroed before anyone scatters into it
 
-  const size_t groups = VEC ? n / 4 : 0;
+  constexpr int PODS = R <= 4 ? 4 : 2;
+  const size_t groups = VEC ? n / PODS : 0;
   const size_t stride = (size_t)gridDim.x * THREADS;
   for (size_t g = (size_t)blockIdx.x * THREADS + threadIdx.x; g < groups; g += stride) {
-    uint32_t ns[4];
-    long long q[R][4];
-    const size_t base = g * 4;
-    const uint4 v = ldg_nc_u32x4(ns_id + base);
-    ns[0] = v.x; ns[1] = v.y; ns[2] = v.z; ns[3] = v.w;
+    uint32_t ns[PODS];
+    long long q[R][PODS];
+    const size_t base = g * PODS;
+    ldg_ns<PODS>(ns_id + base, ns);
 #pragma unroll
-    for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
-    scatter_pods_cluster<R, 4, CSIZE>(used, NS, wide_mask, sbase, cap, hi_slot, ns, q);
+    for (int r = 0; r < R; ++r) ldg_req<PODS>(req.p[r] + base, q[r]);
+    scatter_pods_cluster<R, PODS, CSIZE>(used, NS, wide_mask, sbase, cap, hi_slot, ns, q);
   }
-  for (size_t i = groups * 4 + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
+  for (size_t i = groups * PODS + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
     uint32_t ns[1] = {ns_id[i]};
     long long q[R][1];
 #pragma unroll
@@ -678,9 +698,10 @@ k1_scatter_cluster(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n,
 // head[ns].h[r] = hard[r] - used[r], saturated to the i64 range, and for R <= 3 h[3] = hard_mask.
 // "exceeded" is the overflow-free comparison used + req > hard (as Kubernetes' arbitrary-precision
 // Quantity arithmetic would decide it), i.e. req > hard - used with the difference saturated.
-struct __align__(32) HeadRow {
-  long long h[4];
-};
+// The table is NS rows of HEADW(R) words: 4 (one 32-byte sector) for R <= 3, 8 (two sectors) for
+// R <= 8; the last word holds hard_mask when there is room (R < HEADW), else the mask is gathered
+// from its own byte array.
+__host__ __device__ constexpr int head_words(int R) { return R <= 3 ? 4 : 8; }
 
 __device__ __forceinline__ long long sat_sub_i64(long long a, long long b) {
   const long long d = (long long)((unsigned long long)a - (unsigned long long)b);
@@ -689,28 +710,40 @@ __device__ __forceinline__ long long sat_sub_i64(long long a, long long b) {
 }
 
 static __global__ void k_build_headroom(const long long* __restrict__ used, const long long* __restrict__ hard,
-                                        const uint8_t* __restrict__ hard_mask, HeadRow* head, uint32_t NS, int R) {
-  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < (size_t)NS * 4;
+                                        const uint8_t* __restrict__ hard_mask, long long* head, uint32_t NS, int R) {
+  const int W = head_words(R);
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < (size_t)NS * W;
        t += (size_t)gridDim.x * blockDim.x) {
-    const uint32_t ns = (uint32_t)(t >> 2), r = (uint32_t)(t & 3);
+    const uint32_t ns = (uint32_t)(t / W);
+    const int r = (int)(t % W);
     long long v = 0;
-    if ((int)r < R) v = sat_sub_i64(hard[(size_t)r * NS + ns], used[(size_t)r * NS + ns]);
-    else if (r == 3) v = hard_mask[ns];
-    head[ns].h[r] = v;
+    if (r < R) v = sat_sub_i64(hard[(size_t)r * NS + ns], used[(size_t)r * NS + ns]);
+    else if (r == W - 1) v = hard_mask[ns];
+    head[t] = v;
   }
 }
 
-// 4 pods per thread: one 128-bit ns load, R 256-bit request loads, one 256-bit HeadRow gather per
-// pod, one 32-bit verdict store.  verdict = missing << 4 | exceeded.
-template <int R>
+// verdict = missing << SHIFT | exceeded, SHIFT = 4 for the u8 form (R <= 4), 8 for the u16 form
+template <int R, int SHIFT>
 __device__ __forceinline__ uint32_t quota_verdict(uint32_t ns, const long long (&q)[R], uint32_t rmask,
-                                                  const HeadRow* __restrict__ head,
+                                                  const long long* __restrict__ head,
                                                   const uint8_t* __restrict__ hard_mask, uint32_t NS,
                                                   uint32_t compute_mask) {
-  if (ns >= NS) return 0xFFu;
-  long long h[4];
-  ldg_row_half(&head[ns].h[0], h);
-  const uint32_t hm = (R <= 3) ? (uint32_t)h[3] : (uint32_t)hard_mask[ns];
+  if (ns >= NS) return SHIFT == 4 ? 0xFFu : 0xFFFFu;
+  constexpr int W = head_words(R);
+  long long h[W];
+  {
+    long long t[4];
+    ldg_row_half(head + (size_t)ns * W, t);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = t[i];
+    if constexpr (W == 8) {
+      ldg_row_half(head + (size_t)ns * W + 4, t);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) h[4 + i] = t[i];
+    }
+  }
+  const uint32_t hm = (R < W) ? (uint32_t)h[W - 1] : (uint32_t)hard_mask[ns];
   uint32_t missing = 0, exceeded = 0;
 #pragma unroll
   for (int r = 0; r < R; ++r) {
@@ -719,45 +752,61 @@ __device__ __forceinline__ uint32_t quota_verdict(uint32_t ns, const long long (
     if (constrained && !present && ((compute_mask >> r) & 1u)) missing |= 1u << r;
     if (constrained && present && q[r] > 0 && q[r] > h[r]) exceeded |= 1u << r;
   }
-  return (missing << 4) | exceeded;
+  return (missing << SHIFT) | exceeded;
 }
 
 constexpr int kK2Threads = 256;
 
-template <int R, bool HAS_MASK, bool VEC>
+// PODS pods per thread (4 for R <= 4, 2 above): one vector ns load, R vector request loads, one
+// HeadRow gather per pod (one or two 32-byte sectors), one packed verdict store.
+template <int R, bool HAS_MASK, bool VEC, typename VT>
 __global__ void __launch_bounds__(kK2Threads)
 k2_quota_eval(const uint32_t* __restrict__ ns_id, ReqCols<R> req, const uint8_t* __restrict__ req_mask,
-              size_t n, const HeadRow* __restrict__ rows, const uint8_t* __restrict__ hard_mask,
-              uint32_t NS, uint32_t compute_mask, uint8_t* __restrict__ verdict) {
-  const size_t groups = VEC ? n / 4 : 0;
+              size_t n, const long long* __restrict__ head, const uint8_t* __restrict__ hard_mask,
+              uint32_t NS, uint32_t compute_mask, VT* __restrict__ verdict) {
+  constexpr int PODS = R <= 4 ? 4 : 2;
+  constexpr int SHIFT = sizeof(VT) == 1 ? 4 : 8;
+  const size_t groups = VEC ? n / PODS : 0;
   for (size_t g = (size_t)blockIdx.x * kK2Threads + threadIdx.x; g < groups;
        g += (size_t)gridDim.x * kK2Threads) {
-    const size_t base = g * 4;
-    const uint4 nv = ldg_nc_u32x4(ns_id + base);
-    const uint32_t ns[4] = {nv.x, nv.y, nv.z, nv.w};
-    long long q[R][4];
+    const size_t base = g * PODS;
+    uint32_t ns[PODS];
+    long long q[R][PODS];
+    ldg_ns<PODS>(ns_id + base, ns);
 #pragma unroll
-    for (int r = 0; r < R; ++r) ldg_nc_i64x4(req.p[r] + base, q[r]);
+    for (int r = 0; r < R; ++r) ldg_req<PODS>(req.p[r] + base, q[r]);
     uint32_t rm = 0xFFFFFFFFu;
-    if (HAS_MASK) rm = __ldg(reinterpret_cast<const uint32_t*>(req_mask + base));
-    uint32_t out = 0;
+    if (HAS_MASK) {
+      if constexpr (PODS == 4) rm = __ldg(reinterpret_cast<const uint32_t*>(req_mask + base));
+      else rm = __ldg(reinterpret_cast<const unsigned short*>(req_mask + base));
+    }
+    VT out[PODS];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < PODS; ++k) {
       long long qk[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) qk[r] = q[r][k];
-      out |= quota_verdict<R>(ns[k], qk, (rm >> (8 * k)) & 0xFFu, rows, hard_mask, NS, compute_mask)
-             << (8 * k);
+      out[k] = (VT)quota_verdict<R, SHIFT>(ns[k], qk, (rm >> (8 * k)) & 0xFFu, head, hard_mask, NS, compute_mask);
     }
-    *reinterpret_cast<uint32_t*>(verdict + base) = out;
+    if constexpr (sizeof(VT) * PODS == 8) {
+      *reinterpret_cast<uint2*>(verdict + base) =
+          make_uint2((uint32_t)out[0] | ((uint32_t)out[1] << 16), (uint32_t)out[2] | ((uint32_t)out[3] << 16));
+    } else if constexpr (sizeof(VT) * PODS == 4) {
+      uint32_t w = 0;
+#pragma unroll
+      for (int k = 0; k < PODS; ++k) w |= (uint32_t)out[k] << (8 * sizeof(VT) * k);
+      *reinterpret_cast<uint32_t*>(verdict + base) = w;
+    } else {
+      *reinterpret_cast<unsigned short*>(verdict + base) = (unsigned short)((uint32_t)out[0] | ((uint32_t)out[1] << 8));
+    }
   }
-  for (size_t i = groups * 4 + (size_t)blockIdx.x * kK2Threads + threadIdx.x; i < n;
+  for (size_t i = groups * PODS + (size_t)blockIdx.x * kK2Threads + threadIdx.x; i < n;
        i += (size_t)gridDim.x * kK2Threads) {
     long long qk[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) qk[r] = req.p[r][i];
     const uint32_t rm = HAS_MASK ? req_mask[i] : 0xFFu;
-    verdict[i] = (uint8_t)quota_verdict<R>(ns_id[i], qk, rm, rows, hard_mask, NS, compute_mask);
+    verdict[i] = (VT)quota_verdict<R, SHIFT>(ns_id[i], qk, rm, head, hard_mask, NS, compute_mask);
   }
 }
 

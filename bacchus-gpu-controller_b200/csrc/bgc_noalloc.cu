@@ -20,7 +20,7 @@
 //     device performs a one-time set-up — it asks the runtime for the device address of the
 //     static array (cudaGetSymbolAddress) and opts the kernels into large shared memory.  Make
 //     that first call before starting any stream capture on that device.
-//   * ns_count above BGC_STATIC_MAX_NS (or R outside 1..BGC_MAX_R) is rejected with BGC_E_BADARG
+//   * ns_count above BGC_STATIC_MAX_NS (or R outside 1..4) is rejected with BGC_E_BADARG
 //     and a message in `errbuf`; nothing is launched.
 //   * Every call on a device shares the one array, and the array keeps whatever the previous call
 //     left in it.  Each call therefore first clears the slots it is about to use; but two calls
@@ -38,12 +38,13 @@ using namespace bgc;
 namespace {
 
 constexpr int kMaxDevices = 64;
+constexpr int kStaticMaxR = 4;  // columns the static table is sized for
 constexpr size_t kStaticSmemBudget = 200 * 1024;
 
 // The scratch itself: the [R][ns_count] usage table the kernel accumulates into.  In HOST code the
 // name `g_static_used` is only a handle for the runtime (a host-side shadow symbol), not a device
 // address; kernels must be given the pointer obtained from cudaGetSymbolAddress below.
-static __device__ __align__(256) long long g_static_used[(size_t)BGC_STATIC_MAX_NS * kMaxR];
+static __device__ __align__(256) long long g_static_used[(size_t)BGC_STATIC_MAX_NS * kStaticMaxR];
 
 struct PerDevice {
   bool ready = false;
@@ -134,8 +135,8 @@ extern "C" int bgc_usage_reduce_static_dev(const uint32_t* d_ns_id, const int64_
                                            size_t n, uint32_t ns_count, unsigned flags, int64_t* d_used_out,
                                            void* cuda_stream, char* errbuf, size_t errbuf_len) {
   if (errbuf && errbuf_len) errbuf[0] = 0;
-  if (R < 1 || R > BGC_MAX_R)
-    return say(errbuf, errbuf_len, BGC_E_BADARG, "R = %u is outside 1..%d", R, BGC_MAX_R);
+  if (R < 1 || R > (uint32_t)kStaticMaxR)
+    return say(errbuf, errbuf_len, BGC_E_BADARG, "R = %u is outside 1..%d", R, kStaticMaxR);
   if (ns_count < 1 || ns_count > BGC_STATIC_MAX_NS)
     return say(errbuf, errbuf_len, BGC_E_BADARG,
                "ns_count = %u exceeds the static table (BGC_STATIC_MAX_NS = %d namespaces); use bgc_usage_reduce_dev",
@@ -144,7 +145,7 @@ extern "C" int bgc_usage_reduce_static_dev(const uint32_t* d_ns_id, const int64_
     return say(errbuf, errbuf_len, BGC_E_BADARG, "null pointer argument");
   if (flags & BGC_REDUCE_ACCUMULATE)
     return say(errbuf, errbuf_len, BGC_E_BADARG, "BGC_REDUCE_ACCUMULATE is not supported: the table is cleared on every call");
-  const long long* cols[kMaxR] = {nullptr, nullptr, nullptr, nullptr};
+  const long long* cols[kMaxR] = {};
   for (uint32_t r = 0; r < R && n; ++r) {
     if (!d_req[r]) return say(errbuf, errbuf_len, BGC_E_BADARG, "null request column %u", r);
     cols[r] = reinterpret_cast<const long long*>(d_req[r]);

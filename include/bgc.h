@@ -36,7 +36,8 @@ extern "C" {
 #define BGC_E_OOM (-3)    /* device or pinned-host allocation failed */
 #define BGC_E_STATE (-4)  /* call order: quota table not set before reduce/eval */
 
-#define BGC_MAX_R 4 /* resources per pod handled by the u8 verdict encoding */
+#define BGC_MAX_R 8  /* resources per pod: up to 4 with u8 verdicts, up to 8 with u16 verdicts */
+#define BGC_MAX_R8 4 /* widest R of the u8 verdict encoding */
 
 /* ---- row A1/A2: decision codes of the batched form of mutate() --------------------------- */
 /* op: kube-core `Operation` as matched at src/admission.rs:272-310 */
@@ -85,7 +86,8 @@ enum {
 enum { BGC_UNIT_COUNT = 0, BGC_UNIT_MILLI = 1, BGC_UNIT_BYTES = 2 };
 
 #define BGC_VERDICT_ALLOW 0x00u
-#define BGC_VERDICT_BAD_NS 0xFFu /* ns_id >= NS */
+#define BGC_VERDICT_BAD_NS 0xFFu     /* ns_id >= NS (u8 form) */
+#define BGC_VERDICT16_BAD_NS 0xFFFFu /* ns_id >= NS (u16 form) */
 /* verdict = missing << 4 | exceeded, one bit per resource r < R.
  * exceeded bit r: namespace constrains r, the pod states r, req > 0 and used + req > hard, decided
  * without 64-bit overflow (as Kubernetes' Quantity arithmetic would);
@@ -156,13 +158,20 @@ int bgc_quota_eval(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *re
                    const uint8_t *req_mask, size_t n, uint8_t *verdict);
 int bgc_quota_eval_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
                        const uint8_t *d_req_mask, size_t n, uint8_t *d_verdict);
+/* u16 form for up to 8 resources — e.g. the six pod-relevant keys of src/synchronizer.rs:249-281 in
+ * one pass: verdict = missing << 8 | exceeded.  Works for any R <= BGC_MAX_R; the
+ * u8 entry points above refuse R > 4. */
+int bgc_quota_eval16(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *req,
+                     const uint8_t *req_mask, size_t n, uint16_t *verdict);
+int bgc_quota_eval16_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
+                         const uint8_t *d_req_mask, size_t n, uint16_t *d_verdict);
 
 /* ---- row N1: K3 admit_greedy — sequential admission inside one batch -----------
  * No reference function; this is what kube-apiserver does one pod at a time against the
  * ResourceQuota the reference writes (src/controller.rs:89-110): per namespace, in arrival order, a
  * pod is admitted iff its verdict (same encoding and rules as bgc_quota_eval) against the CURRENT
  * usage is 0, and only admitted pods add their requests to the usage table, which is updated in
- * place.  Order-dependent, so the checker is the literal loop.  n < 2^31. */
+ * place.  Order-dependent, so the checker is the literal loop.  n < 2^31, R <= 4. */
 int bgc_admit_greedy(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *req,
                      const uint8_t *req_mask, size_t n, uint8_t *verdict);
 int bgc_admit_greedy_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
@@ -176,7 +185,7 @@ int bgc_admit_greedy_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *c
  * array of BGC_STATIC_MAX_NS namespaces (512 KiB per GPU, held from library load to process exit).
  *   - runs on the CURRENT device, on `cuda_stream`; inputs and d_used_out ([R][ns_count]) are
  *     device pointers owned by the caller;
- *   - ns_count > BGC_STATIC_MAX_NS or R outside 1..BGC_MAX_R → BGC_E_BADARG, message in errbuf
+ *   - ns_count > BGC_STATIC_MAX_NS or R outside 1..4 → BGC_E_BADARG, message in errbuf
  *     (errbuf may be NULL);
  *   - the first call on a device does a one-time set-up (resolves the array's device address);
  *     make that call before any stream capture on the device;

@@ -50,7 +50,7 @@ class PolicyDecision(C.Structure):
 class GenParams(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("set", C.c_uint32), ("ns_count", C.c_uint32), ("dist", C.c_uint32),
                 ("grouped", C.c_uint32), ("n_total", C.c_uint64), ("scramble_a", C.c_uint64),
-                ("scramble_b", C.c_uint64), ("cdf", C.c_void_p), ("R", C.c_uint32), ("kind", C.c_uint32 * 4)]
+                ("scramble_b", C.c_uint64), ("cdf", C.c_void_p), ("R", C.c_uint32), ("kind", C.c_uint32 * 8)]
 
 
 def lib():
@@ -171,6 +171,16 @@ def admit_greedy(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask):
     lib().quota_ref_admit_greedy(_p(ns_id), _ptrs(req), _p(req_mask), C.c_size_t(n), C.c_uint32(NS), C.c_uint32(R), _p(u),
                                  _p(np.ascontiguousarray(hard)), _p(hard_mask), C.c_uint8(compute_mask), _p(verdict))
     return verdict, u
+
+
+def quota_eval16(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask, threads: int = 1):
+    R = len(req)
+    n = ns_id.shape[0]
+    verdict = np.empty(n, np.uint16)
+    lib().quota_ref_quota_eval16(_p(ns_id), _ptrs(req), _p(req_mask), C.c_size_t(n), C.c_uint32(NS), C.c_uint32(R),
+                                 _p(np.ascontiguousarray(used)), _p(np.ascontiguousarray(hard)), _p(hard_mask),
+                                 C.c_uint8(compute_mask), _p(verdict), C.c_int(threads))
+    return verdict
 
 
 def gen_params(seed, set_, NS, dist, grouped, n_total, a, b, cdf, kinds):

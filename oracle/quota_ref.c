@@ -50,10 +50,11 @@ void quota_ref_usage_reduce(const uint32_t *ns_id, const int64_t *const *req, si
 #endif
 }
 
-static inline uint8_t eval_one(uint32_t ns, const int64_t *const *req, uint8_t rmask, size_t j,
-                               uint32_t NS, uint32_t R, const int64_t *used, const int64_t *hard,
-                               const uint8_t *hard_mask, uint8_t compute_mask) {
-  if (ns >= NS) return QUOTA_REF_VERDICT_BAD_NS;
+/* returns missing | exceeded << 8 (or 0xFFFFFFFF for an unknown namespace); the callers pack it */
+static inline uint32_t eval_bits(uint32_t ns, const int64_t *const *req, uint8_t rmask, size_t j,
+                                 uint32_t NS, uint32_t R, const int64_t *used, const int64_t *hard,
+                                 const uint8_t *hard_mask, uint8_t compute_mask) {
+  if (ns >= NS) return 0xFFFFFFFFu;
   const uint8_t hm = hard_mask[ns];
   unsigned missing = 0, exceeded = 0;
   for (uint32_t r = 0; r < R; ++r) {
@@ -68,7 +69,15 @@ static inline uint8_t eval_one(uint32_t ns, const int64_t *const *req, uint8_t r
     const __int128 total = (__int128)used[(size_t)r * NS + ns] + (__int128)q;
     if (total > (__int128)hard[(size_t)r * NS + ns]) exceeded |= 1u << r;
   }
-  return (uint8_t)((missing << 4) | exceeded);
+  return missing | (exceeded << 8);
+}
+
+static inline uint8_t eval_one(uint32_t ns, const int64_t *const *req, uint8_t rmask, size_t j,
+                               uint32_t NS, uint32_t R, const int64_t *used, const int64_t *hard,
+                               const uint8_t *hard_mask, uint8_t compute_mask) {
+  const uint32_t b = eval_bits(ns, req, rmask, j, NS, R, used, hard, hard_mask, compute_mask);
+  if (b == 0xFFFFFFFFu) return QUOTA_REF_VERDICT_BAD_NS;
+  return (uint8_t)(((b & 0xFF) << 4) | (b >> 8));
 }
 
 void quota_ref_quota_eval(const uint32_t *ns_id, const int64_t *const *req,
@@ -82,6 +91,20 @@ void quota_ref_quota_eval(const uint32_t *ns_id, const int64_t *const *req,
   for (long long j = 0; j < (long long)n; ++j)
     verdict[j] = eval_one(ns_id[j], req, req_mask ? req_mask[j] : 0xFF, (size_t)j, NS, R, used,
                           hard, hard_mask, compute_mask);
+}
+
+void quota_ref_quota_eval16(const uint32_t *ns_id, const int64_t *const *req,
+                            const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
+                            const int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
+                            uint8_t compute_mask, uint16_t *verdict, int threads) {
+  (void)threads;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthreads(threads))
+#endif
+  for (long long j = 0; j < (long long)n; ++j) {
+    const uint32_t b = eval_bits(ns_id[j], req, req_mask ? req_mask[j] : 0xFF, (size_t)j, NS, R, used, hard, hard_mask, compute_mask);
+    verdict[j] = b == 0xFFFFFFFFu ? 0xFFFF : (uint16_t)(((b & 0xFF) << 8) | (b >> 8));
+  }
 }
 
 void quota_ref_admit_greedy(const uint32_t *ns_id, const int64_t *const *req,

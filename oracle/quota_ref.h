@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define QUOTA_REF_MAX_R 4
+#define QUOTA_REF_MAX_R 8
 #define QUOTA_REF_VERDICT_BAD_NS 0xFFu
 
 /* A3: used[r][ns] = sum over pods i with ns_id[i]==ns of req[r][i], wrapping 64-bit.
@@ -40,6 +40,12 @@ void quota_ref_quota_eval(const uint32_t *ns_id, const int64_t *const *req,
                           const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
                           const int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
                           uint8_t compute_mask, uint8_t *verdict, int threads);
+
+/* The u16 form for up to 8 resources: verdict = (missing<<8)|exceeded, unknown namespace 0xFFFF. */
+void quota_ref_quota_eval16(const uint32_t *ns_id, const int64_t *const *req,
+                            const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
+                            const int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
+                            uint8_t compute_mask, uint16_t *verdict, int threads);
 
 /* N1: Kubernetes-faithful sequential admission inside one batch.  Pods are taken
  * in arrival order; pod j is admitted iff its verdict — computed exactly like quota_ref_quota_eval

@@ -23,7 +23,7 @@ def usage_reduce(ns_id: np.ndarray, req: list, NS: int) -> np.ndarray:
     return used
 
 
-def quota_eval(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask) -> np.ndarray:
+def quota_eval(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask, wide: bool = False) -> np.ndarray:
     R = len(req)
     n = ns_id.shape[0]
     bad = ns_id >= NS
@@ -43,6 +43,10 @@ def quota_eval(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask) ->
         overflow = (req[r] > 0) & (total < u)       # true sum > INT64_MAX >= hard
         ex = constrained & present & (req[r] > 0) & (overflow | (total > hard[r][ns]))
         exceeded |= (ex.astype(np.uint8) << r)
+    if wide:   # u16 form, up to 8 resources
+        out = ((missing.astype(np.uint16) << 8) | exceeded).astype(np.uint16)
+        out[bad] = 0xFFFF
+        return out
     out = ((missing << 4) | exceeded).astype(np.uint8)
     out[bad] = VERDICT_BAD_NS
     return out

@@ -188,7 +188,7 @@ def test_errors_are_reported_not_thrown(bgc, engine):
         engine.usage_get()
     assert e.value.code == bgc.E_STATE
     with pytest.raises(bgc.BgcError) as e:
-        bgc.Engine(0).quota_table_set(np.zeros((5, NS), np.int64), np.zeros(NS, np.uint8), [0] * 5)
+        bgc.Engine(0).quota_table_set(np.zeros((9, NS), np.int64), np.zeros(NS, np.uint8), [0] * 9)
     assert e.value.code == bgc.E_BADARG
     engine.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), [0, 1])
     with pytest.raises(ValueError):

@@ -9,8 +9,13 @@ from __future__ import annotations
 import numpy as np
 
 SEEDS = {"C1": 0xB2000001, "C2": 0xB2000002, "C3": 0xB2000003, "C4": 0xB2000004, "C5": 0xB2000005}
-KINDS = {2: [0, 1], 3: [0, 1, 2], 1: [1], 4: [0, 1, 2, 3]}         # gpu, cpu, memory, mig
-UNITS = {2: [0, 1], 3: [0, 1, 2], 1: [1], 4: [0, 1, 2, 0]}         # COUNT, MILLI, BYTES
+# generator kinds: 0 gpu, 1 cpu millicores, 2 memory bytes, 3 mig; units: 0 COUNT, 1 MILLI, 2 BYTES.
+# R = 6 is the pod-relevant key set of src/synchronizer.rs:249-281 (requests.* and limits.* for cpu/memory)
+KINDS = {1: [1], 2: [0, 1], 3: [0, 1, 2], 4: [0, 1, 2, 3], 5: [0, 1, 2, 3, 1], 6: [0, 1, 2, 3, 1, 2],
+         7: [0, 1, 2, 3, 1, 2, 0], 8: [0, 1, 2, 3, 1, 2, 0, 3]}
+UNITS = {1: [1], 2: [0, 1], 3: [0, 1, 2], 4: [0, 1, 2, 0], 5: [0, 1, 2, 0, 1], 6: [0, 1, 2, 0, 1, 2],
+         7: [0, 1, 2, 0, 1, 2, 0], 8: [0, 1, 2, 0, 1, 2, 0, 0]}
+C1_KEYS6 = ["requests.nvidia.com/gpu", "requests.cpu", "requests.memory", "requests.nvidia.com/mig-1g.10gb", "limits.cpu", "limits.memory"]
 
 
 def _sm64(x):
