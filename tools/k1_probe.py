@@ -46,7 +46,7 @@ def main():
     cases = [  # (NS, R, dist, s, grouped)
         (10_000, 3, 1, 1.1, 0), (10_000, 3, 0, 0, 0), (10_000, 3, 1, 1.1, 1), (10_000, 2, 0, 0, 0),
         (100, 3, 1, 1.1, 0), (1_000_000, 3, 1, 1.1, 0), (1_000_000, 3, 0, 0, 0), (10_000, 3, 1, 1.5, 0),
-        (125_000, 3, 1, 1.1, 0), (500_000, 3, 1, 1.1, 0), (20_000, 3, 1, 1.1, 0), (50_000, 3, 0, 0, 0), (125_000, 3, 0, 0, 0), (200_000, 3, 1, 1.1, 0), (10_000, 4, 1, 1.1, 0), (10_000, 1, 1, 1.1, 0),
+        (125_000, 3, 1, 1.1, 0), (500_000, 3, 1, 1.1, 0), (20_000, 3, 1, 1.1, 0), (50_000, 3, 0, 0, 0), (125_000, 3, 0, 0, 0), (200_000, 3, 1, 1.1, 0), (10_000, 4, 1, 1.1, 0), (10_000, 1, 1, 1.1, 0), (5_000, 6, 1, 1.1, 0), (10_001, 6, 1, 1.1, 0), (10_001, 8, 0, 0, 0),
     ]
     if args.cases != "all":
         cases = [c for c in cases if str(c[0]) in args.cases.split(",")]
@@ -81,9 +81,9 @@ def main():
         hard, hm = make_hard(ref, 1)
         eng.quota_table_set(hard, hm, UNITS[R])
         eng.usage_set(ref)
-        v = torch.empty(n, dtype=torch.uint8, device="cuda")
+        v = torch.empty(n, dtype=torch.uint8 if R <= 4 else torch.int16, device="cuda")
         ms = timeit(lambda: eng.quota_eval_dev(ns, req, None, v))
-        gbs = n * (5 + 8 * R) / ms / 1e6
+        gbs = n * (4 + 8 * R + (1 if R <= 4 else 2)) / ms / 1e6
         print(json.dumps({"kernel": "k2", "NS": NS, "R": R, "dist": "zipf%.1f" % s if dist else "uniform", "ms": round(ms, 4),
                           "GBps": round(gbs, 1), "frac": round(gbs / PEAK, 3), "deny": float((v[: 1 << 20] != 0).float().mean())}), flush=True)
         del ns, req, v
