@@ -423,40 +423,66 @@ int bgc_flatten_pods(const bgc_pod_spec* pods, size_t n, const char* const* quot
     else if (std::strncmp(k, "requests.", 9) == 0) keys[r] = {false, k + 9};
     else keys[r] = {false, k};
   }
-  size_t w = 0;
-  for (size_t i = 0; i < n; ++i) {
+  // Phase 1 (parallel when the namespace map is read-only): every pod's row is computed in place at
+  // its own index; phase 2 compacts away the terminal pods sequentially.
+  std::vector<uint8_t> keep(n, 0);
+  int first_error = BGC_OK;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) if (n >= 2048 && !intern)
+#endif
+  for (long long ii = 0; ii < (long long)n; ++ii) {
+    const size_t i = (size_t)ii;
     const bgc_pod_spec& pod = pods[i];
     if (pod.phase == BGC_PHASE_SUCCEEDED || pod.phase == BGC_PHASE_FAILED) continue;  // terminal pods hold no quota
     unsigned mask = 0;
-    for (uint32_t r = 0; r < R; ++r) {
+    int err = BGC_OK;
+    for (uint32_t r = 0; r < R && !err; ++r) {
       bool all_state = true;
       uint64_t app = 0;
       int64_t init_max = 0;
-      for (size_t c = 0; c < pod.n_containers; ++c) {
+      for (size_t c = 0; c < pod.n_containers && !err; ++c) {
         int64_t v; bool found;
         const bgc_resource_list& l = keys[r].limits ? pod.containers[c].limits : pod.containers[c].requests;
-        if (int rc = sum_list(l, keys[r].name, unit[r], &v, &found)) return rc;
+        err = sum_list(l, keys[r].name, unit[r], &v, &found);
         all_state = all_state && found;
         app += (uint64_t)v;
       }
-      for (size_t c = 0; c < pod.n_init_containers; ++c) {
+      for (size_t c = 0; c < pod.n_init_containers && !err; ++c) {
         int64_t v; bool found;
         const bgc_resource_list& l = keys[r].limits ? pod.init_containers[c].limits : pod.init_containers[c].requests;
-        if (int rc = sum_list(l, keys[r].name, unit[r], &v, &found)) return rc;
+        err = sum_list(l, keys[r].name, unit[r], &v, &found);
         all_state = all_state && found;
         if (v > init_max) init_max = v;
       }
       int64_t total = (int64_t)app > init_max ? (int64_t)app : init_max;
-      if (pod.overhead) {
+      if (pod.overhead && !err) {
         int64_t v; bool found;
-        if (int rc = sum_list(*pod.overhead, keys[r].name, unit[r], &v, &found)) return rc;
+        err = sum_list(*pod.overhead, keys[r].name, unit[r], &v, &found);
         total = (int64_t)((uint64_t)total + (uint64_t)v);
       }
-      req[r][w] = total;
+      req[r][i] = total;
       if (all_state && pod.n_containers + pod.n_init_containers > 0) mask |= 1u << r;
     }
-    ns_id[w] = intern ? bgc_nsmap_intern(map, pod.ns) : bgc_nsmap_lookup(map, pod.ns);
-    if (req_mask) req_mask[w] = (uint8_t)mask;
+    if (err) {
+#ifdef _OPENMP
+#pragma omp critical
+#endif
+      if (!first_error) first_error = err;
+      continue;
+    }
+    ns_id[i] = intern ? bgc_nsmap_intern(map, pod.ns) : bgc_nsmap_lookup(map, pod.ns);
+    if (req_mask) req_mask[i] = (uint8_t)mask;
+    keep[i] = 1;
+  }
+  if (first_error) return first_error;
+  size_t w = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (!keep[i]) continue;
+    if (w != i) {
+      ns_id[w] = ns_id[i];
+      for (uint32_t r = 0; r < R; ++r) req[r][w] = req[r][i];
+      if (req_mask) req_mask[w] = req_mask[i];
+    }
     ++w;
   }
   *n_out = w;
