@@ -1,0 +1,64 @@
+/* examples/mutate_batch.c — the C ABI from plain C: a batch of UserBootstrap admission requests is
+ * flattened on the host, decided on the GPU and printed; then a handful of pods are checked against a
+ * quota table.  Build (after `make -C bacchus-gpu-controller_b200/csrc`):
+ *   gcc -std=c99 -Iinclude examples/mutate_batch.c -Lbacchus-gpu-controller_b200 -lbgc \
+ *       -Wl,-rpath,$PWD/bacchus-gpu-controller_b200 -o /tmp/mutate_batch && /tmp/mutate_batch
+ * Needs a CUDA device: there is no CPU fallback (bgc_ctx_create fails with BGC_E_CUDA otherwise). */
+#include <stdio.h>
+
+#include "bgc.h"
+#include "bgc_host.h"
+
+int main(void) {
+  bgc_ctx *ctx = NULL;
+  int rc = bgc_ctx_create(0, &ctx);
+  if (rc != BGC_OK) {
+    fprintf(stderr, "bgc_ctx_create: %d (no CUDA device?)\n", rc);
+    return 2;
+  }
+  /* Config as the chart sets it (charts/bacchus-gpu-controller/values.yaml:84-89) */
+  const char *authorized[] = {"gpu", "admin"};
+  bgc_admission_config cfg = {"oidc:", "edit", authorized, 2};
+  const char *groups_gpu[] = {"system:authenticated", "gpu"};
+  const char *groups_none[] = {"system:authenticated"};
+  bgc_admission_request reqs[3] = {
+      {"oidc:alice", groups_gpu, 2, BGC_OP_CREATE, 1, "alice", 1, NULL, 0, 0},  /* allowed, patched */
+      {"oidc:bob", groups_none, 1, BGC_OP_CREATE, 1, "bob", 1, NULL, 0, 0},     /* not in an authorised group */
+      {"admin", NULL, 0, BGC_OP_DELETE, 0, NULL, 0, NULL, 0, 0},                /* admin delete */
+  };
+  bgc_admission_response out[3];
+  rc = bgc_mutate_batch(ctx, &cfg, reqs, 3, out);
+  if (rc != BGC_OK) {
+    fprintf(stderr, "bgc_mutate_batch: %s\n", bgc_last_error(ctx));
+    return 1;
+  }
+  for (int i = 0; i < 3; ++i) {
+    char patch[1024];
+    long n = bgc_render_patch(&cfg, &reqs[i], out[i].patch_mask, patch, sizeof patch);
+    printf("request %d: allowed=%d class=%d reason=%d message=%s patch=%s\n", i, out[i].allowed, out[i].klass,
+           out[i].reason, out[i].message ? out[i].message : "-", n > 0 ? patch : "-");
+  }
+
+  /* quota: 2 namespaces, 2 resources (gpu count, cpu millicores) */
+  const int64_t hard[2 * 2] = {/* gpu */ 2, 1, /* cpu */ 8000, 4000};
+  const uint8_t hard_mask[2] = {3, 3}, unit[2] = {BGC_UNIT_COUNT, BGC_UNIT_MILLI};
+  rc = bgc_quota_table_set(ctx, 2, 2, hard, hard_mask, unit);
+  const uint32_t run_ns[3] = {0, 0, 1};
+  const int64_t run_gpu[3] = {1, 0, 1}, run_cpu[3] = {2000, 4000, 1000};
+  const int64_t *run_req[2] = {run_gpu, run_cpu};
+  int64_t used[4];
+  if (rc == BGC_OK) rc = bgc_usage_reduce(ctx, run_ns, run_req, 3, 0, used);
+  const uint32_t cand_ns[3] = {0, 0, 1};
+  const int64_t cand_gpu[3] = {1, 2, 1}, cand_cpu[3] = {2000, 1000, 500};
+  const int64_t *cand_req[2] = {cand_gpu, cand_cpu};
+  uint8_t verdict[3];
+  if (rc == BGC_OK) rc = bgc_quota_eval(ctx, cand_ns, cand_req, NULL, 3, verdict);
+  if (rc != BGC_OK) {
+    fprintf(stderr, "quota path: %s\n", bgc_last_error(ctx));
+    return 1;
+  }
+  printf("used gpu=[%lld,%lld] cpu=[%lld,%lld]; verdicts = %u %u %u (0 = allow, bit r = resource r exceeded)\n",
+         (long long)used[0], (long long)used[1], (long long)used[2], (long long)used[3], verdict[0], verdict[1], verdict[2]);
+  bgc_ctx_destroy(ctx);
+  return 0;
+}

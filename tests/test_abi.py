@@ -58,3 +58,44 @@ def test_product_never_imports_oracle():
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert not re.search(r"import\s+oracle|from\s+oracle|oracle/|liboracle|_ref\.(c|h|py)", text), \
                     f"{f} reaches into oracle/"
+
+
+def test_headers_are_plain_c(tmp_path):
+    """The boundary is a C ABI: every header must compile as C99 (not only as C++), and the C example links."""
+    import subprocess
+    src = tmp_path / "all_headers.c"
+    src.write_text('#include "bgc.h"\n#include "bgc_host.h"\n#include "bgc_synth.h"\nint main(void) { return BGC_OK; }\n')
+    r = subprocess.run(["/usr/bin/gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-fsyntax-only",
+                        "-I", os.path.join(ROOT, "include"), str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    exe = tmp_path / "mutate_batch"
+    r = subprocess.run(["/usr/bin/gcc", "-std=c99", "-Wall", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "examples", "mutate_batch.c"),
+                        "-L", os.path.join(ROOT, "bacchus-gpu-controller_b200"), "-lbgc",
+                        "-Wl,-rpath," + os.path.join(ROOT, "bacchus-gpu-controller_b200"), "-o", str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    import torch
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert out.returncode == 0, out.stderr
+        assert "request 0: allowed=1 class=1" in out.stdout and "user is not in authorized group" in out.stdout
+        assert "verdicts = 0 1 1" in out.stdout
+    else:
+        assert out.returncode == 2          # no device: fails loudly, no CPU fallback
+
+
+import pytest  # noqa: E402
+
+
+@pytest.mark.gpu
+def test_c_example_runs_on_the_device(tmp_path):
+    import subprocess
+    exe = tmp_path / "mutate_batch"
+    r = subprocess.run(["/usr/bin/gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "examples", "mutate_batch.c"),
+                        "-L", os.path.join(ROOT, "bacchus-gpu-controller_b200"), "-lbgc",
+                        "-Wl,-rpath," + os.path.join(ROOT, "bacchus-gpu-controller_b200"), "-o", str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert "request 0: allowed=1 class=1" in out.stdout and "user is not in authorized group" in out.stdout
+    assert "request 2: allowed=1 class=0 reason=12" in out.stdout
+    assert "used gpu=[1,1] cpu=[6000,1000]; verdicts = 0 1 1" in out.stdout
