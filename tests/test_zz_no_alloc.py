@@ -4,7 +4,7 @@ Some users of libbgc.so run where device allocation at call time is off the tabl
 process gave every byte of HBM to its own pool at start-up (a library's cudaMalloc would fail or
 steal budgeted memory), or the call sits on a latency-critical path where cudaMalloc/cudaFree would
 stall all streams with their device-wide synchronisation.  For them the library offers one entry
-point that accumulates into a fixed 1 MiB static device table instead of allocated memory.
+point that accumulates into a fixed 512 KiB static device table instead of allocated memory.
 
 What is checked here, through the C ABI: the static-table result is bit-identical to the regular
 bgc_usage_reduce_dev on the same device columns, on two calls in a row with different inputs (the
