@@ -1,0 +1,100 @@
+#!/usr/bin/env python
+"""Randomised soak test: random shapes, value ranges, K1 variants, hints, masks and pointer offsets,
+every result compared bit for bit with the CPU oracle.  Usage: python tools/fuzz_gpu.py [--seconds S] [--seed N]"""
+import argparse, importlib, os, sys, time
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import oracle
+from workloads import UNITS, make_hard
+bgc = importlib.import_module("bacchus-gpu-controller_b200")
+
+ap = argparse.ArgumentParser(); ap.add_argument("--seconds", type=float, default=60); ap.add_argument("--seed", type=int, default=1)
+args = ap.parse_args()
+eng = bgc.Engine(0); eng.use_torch_stream()
+t_end = time.time() + args.seconds
+it = 0
+stats = {}
+while time.time() < t_end:
+    seed = args.seed * 1_000_003 + it
+    rng = np.random.default_rng(seed)
+    it += 1
+    R = int(rng.integers(1, 9))
+    NS = int(np.exp(rng.uniform(0, np.log(300_000))))
+    n = int(np.exp(rng.uniform(0, np.log(400_000))))
+    mode = rng.integers(0, 4)
+    if mode == 0:
+        ns = rng.integers(0, NS, n, dtype=np.uint32)
+    elif mode == 1:      # skewed
+        ns = (rng.zipf(1.3, n) % NS).astype(np.uint32)
+    elif mode == 2:      # runs of random length
+        lens = rng.geometric(1.0 / max(1, int(rng.integers(1, 600))), n)
+        ns = np.repeat(rng.integers(0, NS, n, dtype=np.uint32), lens)[:n]
+    else:                # few hot namespaces
+        ns = rng.choice(rng.integers(0, NS, 3, dtype=np.uint32), n)
+    if rng.random() < 0.3 and n > 4:
+        ns[rng.integers(0, n, max(1, n // 50))] = rng.choice(np.array([NS, NS + 7, 0xFFFFFFFF], np.uint32))
+    vmode = rng.integers(0, 4)
+    def col():
+        if vmode == 0: return rng.integers(0, 1 << 12, n, dtype=np.int64)
+        if vmode == 1: return rng.integers(0, 1 << 40, n, dtype=np.int64)
+        if vmode == 2: return rng.integers(-2**63, 2**63 - 1, n, dtype=np.int64)
+        return rng.integers(-1000, 1 << 33, n, dtype=np.int64)
+    req = [col() for _ in range(R)]
+    for c in req:
+        c[rng.random(n) < 0.3] = 0
+    mask = rng.integers(0, 256, n, dtype=np.uint8) if rng.random() < 0.5 else None
+    units = list(rng.integers(0, 3, R))
+    cm = sum(1 << r for r, u in enumerate(units) if u)
+    want = oracle.usage_reduce(ns, req, NS, threads=4)
+    hard, hm = make_hard(want, seed)
+    if rng.random() < 0.5:
+        hm = rng.integers(0, 1 << R, NS, dtype=np.uint8)
+    eng.quota_table_set(hard, hm, units)
+    variant = int(rng.choice([0, 1, 2, 3, 2 | (1 << 8), 2 | (2 << 8), 2 | (3 << 8), 3 | (1 << 8), 3 | (3 << 8), 4, 5]))
+    if R > 4 and (variant >> 8):
+        variant &= 0xFF
+    flags = int(rng.integers(0, 2))
+    eng.set_k1_variant(variant)
+    key = None
+    try:
+        off = int(rng.integers(0, 4)) if n > 8 else 0
+        if rng.random() < 0.5:   # host path
+            got = eng.usage_reduce(ns, req, flags=flags)
+        else:                    # device path with an element offset (misaligned columns)
+            d_ns = torch.from_numpy(np.concatenate([np.zeros(off, np.uint32), ns]).view(np.int32)).cuda()
+            d_req = [torch.from_numpy(np.concatenate([np.zeros(off, np.int64), c])).cuda() for c in req]
+            d_used = torch.empty(R * NS, dtype=torch.int64, device="cuda")
+            eng.usage_reduce_dev(d_ns[off:], [c[off:] for c in d_req], flags, d_used)
+            torch.cuda.synchronize()
+            got = d_used.cpu().numpy().reshape(R, NS)
+        key = eng.last_k1_variant()
+    except bgc.BgcError as e:
+        if "does not fit" in str(e):
+            eng.set_k1_variant(0)
+            got = eng.usage_reduce(ns, req, flags=flags)
+            key = eng.last_k1_variant()
+        else:
+            raise
+    assert np.array_equal(got, want), f"K1 mismatch seed={seed} R={R} NS={NS} n={n} variant={variant} flags={flags} {key}"
+    stats[key] = stats.get(key, 0) + 1
+    w16 = oracle.quota_eval16(ns, req, mask, NS, want, hard, hm, cm, threads=4)
+    assert np.array_equal(eng.quota_eval(ns, req, mask, wide=True), w16), f"K2/16 mismatch seed={seed}"
+    if R <= 4:
+        w8 = oracle.quota_eval(ns, req, mask, NS, want, hard, hm, cm, threads=4)
+        assert np.array_equal(eng.quota_eval(ns, req, mask), w8), f"K2/8 mismatch seed={seed}"
+        if it % 3 == 0:
+            h2 = hard + np.abs(hard) // 4 + 100
+            eng.quota_table_set(h2, hm, units); eng.usage_set(want)
+            gv, gu = oracle.admit_greedy(ns, req, mask, NS, want, h2, hm, cm)
+            assert np.array_equal(eng.admit_greedy(ns, req, mask), gv), f"K3 verdict mismatch seed={seed} R={R} NS={NS} n={n}"
+            assert np.array_equal(eng.usage_get(), gu), f"K3 usage mismatch seed={seed}"
+            stats["k3"] = stats.get("k3", 0) + 1
+    if it % 5 == 0:
+        m = int(rng.integers(1, 200_000))
+        op = rng.integers(0, 256, m, dtype=np.uint8); fl = rng.integers(0, 65536, m, dtype=np.uint16)
+        c, p = eng.policy_eval(op, fl)
+        rc, rp = oracle.policy_bits(np.minimum(op, 3).astype(np.uint8), (fl & 1023).astype(np.uint16), 4)
+        assert np.array_equal(c, rc) and np.array_equal(p, rp), f"K0 mismatch seed={seed}"
+        stats["k0"] = stats.get("k0", 0) + 1
+print(f"fuzz ok: {it} random cases in {args.seconds:.0f} s, seed base {args.seed}; coverage {stats}")
