@@ -769,6 +769,15 @@ int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   int rc;
   if (!(flags & BGC_REDUCE_ACCUMULATE) && (rc = clear_used(ctx, ctx->own_stream))) return rc;
+  // The columns are in host memory here, so the grouping hint can be inferred for free: 1,024
+  // evenly spaced neighbour pairs; if nearly all of them share a namespace the segmented kernel is
+  // the right one.  Either kernel is exact for any input — this only picks the faster.
+  if (!(flags & BGC_REDUCE_GROUPED) && ctx->k1_forced == BGC_K1_AUTO && n >= 4096) {
+    const size_t step = (n - 1) / 1024;
+    size_t same = 0;
+    for (size_t k = 0; k < 1024; ++k) same += ns_id[k * step] == ns_id[k * step + 1];
+    if (same >= 1000) flags |= BGC_REDUCE_GROUPED;
+  }
   Spans sp;
   if (n) {
     if ((rc = ensure_slots(ctx, n, R))) return rc;

@@ -95,7 +95,8 @@ enum { BGC_UNIT_COUNT = 0, BGC_UNIT_MILLI = 1, BGC_UNIT_BYTES = 2 };
  * not state it (req_mask bit clear).  0 = allow. */
 
 /* flags of bgc_usage_reduce* */
-#define BGC_REDUCE_GROUPED 1u    /* hint: pods arrive grouped by namespace (any order of groups) */
+#define BGC_REDUCE_GROUPED 1u    /* hint: pods arrive grouped by namespace (any order of groups); the host-pointer
+                                    entry point infers it from a sample of the batch when not given */
 #define BGC_REDUCE_ACCUMULATE 2u /* add to the current usage table instead of zeroing it first */
 
 typedef struct bgc_ctx bgc_ctx;

@@ -360,3 +360,15 @@ def test_two_contexts_in_two_threads_do_not_interfere(bgc, oracle):
     for th in threads:
         th.join()
     assert not errors, errors
+
+
+def test_host_entry_point_infers_the_grouping_hint(engine, oracle):
+    R, NS, n = 3, 2000, 400_000
+    rng = np.random.default_rng(12)
+    req = [rng.integers(0, 1 << 30, n, dtype=np.int64) for _ in range(R)]
+    grouped = np.repeat(rng.permutation(NS).astype(np.uint32), n // NS)
+    shuffled = rng.permutation(grouped)
+    engine.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
+    for ns, expect in ((grouped, "segmented_global_red"), (shuffled, "scatter_smem_direct")):
+        assert np.array_equal(engine.usage_reduce(ns, req), oracle.usage_reduce(ns, req, NS, threads=4))
+        assert engine.last_k1_variant() == expect
