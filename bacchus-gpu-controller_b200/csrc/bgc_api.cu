@@ -502,9 +502,15 @@ int bgc_ctx_create(int device, bgc_ctx** out) {
   if (e == cudaSuccess) e = cudaMalloc(&ctx->d_scratch, 256 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaHostAlloc(&ctx->zc_host, kZeroCopyBytes, cudaHostAllocMapped);
   if (e == cudaSuccess) e = cudaHostGetDevicePointer(&ctx->zc_dev, ctx->zc_host, 0);
-  if (e != cudaSuccess) {
+  if (e != cudaSuccess) {  // release whatever was created before the failure
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    if (ctx->h2d_stream) cudaStreamDestroy(ctx->h2d_stream);
+    if (ctx->d2h_stream) cudaStreamDestroy(ctx->d2h_stream);
+    cudaFree(ctx->d_scratch);
+    cudaFreeHost(ctx->zc_host);
     delete ctx;
-    return BGC_E_CUDA;
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? BGC_E_OOM : BGC_E_CUDA;
   }
   ctx->stream = ctx->own_stream;
   if (const char* v = std::getenv("BGC_ZEROCOPY_MAX_PODS")) {
