@@ -131,8 +131,14 @@ int launch_k0(bgc_ctx* ctx, cudaStream_t st, const uint8_t* op, const uint16_t* 
               uint8_t* code, uint8_t* pm) {
   if (n == 0) return BGC_OK;
   const int vec = aligned(op, 32) && aligned(flags, 32) && aligned(code, 32) && aligned(pm, 32);
-  const int grid = grid_for((n + kK0PerThread - 1) / kK0PerThread, kK0Threads, ctx->sm_count * 8);
-  k0_policy_eval<<<grid, kK0Threads, 0, st>>>(op, flags, n, code, pm, vec);
+  // tuning knobs; measured on 2^30 requests: 8 CTAs/SM of grid-stride looping 88 % of the copy peak, 256 CTAs/SM
+  // (3-4 trips per thread) 105 %: a streaming kernel wants its resident CTAs to sweep memory as one front
+  static const int st_mode = std::getenv("BGC_K0_STORE") ? std::atoi(std::getenv("BGC_K0_STORE")) : 0;
+  static const int blocks_per_sm = std::getenv("BGC_K0_BLOCKS") ? std::atoi(std::getenv("BGC_K0_BLOCKS")) : 256;
+  const int grid = grid_for((n + kK0PerThread - 1) / kK0PerThread, kK0Threads, ctx->sm_count * blocks_per_sm);
+  if (st_mode == 1) k0_policy_eval<1><<<grid, kK0Threads, 0, st>>>(op, flags, n, code, pm, vec);
+  else if (st_mode == 2) k0_policy_eval<2><<<grid, kK0Threads, 0, st>>>(op, flags, n, code, pm, vec);
+  else k0_policy_eval<0><<<grid, kK0Threads, 0, st>>>(op, flags, n, code, pm, vec);
   ctx->tm.launches++;
   CU(cudaGetLastError());
   return BGC_OK;
@@ -338,7 +344,8 @@ int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
     CU(cudaGetLastError());
     ctx->head_stale = false;
   }
-  const int grid = grid_for((n + PODS - 1) / PODS, kK2Threads, ctx->sm_count * 8);
+  static const int k2_blocks = std::getenv("BGC_K2_BLOCKS") ? std::atoi(std::getenv("BGC_K2_BLOCKS")) : 32;  // tuning knob
+  const int grid = grid_for((n + PODS - 1) / PODS, kK2Threads, ctx->sm_count * k2_blocks);
   if (vec)
     k2_quota_eval<R, HAS_MASK, true, VT><<<grid, kK2Threads, 0, st>>>(
         ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);

@@ -79,10 +79,17 @@ __device__ __forceinline__ void ldg_nc_u32x8(const void* p, uint32_t (&v)[8]) {
       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
       : "l"(p));
 }
+template <int MODE = 0>
 __device__ __forceinline__ void stg_u32x8(void* p, const uint32_t (&v)[8]) {
-  asm volatile("st.global.L1::no_allocate.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]),
-               "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
-               : "memory");
+  if constexpr (MODE == 0)
+    asm volatile("st.global.L1::no_allocate.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+  else if constexpr (MODE == 1)
+    asm volatile("st.global.cs.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+  else
+    asm volatile("st.global.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
 }
 __device__ __forceinline__ void red_add_i64(long long* p, long long v) {
   asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -126,6 +133,7 @@ __device__ __forceinline__ uint32_t policy_decide(uint32_t op, uint32_t f) {
 constexpr int kK0Threads = 256;
 constexpr int kK0PerThread = 32;
 
+template <int ST>
 static __global__ void __launch_bounds__(kK0Threads)
 k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flags, size_t n,
                uint8_t* __restrict__ code, uint8_t* __restrict__ patch_mask, int vec_ok) {
@@ -159,8 +167,8 @@ k0_policy_eval(const uint8_t* __restrict__ op, const uint16_t* __restrict__ flag
       cw[w] = c;
       pw[w] = p;
     }
-    stg_u32x8(code + base, cw);
-    stg_u32x8(patch_mask + base, pw);
+    stg_u32x8<ST>(code + base, cw);
+    stg_u32x8<ST>(patch_mask + base, pw);
   }
   // scalar tail (and the whole batch when the pointers are not 32-byte aligned)
   for (size_t i = groups * kK0PerThread + (size_t)blockIdx.x * kK0Threads + threadIdx.x; i < n;
