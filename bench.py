@@ -294,10 +294,19 @@ def main():
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    t_w = time.perf_counter()
     for _ in range(max(args.warmup, 3)):
         step()
-    while time.perf_counter() - t_w < 0.5:      # keep the GPU under the same load for a few samples
+    barrier()
+    # keep the GPU under the same load for ~0.5 s so that the clock sampler sees it.  The number of
+    # extra steps is decided by rank 0 and broadcast: with index sharding every step contains a
+    # collective, so all ranks must run exactly the same number of steps.
+    t_w = time.perf_counter()
+    step()
+    torch.cuda.synchronize()
+    extra = torch.tensor([int(min(2000, max(0, 0.5 / max(time.perf_counter() - t_w, 1e-5))))], device=dev, dtype=torch.int64)
+    if world > 1:
+        dist.broadcast(extra, src=0)
+    for _ in range(int(extra.item())):
         step()
     barrier()
     launches0 = eng.timings()["launches"]
