@@ -53,6 +53,7 @@ EXPORTS = [
     "bgc_sheet_get_row", "bgc_sheet_match", "bgc_sheet_row_quota",
     "bgc_review_parse", "bgc_review_destroy", "bgc_review_has_request", "bgc_review_uid", "bgc_review_kind",
     "bgc_review_request", "bgc_review_pod", "bgc_render_review_response",
+    "bgc_format_quantity", "bgc_render_quota_denial",
     "bgc_reconcile_plan", "bgc_plan_destroy", "bgc_plan_count", "bgc_plan_item", "bgc_plan_requeue_seconds",
 ]
 

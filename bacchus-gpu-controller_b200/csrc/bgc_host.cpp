@@ -380,6 +380,67 @@ int bgc_parse_quantity(const char* s, int unit, int64_t* out) {
   return BGC_OK;
 }
 
+long bgc_format_quantity(int64_t value, int unit, char* buf, size_t cap) {
+  if (!buf || unit < BGC_UNIT_COUNT || unit > BGC_UNIT_BYTES) return BGC_E_BADARG;
+  char tmp[48];
+  int w;
+  if (unit == BGC_UNIT_MILLI) {
+    if (value % 1000 == 0) w = snprintf(tmp, sizeof tmp, "%lld", (long long)(value / 1000));
+    else w = snprintf(tmp, sizeof tmp, "%lldm", (long long)value);
+  } else if (unit == BGC_UNIT_BYTES && value != 0) {
+    static const char* const suf[] = {"", "Ki", "Mi", "Gi", "Ti", "Pi", "Ei"};
+    int k = 0;
+    int64_t v = value;
+    while (k < 6 && v % 1024 == 0) { v /= 1024; ++k; }
+    w = snprintf(tmp, sizeof tmp, "%lld%s", (long long)v, suf[k]);
+  } else {
+    w = snprintf(tmp, sizeof tmp, "%lld", (long long)value);
+  }
+  if (w < 0 || (size_t)w + 1 > cap) return BGC_E_BADARG;
+  std::memcpy(buf, tmp, (size_t)w + 1);
+  return w;
+}
+
+long bgc_render_quota_denial(unsigned verdict, int wide, const char* quota_name, const char* const* quota_keys,
+                             const uint8_t* unit, uint32_t R, const int64_t* req, const int64_t* used,
+                             const int64_t* hard, char* buf, size_t cap) {
+  if (!buf || !quota_name || !quota_keys || !unit || !req || !used || !hard || R < 1 || R > BGC_MAX_R) return BGC_E_BADARG;
+  if ((!wide && R > BGC_MAX_R8) || verdict == (wide ? BGC_VERDICT16_BAD_NS : BGC_VERDICT_BAD_NS)) return BGC_E_BADARG;
+  const unsigned shift = wide ? 8 : 4;
+  const unsigned missing = (verdict >> shift) & ((1u << R) - 1u), exceeded = verdict & ((1u << R) - 1u);
+  std::string s;
+  if (missing) {
+    s = "failed quota: ";
+    s += quota_name;
+    s += ": must specify ";
+    bool first = true;
+    for (uint32_t r = 0; r < R; ++r)
+      if ((missing >> r) & 1u) { if (!first) s += ","; s += quota_keys[r]; first = false; }
+  } else if (exceeded) {
+    s = "exceeded quota: ";
+    s += quota_name;
+    const char* const heads[3] = {", requested: ", ", used: ", ", limited: "};
+    const int64_t* const vals[3] = {req, used, hard};
+    for (int part = 0; part < 3; ++part) {
+      s += heads[part];
+      bool first = true;
+      for (uint32_t r = 0; r < R; ++r) {
+        if (!((exceeded >> r) & 1u)) continue;
+        char q[48];
+        if (bgc_format_quantity(vals[part][r], unit[r], q, sizeof q) < 0) return BGC_E_BADARG;
+        if (!first) s += ",";
+        s += quota_keys[r];
+        s += "=";
+        s += q;
+        first = false;
+      }
+    }
+  }
+  if (s.size() + 1 > cap) return BGC_E_BADARG;
+  std::memcpy(buf, s.c_str(), s.size() + 1);
+  return (long)s.size();
+}
+
 bgc_nsmap* bgc_nsmap_create(void) { return new (std::nothrow) bgc_nsmap; }
 void bgc_nsmap_destroy(bgc_nsmap* m) { delete m; }
 uint32_t bgc_nsmap_intern(bgc_nsmap* m, const char* name) {

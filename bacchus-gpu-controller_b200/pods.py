@@ -55,6 +55,34 @@ def parse_quantity(s: str, unit: int) -> int:
     return out.value
 
 
+lib.bgc_format_quantity.restype = C.c_long
+lib.bgc_format_quantity.argtypes = [C.c_int64, C.c_int, C.c_char_p, C.c_size_t]
+lib.bgc_render_quota_denial.restype = C.c_long
+
+
+def format_quantity(value: int, unit: int) -> str:
+    buf = C.create_string_buffer(64)
+    if lib.bgc_format_quantity(C.c_int64(value), unit, buf, 64) < 0:
+        raise ValueError("bad unit")
+    return buf.value.decode()
+
+
+def quota_denial_message(verdict: int, quota_name: str, quota_keys: Sequence[str], req, used, hard, wide: bool = False):
+    """Message for one rejected pod (None when the pod is allowed); req/used/hard are the R values of
+    this pod and of its namespace."""
+    R = len(quota_keys)
+    keys = (C.c_char_p * R)(*[k.encode() for k in quota_keys])
+    unit = np.array([QUOTA_KEYS[k] for k in quota_keys], np.uint8)
+    a = [np.ascontiguousarray(x, dtype=np.int64) for x in (req, used, hard)]
+    buf = C.create_string_buffer(2048)
+    n = lib.bgc_render_quota_denial(C.c_uint(int(verdict)), C.c_int(int(wide)), quota_name.encode(), keys, C.c_void_p(unit.ctypes.data),
+                                    C.c_uint32(R), C.c_void_p(a[0].ctypes.data), C.c_void_p(a[1].ctypes.data),
+                                    C.c_void_p(a[2].ctypes.data), buf, C.c_size_t(2048))
+    if n < 0:
+        raise BgcError(int(n), "bgc_render_quota_denial")
+    return buf.value.decode() if n else None
+
+
 class NamespaceMap:
     def __init__(self):
         self._h = C.c_void_p(lib.bgc_nsmap_create())

@@ -104,6 +104,25 @@ typedef struct bgc_pod_spec {
  * overflow. */
 int bgc_parse_quantity(const char *s, int unit, int64_t *out);
 
+/* canonical integer → Kubernetes quantity text, the inverse of bgc_parse_quantity for the forms the
+ * reference writes (src/synchronizer.rs:253-277) and Kubernetes prints: MILLI → "<n>" when a whole
+ * number of cores else "<n>m"; BYTES → the largest exact binary suffix ("64Gi", "1536Mi") else the
+ * plain integer; COUNT → the plain integer.  Returns the length written or BGC_E_BADARG. */
+long bgc_format_quantity(int64_t value, int unit, char *buf, size_t cap);
+
+/* The message kube-apiserver's ResourceQuota admission attaches to a rejected pod, for one verdict of
+ * bgc_quota_eval / bgc_quota_eval16 (wide != 0: the u16 layout):
+ *   missing  → "failed quota: <quota>: must specify k1,k2"
+ *   exceeded → "exceeded quota: <quota>, requested: k=v,..., used: k=v,..., limited: k=v,..."
+ * (missing wins, as the plugin checks it first; keys in the order given; every failing resource is
+ * listed).  <quota> is the ResourceQuota's name — the reference names it after the namespace
+ * (src/controller.rs:92).  req / used / hard are the R values of this pod / its namespace.
+ * Message wording restated from Kubernetes' plugin from memory — unpinned.  Returns the length
+ * written, 0 for an allowed pod, or BGC_E_BADARG. */
+long bgc_render_quota_denial(unsigned verdict, int wide, const char *quota_name, const char *const *quota_keys,
+                             const uint8_t *unit, uint32_t R, const int64_t *req, const int64_t *used,
+                             const int64_t *hard, char *buf, size_t cap);
+
 /* namespace name ↔ dense u32 id */
 typedef struct bgc_nsmap bgc_nsmap;
 bgc_nsmap *bgc_nsmap_create(void);

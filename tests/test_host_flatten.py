@@ -148,3 +148,62 @@ def test_hard_from_sheet_row_follows_synchronizer(bgc):
     assert bgc.pods.parse_quantity("16", 1) == 16000 and bgc.pods.parse_quantity("64Gi", 2) == 64 << 30
     with pytest.raises(bgc.BgcError):
         bgc.pods.hard_from_sheet_row(1, 1, 1, 1, 1, ["requests.foo"])
+
+
+@pytest.mark.parametrize("value,unit,text", [
+    (0, 1, "0"), (500, 1, "500m"), (2000, 1, "2"), (16000, 1, "16"), (-250, 1, "-250m"), (1500, 1, "1500m"),
+    (0, 2, "0"), (64 << 30, 2, "64Gi"), (1536 << 20, 2, "1536Mi"), (1000, 2, "1000"), (1 << 60, 2, "1Ei"), (3 << 10, 2, "3Ki"),
+    (7, 0, "7"), (-1, 0, "-1"), (1 << 40, 0, "1099511627776"),
+])
+def test_format_quantity_round_trips(bgc, value, unit, text):
+    assert bgc.pods.format_quantity(value, unit) == text
+    assert bgc.pods.parse_quantity(text, unit) == value
+
+
+def test_quota_denial_messages(bgc):
+    Pd = bgc.pods
+    keys = ["requests.nvidia.com/gpu", "requests.cpu", "requests.memory"]
+    req, used, hard = [1, 1500, 2 << 30], [2, 7000, 3 << 30], [2, 8000, 4 << 30]
+    assert Pd.quota_denial_message(0, "alice", keys, req, used, hard) is None
+    assert Pd.quota_denial_message(0b011, "alice", keys, req, used, hard) == (
+        "exceeded quota: alice, requested: requests.nvidia.com/gpu=1,requests.cpu=1500m, "
+        "used: requests.nvidia.com/gpu=2,requests.cpu=7, limited: requests.nvidia.com/gpu=2,requests.cpu=8")
+    assert Pd.quota_denial_message(0b100, "alice", keys, req, used, hard) == (
+        "exceeded quota: alice, requested: requests.memory=2Gi, used: requests.memory=3Gi, limited: requests.memory=4Gi")
+    # missing wins over exceeded; u8 layout has missing in bits 4..7, u16 in bits 8..15
+    assert Pd.quota_denial_message((0b110 << 4) | 0b001, "bob", keys, req, used, hard) == "failed quota: bob: must specify requests.cpu,requests.memory"
+    assert Pd.quota_denial_message((0b010 << 8), "bob", keys, req, used, hard, wide=True) == "failed quota: bob: must specify requests.cpu"
+    with pytest.raises(bgc.BgcError):
+        Pd.quota_denial_message(0xFF, "bob", keys, req, used, hard)          # unknown namespace has no quota to name
+
+
+def test_parse_quantity_property_vs_exact_fractions(bgc):
+    """Random quantity strings in every suffix family against exact rational arithmetic (ceil)."""
+    from fractions import Fraction
+    from hypothesis import given, settings, strategies as st
+    suffixes = {"": 1, "n": Fraction(1, 10**9), "u": Fraction(1, 10**6), "m": Fraction(1, 1000), "k": 10**3, "M": 10**6, "G": 10**9,
+                "T": 10**12, "Ki": 1 << 10, "Mi": 1 << 20, "Gi": 1 << 30, "Ti": 1 << 40}
+
+    @settings(max_examples=400, deadline=None)
+    @given(st.integers(0, 10**9), st.integers(0, 999999), st.integers(0, 6), st.sampled_from(sorted(suffixes)), st.integers(0, 2), st.booleans())
+    def check(whole, frac, frac_digits, suffix, unit, negative):
+        text = str(whole)
+        value = Fraction(whole)
+        if frac_digits:
+            f = frac % (10 ** frac_digits)
+            text += "." + str(f).zfill(frac_digits)
+            value += Fraction(f, 10 ** frac_digits)
+        value *= suffixes[suffix]
+        if negative:
+            text, value = "-" + text, -value
+        text += suffix
+        scaled = value * (1000 if unit == 1 else 1)
+        want = -((-scaled.numerator) // scaled.denominator)         # ceil, also for negatives (rounds toward zero)
+        if abs(want) >= 2**63:
+            return
+        assert bgc.pods.parse_quantity(text, unit) == want, text
+
+    check()
+    # decimal exponents
+    for text, unit, want in [("1e3", 0, 1000), ("12e-1", 0, 2), ("5e-1", 1, 500), ("1.5e3", 2, 1500), ("25e-4", 1, 3)]:
+        assert bgc.pods.parse_quantity(text, unit) == want
