@@ -135,3 +135,36 @@ def flatten_pod_reviews(bodies: Sequence[bytes | str], quota_keys: Sequence[str]
         raise BgcError(rc, "bgc_flatten_pods")
     m = n_out.value
     return ns_id[:m].copy(), [c[:m].copy() for c in req], mask[:m].copy(), unit
+
+
+def handle_pod_reviews(engine, bodies: Sequence[bytes | str], quota_keys: Sequence[str], nsmap, used=None, hard=None, wide: bool | None = None) -> list:
+    """Pod-create AdmissionReviews, wire bytes to wire bytes: parse -> flatten (row A5) -> snapshot
+    verdicts on the GPU (K2) -> AdmissionReview responses, denied pods carrying the message
+    kube-apiserver's ResourceQuota plugin would give (`pods.quota_denial_message`).  `used` / `hard`
+    ([R][NS] arrays) are only needed for the denial text; pass None to get bare allow/deny.
+    Not a reference path: the reference's webhook never sees pods."""
+    from .pods import quota_denial_message
+    R = len(quota_keys)
+    if wide is None:
+        wide = R > 4
+    reviews = [Review(b) for b in bodies]
+    ns_id, req, mask, _unit = flatten_pod_reviews(bodies, quota_keys, nsmap, intern=False)
+    if ns_id.shape[0] != len(reviews):
+        raise ValueError("terminal pods cannot appear in create reviews")
+    verdict = engine.quota_eval(ns_id, req, mask, wide=wide) if wide else engine.quota_eval(ns_id, req, mask)
+    bad = 0xFFFF if wide else 0xFF
+    out = []
+    for i, r in enumerate(reviews):
+        v = int(verdict[i])
+        if v == 0:
+            resp, msg = _CResponse(1, 0, 0, 0, None), None
+        elif v == bad:
+            resp, msg = _CResponse(0, 2, 0, 0, None), "namespace is not known to the quota engine"
+        else:
+            ns = int(ns_id[i])
+            msg = "exceeded quota" if used is None or hard is None else quota_denial_message(
+                v, nsmap.name(ns), quota_keys, [int(c[i]) for c in req], [int(used[k][ns]) for k in range(R)],
+                [int(hard[k][ns]) for k in range(R)], wide=wide)
+            resp = _CResponse(0, 2, 0, 0, None)
+        out.append(_render(r.uid, resp, msg, None))
+    return out

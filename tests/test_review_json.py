@@ -91,3 +91,54 @@ def test_wire_bytes_to_response_json(bgc, engine):
             assert "patch" not in resp
     last = json.loads(outs[-1])["response"]
     assert last["allowed"] is False and last["status"]["reason"] == "InvalidRequest"
+
+
+def test_pod_reviews_wire_to_wire_with_a_stand_in_engine(bgc, oracle):
+    """`review.handle_pod_reviews` composes parse -> flatten -> K2 -> render.  K2 itself is covered by the
+    GPU tests; here a stand-in engine whose quota_eval is the oracle lets the composition run on CPU."""
+    import os, sys
+    sys.path.insert(0, os.path.dirname(__file__))
+    from workloads import C1_KEYS, C1_KEYS6, c1_namespaces, c1_pods
+    nss = c1_namespaces()
+    m = bgc.pods.NamespaceMap()
+    for ns in nss:
+        m.intern(ns["name"])
+    for keys, wide in ((C1_KEYS, False), (C1_KEYS6, True)):
+        R = len(keys)
+        hard = np.zeros((R, len(nss)), np.int64)
+        hm = np.zeros(len(nss), np.uint8)
+        for i, ns in enumerate(nss):
+            h, unit = bgc.pods.hard_from_sheet_row(ns["cpu"], ns["memory"], ns["gpu"], ns["storage"], ns["mig"], keys)
+            hard[:, i] = h
+            hm[i] = (1 << R) - 1 if ns["has_quota"] else 0
+        r_ns, r_req, _, _ = bgc.pods.flatten_pods(c1_pods(3000, nss, running=True), keys, m, intern=False)
+        used = oracle.usage_reduce(r_ns, r_req, len(nss))
+        cm = sum(1 << r for r, u in enumerate(unit) if u)
+
+        class StandIn:
+            def quota_eval(self, ns_id, req, mask, wide=False):
+                f = oracle.quota_eval16 if wide else oracle.quota_eval
+                return f(ns_id, req, mask, len(nss), used, hard, hm, cm)
+
+        pods = c1_pods(400, nss, running=False)
+        pods[5]["metadata"]["namespace"] = "ghost"
+        bodies = [json.dumps({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview",
+                              "request": {"uid": f"u{i}", "operation": "CREATE", "kind": {"kind": "Pod"}, "namespace": p["metadata"]["namespace"], "object": p}})
+                  for i, p in enumerate(pods)]
+        outs = bgc.review.handle_pod_reviews(StandIn(), bodies, keys, m, used, hard, wide=wide)
+        c_ns, c_req, c_mask, _ = bgc.pods.flatten_pods(pods, keys, m, intern=False)
+        verdict = StandIn().quota_eval(c_ns, c_req, c_mask, wide=wide)
+        seen = set()
+        for i, text in enumerate(outs):
+            resp = json.loads(text)["response"]
+            assert resp["uid"] == f"u{i}" and resp["allowed"] == (verdict[i] == 0)
+            if verdict[i] == 0:
+                assert resp["status"] == {}
+            elif i == 5:
+                assert "not known" in resp["status"]["message"]
+            else:
+                msg = resp["status"]["message"]
+                ns_name = pods[i]["metadata"]["namespace"]
+                assert msg.startswith(f"exceeded quota: {ns_name}, requested: ") or msg.startswith(f"failed quota: {ns_name}: must specify ")
+                seen.add(msg.split(":")[0])
+        assert seen == {"exceeded quota", "failed quota"}
