@@ -1,0 +1,473 @@
+// bgc_k3.cuh — K3 admit_greedy (row N1).  Part of libbgc.so's device code; included through bgc_kernels.cuh.
+#pragma once
+#include "bgc_common.cuh"
+
+namespace bgc {
+
+// ------------------------------------------------------------------ K3 admit_greedy (row N1)
+// Kubernetes-faithful sequential admission inside a batch: per namespace, in arrival order, a pod
+// is admitted iff its verdict against the CURRENT usage is 0, and only admitted pods add to usage.
+// The recurrence is order-dependent inside a namespace and independent across namespaces, so:
+//   1. pod indices are grouped by namespace with a stable radix sort (arrival order preserved);
+//   2. one warp walks one namespace, 32 pods per tile, alternating two warp-wide steps:
+//      admit-run : exclusive prefix sums of the requests assume "everyone so far is admitted"; the
+//                  FIRST lane whose check fails under that prefix is the true first rejection
+//                  (everything before it really was admitted), found with one ballot;
+//      reject-run: while usage stands still, every following pod that does not fit on its own is
+//                  rejected, up to the first one that fits — again one ballot.
+// A tile costs one scan per admit->reject alternation, not one step per pod.
+static __global__ void k_greedy_keys(const uint32_t* __restrict__ ns_id, size_t n, uint32_t NS,
+                                     uint32_t* keys, uint32_t* idx) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t ns = ns_id[i];
+    keys[i] = ns < NS ? ns : NS;  // unknown namespaces sort behind every real one
+    idx[i] = (uint32_t)i;
+  }
+}
+
+// seg[k] = first position in the sorted key array with key >= k, for k = 0..NS+1
+static __global__ void k_greedy_segments(const uint32_t* __restrict__ sorted_keys, size_t n, uint32_t NS,
+                                         uint32_t* seg) {
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k <= (size_t)NS + 1;
+       k += (size_t)gridDim.x * blockDim.x) {
+    size_t lo = 0, hi = n;
+    while (lo < hi) {
+      const size_t mid = lo + ((hi - lo) >> 1);
+      if (sorted_keys[mid] < (uint32_t)k) lo = mid + 1; else hi = mid;
+    }
+    seg[k] = (uint32_t)lo;
+  }
+}
+
+static __global__ void k_greedy_bad_ns(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg,
+                                       uint32_t NS, uint8_t* verdict) {
+  const size_t beg = seg[NS], end = seg[NS + 1];
+  for (size_t i = beg + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += (size_t)gridDim.x * blockDim.x)
+    verdict[order[i]] = 0xFFu;
+}
+
+// requests permuted into grouped order, so the sequential walkers below stream contiguous memory
+template <int R, bool HAS_MASK>
+static __global__ void __launch_bounds__(256)
+k_greedy_gather(const uint32_t* __restrict__ order, ReqCols<R> req, const uint8_t* __restrict__ req_mask, size_t n,
+                ReqColsOut<R> out, uint8_t* __restrict__ mask_out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t idx = order[i];
+#pragma unroll
+    for (int r = 0; r < R; ++r) out.p[r][i] = req.p[r][idx];
+    if (HAS_MASK) mask_out[i] = req_mask[idx];
+  }
+}
+
+template <int R>
+struct GreedyPod {
+  long long q[R];
+  uint32_t mask;
+};
+
+// verdict of one pod against usage T
+template <int R>
+__device__ __forceinline__ uint32_t greedy_verdict(const GreedyPod<R>& p, const long long (&T)[R],
+                                                   const long long (&H)[R], uint32_t hm, uint32_t compute_mask) {
+  uint32_t missing = 0, exceeded = 0;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const bool constrained = (hm >> r) & 1u, present = (p.mask >> r) & 1u;
+    if (constrained && !present && ((compute_mask >> r) & 1u)) missing |= 1u << r;
+    if (constrained && present && p.q[r] > 0 && p.q[r] > sat_sub_i64(H[r], T[r])) exceeded |= 1u << r;
+  }
+  return (missing << 4) | exceeded;
+}
+
+template <int R, bool HAS_MASK>
+__global__ void __launch_bounds__(256)
+k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg, ReqCols<R> req,
+                const uint8_t* __restrict__ req_mask, long long* used, const long long* __restrict__ hard,
+                const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask,
+                uint8_t* __restrict__ verdict, uint32_t team_min) {
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t warps_total = gridDim.x * (blockDim.x >> 5);
+  // heavy namespaces first would be ideal; a strided walk at least spreads neighbours over warps
+  for (uint32_t ns = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); ns < NS; ns += warps_total) {
+    const uint32_t beg = seg[ns], end = seg[ns + 1];
+    if (beg == end || end - beg >= team_min) continue;  // long segments belong to the CTA-wide kernel
+    long long S[R], H[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      S[r] = used[(size_t)r * NS + ns];
+      H[r] = hard[(size_t)r * NS + ns];
+    }
+    const uint32_t hm = hard_mask[ns];
+
+    // `req` / `req_mask` are the GROUPED columns (k_greedy_gather): tile t+1 is in flight while tile t is decided
+    GreedyPod<R> p0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) p0.q[r] = (beg + lane < end) ? req.p[r][beg + lane] : 0;
+    p0.mask = (HAS_MASK && beg + lane < end) ? req_mask[beg + lane] : 0xFFu;
+    for (uint32_t t = beg; t < end; t += 32) {
+      const bool valid = t + lane < end;
+      const GreedyPod<R> p = p0;
+      const bool valid1 = t + 32 + lane < end;
+#pragma unroll
+      for (int r = 0; r < R; ++r) p0.q[r] = valid1 ? req.p[r][t + 32 + lane] : 0;
+      p0.mask = (HAS_MASK && valid1) ? req_mask[t + 32 + lane] : 0xFFu;
+
+      uint32_t my_verdict = 0;
+      uint32_t pos = 0;  // lanes < pos are decided
+      // Monotone fast path.  When every request of the tile is in [0, 2^40] and usage is in
+      // [0, 2^62], usage only grows and cannot overflow, so a pod that does not fit on its own NOW
+      // can never fit later: all such pods are struck out at once, and only pods that lose their
+      // place because of admissions inside this very tile cost an extra round.
+      bool tame = true;
+#pragma unroll
+      for (int r = 0; r < R; ++r) tame = tame && p.q[r] >= 0 && p.q[r] <= (1ll << 40) && S[r] >= 0 && S[r] <= (1ll << 62);
+      if (__all_sync(0xFFFFFFFFu, tame)) {
+        long long S0[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) S0[r] = S[r];
+        uint32_t live = __ballot_sync(0xFFFFFFFFu, valid), admitted = 0;
+        while (live) {
+          const uint32_t v_alone = greedy_verdict<R>(p, S, H, hm, compute_mask);
+          live &= ~__ballot_sync(0xFFFFFFFFu, v_alone != 0);
+          if (!live) break;
+          const bool mine = (live >> lane) & 1u;
+          long long E[R], incl[R];
+#pragma unroll
+          for (int r = 0; r < R; ++r) incl[r] = mine ? p.q[r] : 0;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+              const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
+              if (lane >= (uint32_t)d) incl[r] += o;
+            }
+          }
+          long long T[R];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            E[r] = incl[r] - (mine ? p.q[r] : 0);
+            T[r] = S[r] + E[r];
+          }
+          const uint32_t fail = __ballot_sync(0xFFFFFFFFu, mine && greedy_verdict<R>(p, T, H, hm, compute_mask) != 0);
+          if (!fail) {
+            admitted |= live;
+#pragma unroll
+            for (int r = 0; r < R; ++r) S[r] += __shfl_sync(0xFFFFFFFFu, incl[r], 31);
+            break;
+          }
+          const uint32_t v = __ffs(fail) - 1u;  // first pod squeezed out by admissions of this tile
+          admitted |= live & ((1u << v) - 1u);
+#pragma unroll
+          for (int r = 0; r < R; ++r) S[r] += __shfl_sync(0xFFFFFFFFu, E[r], v);
+          live &= ~((2u << v) - 1u);
+        }
+        // reason bits of the rejected pods are taken against the usage they actually met
+        long long incl[R], T[R];
+        const bool adm = (admitted >> lane) & 1u;
+#pragma unroll
+        for (int r = 0; r < R; ++r) incl[r] = adm ? p.q[r] : 0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
+            if (lane >= (uint32_t)d) incl[r] += o;
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) T[r] = S0[r] + incl[r] - (adm ? p.q[r] : 0);
+        my_verdict = adm ? 0u : greedy_verdict<R>(p, T, H, hm, compute_mask);
+        pos = 32;
+      }
+      while (pos < 32) {
+        // ---- admit-run: exclusive prefix of the adds of lanes >= pos
+        long long E[R], incl[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) incl[r] = (valid && lane >= pos) ? p.q[r] : 0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
+            if (lane >= (uint32_t)d) incl[r] = (long long)((unsigned long long)incl[r] + (unsigned long long)o);
+          }
+        }
+        long long T[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          E[r] = (long long)((unsigned long long)incl[r] - (unsigned long long)((valid && lane >= pos) ? p.q[r] : 0));
+          T[r] = (long long)((unsigned long long)S[r] + (unsigned long long)E[r]);
+        }
+        const uint32_t v_run = greedy_verdict<R>(p, T, H, hm, compute_mask);
+        const uint32_t fail = __ballot_sync(0xFFFFFFFFu, valid && lane >= pos && v_run != 0);
+        if (fail == 0) {  // everyone left in the tile is admitted
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+            S[r] = (long long)((unsigned long long)S[r] + (unsigned long long)__shfl_sync(0xFFFFFFFFu, incl[r], 31));
+          break;
+        }
+        const uint32_t v = __ffs(fail) - 1u;  // first true rejection
+        if (lane == v) my_verdict = v_run;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          S[r] = (long long)((unsigned long long)S[r] + (unsigned long long)__shfl_sync(0xFFFFFFFFu, E[r], v));
+        pos = v + 1;
+        if (pos >= 32) break;
+        // ---- reject-run: usage stands still at S until somebody fits on their own
+        const uint32_t v_alone = greedy_verdict<R>(p, S, H, hm, compute_mask);
+        const uint32_t later = 0xFFFFFFFFu << pos;
+        const uint32_t fits = __ballot_sync(0xFFFFFFFFu, valid && v_alone == 0) & later;
+        const uint32_t stop = fits ? (__ffs(fits) - 1u) : 32u;
+        if (lane >= pos && lane < stop && valid) my_verdict = v_alone;
+        pos = stop;
+        if (pos >= 32) break;
+      }
+      if (valid) verdict[order[t + lane]] = (uint8_t)my_verdict;
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) used[(size_t)r * NS + ns] = S[r];
+    }
+  }
+}
+
+// Hot namespaces (Zipf heads) would keep one warp busy for hundreds of milliseconds, so segments of
+// kGreedyTeamMin pods or more are walked by a whole 1024-thread CTA instead: the same admit-run /
+// reject-run alternation on tiles of 1024 pods, with a two-level (warp shuffle + shared memory)
+// exclusive scan and a shared-memory atomicMin to find the first rejection / first fit.
+constexpr uint32_t kGreedyTeamMin = 32768;
+constexpr int kGreedyTeam = 1024;
+constexpr int kGreedyDepth = 4;  // tiles of requests in flight per CTA (ring of R * 8 KB per tile)
+
+template <int R, bool HAS_MASK>
+__global__ void __launch_bounds__(kGreedyTeam, 1)
+k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg, ReqCols<R> req,
+                     const uint8_t* __restrict__ req_mask, long long* used, const long long* __restrict__ hard,
+                     const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask,
+                     uint8_t* __restrict__ verdict) {
+  extern __shared__ __align__(16) long long g_ring[];  // [kGreedyDepth][R][kGreedyTeam]
+  __shared__ long long s_wtot[R][32];    // per-warp totals, then their exclusive prefix
+  __shared__ long long s_total[R];
+  __shared__ long long s_E[R][kGreedyTeam];
+  __shared__ uint32_t s_first[2], s_fit[2];
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  constexpr uint32_t BIG = 0xFFFFFFFFu;
+
+  for (uint32_t ns = blockIdx.x; ns < NS; ns += gridDim.x) {
+    const uint32_t beg = seg[ns], end = seg[ns + 1];
+    if (end - beg < kGreedyTeamMin) continue;  // short segments belong to the warp kernel
+    long long S[R], H[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      S[r] = used[(size_t)r * NS + ns];
+      H[r] = hard[(size_t)r * NS + ns];
+    }
+    const uint32_t hm = hard_mask[ns];
+    __syncthreads();  // previous namespace's shared state is no longer read
+
+    // A single CTA walks this namespace, so its own loads are all the memory parallelism there is:
+    // kGreedyDepth tiles of requests are kept in flight with cp.async into a shared-memory ring
+    // (every thread only ever reads back the elements it copied itself, so no barrier is needed).
+    auto issue_tile = [&](uint32_t t, uint32_t slot) {
+      if (t + tid < end) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&g_ring[((size_t)slot * R + r) * kGreedyTeam + tid]);
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(req.p[r] + t + tid) : "memory");
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    uint32_t mask_q[kGreedyDepth];
+#pragma unroll
+    for (int d = 0; d < kGreedyDepth; ++d) {
+      const uint32_t t = beg + d * kGreedyTeam;
+      issue_tile(t, d);
+      mask_q[d] = (HAS_MASK && t < end && t + tid < end) ? req_mask[t + tid] : 0xFFu;
+    }
+    uint32_t iter = 0, slot = 0;
+    for (uint32_t t = beg; t < end; t += kGreedyTeam) {
+      const bool valid = t + tid < end;
+      asm volatile("cp.async.wait_group %0;" ::"n"(kGreedyDepth - 1) : "memory");
+      GreedyPod<R> p;
+#pragma unroll
+      for (int r = 0; r < R; ++r) p.q[r] = valid ? g_ring[((size_t)slot * R + r) * kGreedyTeam + tid] : 0;
+      p.mask = mask_q[0];
+#pragma unroll
+      for (int d = 0; d + 1 < kGreedyDepth; ++d) mask_q[d] = mask_q[d + 1];
+      {
+        const uint32_t tn = t + kGreedyDepth * kGreedyTeam;
+        issue_tile(tn < end ? tn : end, slot);  // refills the slot just consumed (or commits an empty group)
+        mask_q[kGreedyDepth - 1] = (HAS_MASK && tn < end && tn + tid < end) ? req_mask[tn + tid] : 0xFFu;
+      }
+      slot = slot + 1 == kGreedyDepth ? 0 : slot + 1;
+
+      uint32_t my_verdict = 0, pos = 0;
+      // block-wide exclusive prefix sum of x[] (0 for threads that do not take part); also leaves the
+      // per-thread prefixes in s_E and the block total in s_total.  Two barriers.
+      auto block_exclusive = [&](const long long (&x)[R], long long (&E)[R]) {
+        long long incl[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) incl[r] = x[r];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
+            if (lane >= (uint32_t)d) incl[r] = (long long)((unsigned long long)incl[r] + (unsigned long long)o);
+          }
+        }
+        if (lane == 31) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) s_wtot[r][warp] = incl[r];
+        }
+        __syncthreads();
+        if (warp == 0) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const long long mine = s_wtot[r][lane];
+            long long y = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+              const long long o = __shfl_up_sync(0xFFFFFFFFu, y, d);
+              if (lane >= (uint32_t)d) y = (long long)((unsigned long long)y + (unsigned long long)o);
+            }
+            s_wtot[r][lane] = (long long)((unsigned long long)y - (unsigned long long)mine);
+            if (lane == 31) s_total[r] = y;
+          }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          E[r] = (long long)((unsigned long long)s_wtot[r][warp] + (unsigned long long)incl[r] - (unsigned long long)x[r]);
+          s_E[r][tid] = E[r];
+        }
+      };
+      // Monotone fast path (see the warp kernel): requests in [0, 2^40], usage in [0, 2^62].
+      bool tame = true;
+#pragma unroll
+      for (int r = 0; r < R; ++r) tame = tame && p.q[r] >= 0 && p.q[r] <= (1ll << 40) && S[r] >= 0 && S[r] <= (1ll << 62);
+      if (__syncthreads_and(tame)) {
+        long long S0[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) S0[r] = S[r];
+        bool live = valid, adm = false;
+        while (true) {
+          if (live && greedy_verdict<R>(p, S, H, hm, compute_mask) != 0) live = false;  // can never fit again
+          if (!__syncthreads_or(live)) break;  // saturated: nobody left to consider
+          const uint32_t par = iter & 1u;
+          ++iter;
+          if (tid == 0) s_first[par] = BIG;
+          long long x[R], E[R], T[R];
+#pragma unroll
+          for (int r = 0; r < R; ++r) x[r] = live ? p.q[r] : 0;
+          block_exclusive(x, E);  // its barriers also publish the reset of s_first[par]
+#pragma unroll
+          for (int r = 0; r < R; ++r) T[r] = S[r] + E[r];
+          const uint32_t fail = __ballot_sync(0xFFFFFFFFu, live && greedy_verdict<R>(p, T, H, hm, compute_mask) != 0);
+          if (fail && lane == (uint32_t)(__ffs(fail) - 1)) atomicMin(&s_first[par], tid);
+          __syncthreads();
+          const uint32_t v = s_first[par];
+          if (v == BIG) {
+            adm = adm || live;
+#pragma unroll
+            for (int r = 0; r < R; ++r) S[r] += s_total[r];
+            break;
+          }
+          if (live && tid < v) adm = true;
+#pragma unroll
+          for (int r = 0; r < R; ++r) S[r] += s_E[r][v];
+          if (tid <= v) live = false;
+        }
+        if (__syncthreads_or(adm)) {  // reason bits against the usage each rejected pod actually met
+          long long x[R], E[R], T[R];
+#pragma unroll
+          for (int r = 0; r < R; ++r) x[r] = adm ? p.q[r] : 0;
+          block_exclusive(x, E);
+#pragma unroll
+          for (int r = 0; r < R; ++r) T[r] = S0[r] + E[r];
+          my_verdict = adm ? 0u : greedy_verdict<R>(p, T, H, hm, compute_mask);
+        } else {                      // nothing admitted in this tile: usage never moved
+          my_verdict = valid ? greedy_verdict<R>(p, S0, H, hm, compute_mask) : 0u;
+        }
+        pos = kGreedyTeam;
+        __syncthreads();  // s_E / s_wtot are reused by the next tile
+      }
+      while (pos < (uint32_t)kGreedyTeam) {
+        const uint32_t par = iter & 1u;
+        ++iter;
+        // ---- admit-run: block-wide exclusive prefix of the adds of threads >= pos
+        long long a[R], incl[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) incl[r] = a[r] = (valid && tid >= pos) ? p.q[r] : 0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
+            if (lane >= (uint32_t)d) incl[r] = (long long)((unsigned long long)incl[r] + (unsigned long long)o);
+          }
+        }
+        if (lane == 31) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) s_wtot[r][warp] = incl[r];
+        }
+        if (tid == 0) { s_first[par] = BIG; s_fit[par] = BIG; }
+        __syncthreads();
+        if (warp == 0) {  // exclusive scan of the 32 warp totals
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const long long mine = s_wtot[r][lane];
+            long long x = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+              const long long o = __shfl_up_sync(0xFFFFFFFFu, x, d);
+              if (lane >= (uint32_t)d) x = (long long)((unsigned long long)x + (unsigned long long)o);
+            }
+            s_wtot[r][lane] = (long long)((unsigned long long)x - (unsigned long long)mine);
+            if (lane == 31) s_total[r] = x;
+          }
+        }
+        __syncthreads();
+        long long E[R], T[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          E[r] = (long long)((unsigned long long)s_wtot[r][warp] + (unsigned long long)incl[r] - (unsigned long long)a[r]);
+          T[r] = (long long)((unsigned long long)S[r] + (unsigned long long)E[r]);
+          s_E[r][tid] = E[r];
+        }
+        const uint32_t v_run = greedy_verdict<R>(p, T, H, hm, compute_mask);
+        const uint32_t fail = __ballot_sync(0xFFFFFFFFu, valid && tid >= pos && v_run != 0);
+        if (fail && lane == (uint32_t)(__ffs(fail) - 1)) atomicMin(&s_first[par], tid);
+        __syncthreads();
+        const uint32_t v = s_first[par];
+        if (v == BIG) {  // everyone left in the tile is admitted
+#pragma unroll
+          for (int r = 0; r < R; ++r) S[r] = (long long)((unsigned long long)S[r] + (unsigned long long)s_total[r]);
+          break;
+        }
+        if (tid == v) my_verdict = v_run;
+#pragma unroll
+        for (int r = 0; r < R; ++r) S[r] = (long long)((unsigned long long)S[r] + (unsigned long long)s_E[r][v]);
+        pos = v + 1;
+        if (pos >= (uint32_t)kGreedyTeam) break;
+        // ---- reject-run: usage stands still at S until somebody fits on their own
+        const uint32_t v_alone = greedy_verdict<R>(p, S, H, hm, compute_mask);
+        const uint32_t fits = __ballot_sync(0xFFFFFFFFu, valid && tid >= pos && v_alone == 0);
+        if (fits && lane == (uint32_t)(__ffs(fits) - 1)) atomicMin(&s_fit[par], tid);
+        __syncthreads();
+        const uint32_t stop = s_fit[par] == BIG ? (uint32_t)kGreedyTeam : s_fit[par];
+        if (tid >= pos && tid < stop && valid) my_verdict = v_alone;
+        pos = stop;
+        if (pos >= (uint32_t)kGreedyTeam) break;
+      }
+      if (valid) verdict[order[t + tid]] = (uint8_t)my_verdict;
+    }
+    if (tid == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) used[(size_t)r * NS + ns] = S[r];
+    }
+  }
+}
+
+}  // namespace bgc
