@@ -44,7 +44,7 @@ EXPORTS = [
     "bgc_timings_get", "bgc_policy_eval", "bgc_policy_eval_dev", "bgc_quota_table_set",
     "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_usage_get_dev", "bgc_usage_set_dev", "bgc_quota_eval", "bgc_quota_eval16", "bgc_quota_eval16_dev",
     "bgc_quota_eval_dev", "bgc_ctx_set_k1_variant", "bgc_last_k1_variant", "bgc_version",
-    "bgc_synth_pods_dev", "bgc_synth_policy_dev", "bgc_checksum_u8_dev", "bgc_histogram_u8_dev",
+    "bgc_synth_pods_dev", "bgc_synth_pods_shard_dev", "bgc_synth_policy_dev", "bgc_checksum_u8_dev", "bgc_histogram_u8_dev",
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
     "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
     "bgc_nsmap_intern", "bgc_nsmap_lookup", "bgc_nsmap_size", "bgc_nsmap_name", "bgc_flatten_pods",
@@ -98,6 +98,8 @@ lib.bgc_quota_eval16_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_admit_greedy.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_admit_greedy_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_synth_pods_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64, _Z, _P, _P, _P]
+lib.bgc_synth_pods_shard_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64, _Z, C.c_uint32, C.c_uint32, _P, C.c_uint64, _Z,
+                                         _P, _P, _P, _P, C.POINTER(C.c_uint64)]
 lib.bgc_synth_policy_dev.argtypes = [_P, C.c_uint64, C.c_uint64, _Z, _P, _P]
 lib.bgc_checksum_u8_dev.argtypes = [_P, _P, C.c_uint64, _Z, C.POINTER(C.c_uint64)]
 lib.bgc_histogram_u8_dev.argtypes = [_P, _P, _Z, _P]
@@ -302,6 +304,17 @@ class Engine:
     def synth_pods_dev(self, params: SynthParams, first: int, count: int, d_ns_id, d_req: list, d_req_mask=None):
         ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
         self._ck(lib.bgc_synth_pods_dev(self._h, C.byref(params), first, count, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask)))
+
+    def synth_pods_shard_dev(self, params: SynthParams, first: int, count: int, world: int, rank: int, d_local_of=None,
+                             out_pos: int = 0, d_ns_id=None, d_req: list | None = None, d_req_mask=None, d_src_index=None) -> int:
+        """One shard (mix32(ns) % world == rank) of pods [first, first+count) of ONE global stream, in stream
+        order, appended at out_pos of the shard columns; d_ns_id=None counts only.  Returns the pods kept."""
+        kept = C.c_uint64()
+        ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req]) if d_req else None
+        cap = d_ns_id.numel() if d_ns_id is not None else 0
+        self._ck(lib.bgc_synth_pods_shard_dev(self._h, C.byref(params), first, count, world, rank, _dev_ptr(d_local_of), out_pos, cap,
+                                              _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask), _dev_ptr(d_src_index), C.byref(kept)))
+        return kept.value
 
     def synth_policy_dev(self, seed: int, first: int, count: int, d_op, d_flags):
         self._ck(lib.bgc_synth_policy_dev(self._h, seed, first, count, _dev_ptr(d_op), _dev_ptr(d_flags)))

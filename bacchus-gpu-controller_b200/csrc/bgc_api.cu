@@ -23,6 +23,7 @@ namespace {
 
 constexpr size_t kChunkPods = size_t(4) << 20;      // host-pointer calls move 4 Mi pods per stage
 constexpr size_t kSmemBudget = 224 * 1024;          // CTA-private K1 table budget (<= 227 KB opt-in)
+constexpr size_t kSmemMaxDynamic = 227 * 1024;      // the opt-in maximum of dynamic shared memory per CTA on sm_100
 constexpr int kSlots = 2;
 constexpr size_t kZeroCopyMaxPods = 262144;         // host batches up to this size take the latency path
 constexpr size_t kZeroCopyBytes = kZeroCopyMaxPods * (4 + 8 * kMaxR + 1 + 2 + 2) + 16 * 256;
@@ -58,6 +59,8 @@ struct bgc_ctx {
   // K1
   int k1_forced = BGC_K1_AUTO;
   int k1_shape = 0;                  // scatter kernel launch shape (tuning knob, see bgc_ctx_set_k1_variant)
+  int k1_prefetch = 0;               // L2 bulk-prefetch distance of the scatter kernel in loop trips (BGC_K1_PREFETCH)
+  int k2_prefetch = 0;               // same for K2 (BGC_K2_PREFETCH)
   const char* last_k1 = "none";
   // staging for host-pointer calls
   size_t zc_max_pods = kZeroCopyMaxPods;  // BGC_ZEROCOPY_MAX_PODS overrides (0 disables the latency path)
@@ -78,6 +81,9 @@ struct bgc_ctx {
   // the caller's pinned buffers, or from this pinned, device-mapped staging area
   uint8_t* zc_host = nullptr;
   uint8_t* zc_dev = nullptr;
+  // one-shard-of-a-global-stream generator (row E): per-tile counts and offsets of one chunk
+  uint32_t* sh_tile_count = nullptr;
+  unsigned long long* sh_tile_off = nullptr;  // [kShardChunkTiles] offsets + 1 total
   bgc_timings tm{};
 };
 
@@ -194,7 +200,7 @@ int launch_k1_scatter(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const l
     int grid = ctx->sm_count;
     if ((size_t)grid * threads > groups) grid = (int)((groups + threads - 1) / threads);
     if (grid < 1) grid = 1;
-    kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->d_used, ctx->NS, cap, ctx->wide_mask);
+    kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->d_used, ctx->NS, cap, ctx->wide_mask, (uint32_t)ctx->k1_prefetch);
     ctx->head_stale = true;
     ctx->tm.launches++;
     CU(cudaGetLastError());
@@ -260,8 +266,12 @@ int launch_k1_r(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long lo
   if (variant == BGC_K1_SMEM_DIRECT && direct_bytes > kSmemBudget) variant = BGC_K1_SMEM_HASH;
   uint32_t cap = ctx->NS;
   if (variant == BGC_K1_SMEM_HASH) {
-    cap = 1;
-    while ((size_t)cap * 2 * (k1_slot_bytes(ctx, R) + 4) <= kSmemBudget) cap *= 2;
+    if (flags & BGC_REDUCE_GROUPED) {  // the segmented kernel hashes by shift: power-of-two slot count
+      cap = 1;
+      while ((size_t)cap * 2 * (k1_slot_bytes(ctx, R) + 4) <= kSmemBudget) cap *= 2;
+    } else {  // the scatter kernel reduces the hash by multiply-shift: every byte of shared memory is a slot
+      cap = (uint32_t)(kSmemMaxDynamic / (k1_slot_bytes(ctx, R) + 4));
+    }
   }
   if (variant == BGC_K1_CLUSTER8 || variant == BGC_K1_CLUSTER16) {
     const int cs = variant == BGC_K1_CLUSTER8 ? 8 : 16;
@@ -348,10 +358,10 @@ int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
   const int grid = grid_for((n + PODS - 1) / PODS, kK2Threads, ctx->sm_count * k2_blocks);
   if (vec)
     k2_quota_eval<R, HAS_MASK, true, VT><<<grid, kK2Threads, 0, st>>>(
-        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict, (uint32_t)ctx->k2_prefetch);
   else
     k2_quota_eval<R, HAS_MASK, false, VT><<<grid, kK2Threads, 0, st>>>(
-        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
+        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict, (uint32_t)ctx->k2_prefetch);
   ctx->tm.launches++;
   CU(cudaGetLastError());
   return BGC_OK;
@@ -520,6 +530,8 @@ int bgc_ctx_create(int device, bgc_ctx** out) {
     return e == cudaErrorMemoryAllocation ? BGC_E_OOM : BGC_E_CUDA;
   }
   ctx->stream = ctx->own_stream;
+  if (const char* v = std::getenv("BGC_K1_PREFETCH")) ctx->k1_prefetch = std::atoi(v) < 0 ? 0 : std::atoi(v);
+  if (const char* v = std::getenv("BGC_K2_PREFETCH")) ctx->k2_prefetch = std::atoi(v) < 0 ? 0 : std::atoi(v);
   if (const char* v = std::getenv("BGC_ZEROCOPY_MAX_PODS")) {
     const long long want = std::atoll(v);
     ctx->zc_max_pods = want < 0 ? 0 : ((size_t)want > kZeroCopyMaxPods ? kZeroCopyMaxPods : (size_t)want);
@@ -544,6 +556,7 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   cudaFree(ctx->head);
   cudaFree(ctx->d_hard_mask);
   cudaFree(ctx->d_scratch);
+  cudaFree(ctx->sh_tile_count); cudaFree(ctx->sh_tile_off);
   cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order);
   cudaFree(ctx->g_seg); cudaFree(ctx->g_temp); cudaFree(ctx->g_mask);
   for (auto q : ctx->g_req) cudaFree(q);
@@ -589,6 +602,8 @@ int bgc_ctx_set_k1_variant(bgc_ctx* ctx, int variant) {
   NEED((variant & 0xFF) >= BGC_K1_AUTO && (variant & 0xFF) <= BGC_K1_CLUSTER16, "unknown K1 variant");
   ctx->k1_forced = variant & 0xFF;
   ctx->k1_shape = (variant >> 8) & 0xFF;  // bits 8..15: scatter launch shape (development knob)
+  if ((variant >> 16) & 0xFF) ctx->k1_prefetch = ((variant >> 16) & 0xFF) - 1;  // bits 16..23: prefetch distance + 1
+  if ((variant >> 24) & 0x7F) ctx->k2_prefetch = ((variant >> 24) & 0x7F) - 1;  // bits 24..30: K2 prefetch distance + 1
   return BGC_OK;
 }
 
@@ -678,33 +693,48 @@ int bgc_quota_table_set(bgc_ctx* ctx, uint32_t ns_count, uint32_t R, const int64
   NEED(ns_count > 0 && ns_count < 0xFFFFFFFFu, "ns_count out of range");
   NEED(R >= 1 && R <= BGC_MAX_R, "R must be 1..BGC_MAX_R");
   NEED(hard && hard_mask && unit, "null table pointer");
+  // validate everything before touching the context, so that a refused call leaves it as it was
+  uint32_t compute_mask = 0, wide_mask = 0;
+  for (uint32_t r = 0; r < R; ++r) {
+    NEED(unit[r] <= BGC_UNIT_BYTES, "unknown unit");
+    if (unit[r] != BGC_UNIT_COUNT) compute_mask |= 1u << r;
+    if (unit[r] == BGC_UNIT_BYTES) wide_mask |= 1u << r;
+  }
   CU(cudaSetDevice(ctx->device));
   CU(cudaDeviceSynchronize());
-  if (ns_count != ctx->NS || (int)R != ctx->R) {
+  // any failure from here on leaves the context WITHOUT a table (later calls return BGC_E_STATE)
+  auto drop_tables = [&] {
     cudaFree(ctx->d_used); ctx->d_used = nullptr;
     cudaFree(ctx->d_hard); ctx->d_hard = nullptr;
     cudaFree(ctx->head); ctx->head = nullptr;
     cudaFree(ctx->d_hard_mask); ctx->d_hard_mask = nullptr;
     ctx->NS = 0; ctx->R = 0;
-    CU(cudaMalloc(&ctx->d_used, (size_t)ns_count * R * 8));
-    CU(cudaMalloc(&ctx->d_hard, (size_t)ns_count * R * 8));
-    CU(cudaMalloc(&ctx->head, (size_t)ns_count * head_words((int)R) * 8));
-    CU(cudaMalloc(&ctx->d_hard_mask, ns_count));
+    ctx->head_stale = true;
+  };
+  auto step = [&](cudaError_t e, const char* what) -> int {
+    if (e == cudaSuccess) return BGC_OK;
+    drop_tables();
+    cudaGetLastError();
+    return fail(ctx, e == cudaErrorMemoryAllocation ? BGC_E_OOM : BGC_E_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  };
+  int rc;
+  if (ns_count != ctx->NS || (int)R != ctx->R) {
+    drop_tables();
+    if ((rc = step(cudaMalloc(&ctx->d_used, (size_t)ns_count * R * 8), "cudaMalloc(used)"))) return rc;
+    if ((rc = step(cudaMalloc(&ctx->d_hard, (size_t)ns_count * R * 8), "cudaMalloc(hard)"))) return rc;
+    if ((rc = step(cudaMalloc(&ctx->head, (size_t)ns_count * head_words((int)R) * 8), "cudaMalloc(headroom)"))) return rc;
+    if ((rc = step(cudaMalloc(&ctx->d_hard_mask, ns_count), "cudaMalloc(hard_mask)"))) return rc;
   }
+  if ((rc = step(cudaMemcpyAsync(ctx->d_hard, hard, (size_t)ns_count * R * 8, cudaMemcpyHostToDevice, ctx->own_stream), "copy(hard)"))) return rc;
+  if ((rc = step(cudaMemcpyAsync(ctx->d_hard_mask, hard_mask, ns_count, cudaMemcpyHostToDevice, ctx->own_stream), "copy(hard_mask)"))) return rc;
+  if ((rc = step(cudaMemsetAsync(ctx->d_used, 0, (size_t)ns_count * R * 8, ctx->own_stream), "clear(used)"))) return rc;
+  if ((rc = step(cudaStreamSynchronize(ctx->own_stream), "sync"))) return rc;
+  // commit
   ctx->NS = ns_count;
   ctx->R = (int)R;
-  ctx->compute_mask = 0;
-  ctx->wide_mask = 0;
+  ctx->compute_mask = compute_mask;
+  ctx->wide_mask = wide_mask;
   ctx->head_stale = true;
-  for (uint32_t r = 0; r < R; ++r) {
-    NEED(unit[r] <= BGC_UNIT_BYTES, "unknown unit");
-    if (unit[r] != BGC_UNIT_COUNT) ctx->compute_mask |= 1u << r;
-    if (unit[r] == BGC_UNIT_BYTES) ctx->wide_mask |= 1u << r;
-  }
-  CU(cudaMemcpyAsync(ctx->d_hard, hard, (size_t)ns_count * R * 8, cudaMemcpyHostToDevice, ctx->own_stream));
-  CU(cudaMemcpyAsync(ctx->d_hard_mask, hard_mask, ns_count, cudaMemcpyHostToDevice, ctx->own_stream));
-  CU(cudaMemsetAsync(ctx->d_used, 0, (size_t)ns_count * R * 8, ctx->own_stream));
-  CU(cudaStreamSynchronize(ctx->own_stream));
   return BGC_OK;
 }
 
@@ -1153,6 +1183,71 @@ int bgc_synth_pods_dev(bgc_ctx* ctx, const bgc_synth_params* p, uint64_t first, 
   k_synth_pods<<<grid, 256, 0, ctx->stream>>>(A, first, count);
   ctx->tm.launches++;
   CU(cudaGetLastError());
+  return BGC_OK;
+}
+
+int bgc_synth_pods_shard_dev(bgc_ctx* ctx, const bgc_synth_params* p, uint64_t first, size_t count, uint32_t world,
+                             uint32_t rank, const uint32_t* d_local_of, uint64_t out_pos, size_t out_capacity,
+                             uint32_t* d_ns_id, int64_t* const* d_req, uint8_t* d_req_mask, uint64_t* d_src_index,
+                             uint64_t* kept_out) {
+  if (!ctx) return BGC_E_BADARG;
+  NEED(p && kept_out, "null pointer");
+  NEED(world >= 1 && rank < world, "rank must be below world");
+  NEED(p->R >= 1 && p->R <= BGC_MAX_R, "R must be 1..BGC_MAX_R");
+  NEED(p->ns_count > 0, "ns_count must be positive");
+  NEED(p->dist != BGC_DIST_ZIPF_CDF || p->d_cdf, "zipf needs a device CDF table");
+  NEED(!p->grouped || p->n_total > 0, "grouped mode needs n_total");
+  NEED(!d_ns_id || d_req, "null request column array");
+  *kept_out = 0;
+  if (count == 0) return BGC_OK;
+  CU(cudaSetDevice(ctx->device));
+  constexpr size_t kChunkTiles = 32768;                         // 2^26 pods per chunk
+  constexpr size_t kChunk = kChunkTiles * (size_t)kShardTile;
+  if (!ctx->sh_tile_count) {
+    CU(cudaMalloc(&ctx->sh_tile_count, kChunkTiles * 4));
+    CU(cudaMalloc(&ctx->sh_tile_off, (kChunkTiles + 1) * 8));
+  }
+  SynthArgs A{};
+  const uint32_t sbase = p->set * 16u;
+  A.key_ns = stream_key(p->seed, sbase + 0);
+  A.key_mask = stream_key(p->seed, sbase + 8);
+  for (uint32_t r = 0; r < p->R; ++r) {
+    A.key_req[r] = stream_key(p->seed, sbase + 1 + r);
+    A.kind[r] = p->kind[r];
+    if (d_ns_id) {
+      NEED(d_req[r], "null request column");
+      A.req[r] = reinterpret_cast<long long*>(d_req[r]);
+    }
+  }
+  A.R = p->R; A.ns_count = p->ns_count; A.dist = p->dist; A.grouped = p->grouped;
+  A.step = p->n_total ? UINT64_MAX / p->n_total : 0;
+  A.a = p->scramble_a; A.b = p->scramble_b;
+  A.cdf = p->d_cdf; A.ns_id = d_ns_id; A.req_mask = d_req_mask;
+  unsigned long long kept = 0;
+  for (size_t off = 0; off < count; off += kChunk) {
+    const size_t m = count - off < kChunk ? count - off : kChunk;
+    const size_t tiles = (m + kShardTile - 1) / kShardTile;
+    const int grid = (int)(tiles < (size_t)ctx->sm_count * 16 ? tiles : (size_t)ctx->sm_count * 16);
+    k_synth_shard_count<<<grid, 256, 0, ctx->stream>>>(A, first + off, m, world, rank, ctx->sh_tile_count);
+    k_scan_tiles<<<1, 1024, 0, ctx->stream>>>(ctx->sh_tile_count, tiles, out_pos + kept, ctx->sh_tile_off,
+                                              ctx->sh_tile_off + kChunkTiles);
+    ctx->tm.launches += 2;
+    CU(cudaGetLastError());
+    unsigned long long got = 0;
+    CU(cudaMemcpyAsync(&got, ctx->sh_tile_off + kChunkTiles, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (d_ns_id) {
+      if (out_pos + kept + got > out_capacity)
+        return fail(ctx, BGC_E_BADARG, "shard columns hold %zu pods, this shard needs at least %llu", out_capacity,
+                    (unsigned long long)(out_pos + kept + got));
+      k_synth_shard_emit<<<grid, 256, 0, ctx->stream>>>(A, first + off, m, world, rank, d_local_of, ctx->sh_tile_off,
+                                                        reinterpret_cast<unsigned long long*>(d_src_index));
+      ctx->tm.launches++;
+      CU(cudaGetLastError());
+    }
+    kept += got;
+  }
+  *kept_out = kept;
   return BGC_OK;
 }
 

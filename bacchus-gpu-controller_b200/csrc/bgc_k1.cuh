@@ -225,6 +225,11 @@ k1_usage_reduce(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, lo
 // U groups of 4 consecutive pods, issues all of its loads, then all of its shared-memory atomics
 // (native 32-bit ATOMS on shared-window addresses, so no generic-address conversion per access),
 // and only afterwards looks at the returned old values to propagate the rare carries.
+// One lane asks L2 for a contiguous range (TMA-style bulk prefetch, no registers, no shared memory):
+// keeps HBM requests in flight while the warp is busy with its shared-memory atomics.
+__device__ __forceinline__ void prefetch_l2_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ uint32_t atoms_add_u32(uint32_t saddr, uint32_t v) {
   uint32_t old;
   asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(saddr), "r"(v));
@@ -247,23 +252,12 @@ __device__ __forceinline__ uint32_t atoms_cas_u32(uint32_t saddr, uint32_t cmp, 
 template <int R, int SINK>
 struct ScatterCtx {
   long long* used;
-  uint32_t NS, cap, wide_mask, hash_shift;
+  uint32_t NS, cap, wide_mask;
   uint32_t lo_base[R];  // shared-window byte address of column r's low words
   uint32_t hi_base[R];  // ... of its high words (wide columns only)
   uint32_t key_base;
 
   // slot of a namespace in the CTA-private table, or kHashEmpty when it has none (hash sink, cold)
-  __device__ __forceinline__ uint32_t slot_of(uint32_t ns) const {
-    if (SINK == SINK_DIRECT) return ns;
-    const uint32_t s = slot_hash(ns, hash_shift);
-    const uint32_t kaddr = key_base + s * 4u;
-    uint32_t k = lds_u32(kaddr);
-    if (k == kHashEmpty) {
-      k = atoms_cas_u32(kaddr, kHashEmpty, ns);
-      if (k == kHashEmpty) k = ns;
-    }
-    return k == ns ? s : kHashEmpty;
-  }
 };
 
 template <int R, int SINK, int PODS>
@@ -279,8 +273,8 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
 #pragma unroll
     for (int k = 0; k < PODS; ++k) {
       const uint32_t h = mix32(ns[k]);
-      s1[k] = h >> C.hash_shift;
-      s2[k] = h & (C.cap - 1u);
+      s1[k] = __umulhi(h, C.cap);                 // multiply-shift range reduction: any capacity,
+      s2[k] = __umulhi(h * 0x9E3779B1u, C.cap);   // so the table uses all of shared memory
       k1[k] = lds_u32(C.key_base + s1[k] * 4u);
       k2[k] = lds_u32(C.key_base + s2[k] * 4u);
     }
@@ -340,10 +334,30 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
   }
 }
 
+// The hash sink keeps two candidate slots, two keys, the chosen slot and R old values per pod live on
+// top of the loaded columns: with four pods at once a 64-register thread spills.  Two pods at a time
+// fit; the loads were all issued before, so nothing is lost on the memory side.
+template <int R, int SINK, int PODS>
+__device__ __forceinline__ void scatter_group(const ScatterCtx<R, SINK>& C, const uint32_t (&ns)[PODS],
+                                              const long long (&q)[R][PODS]) {
+  if constexpr (SINK == SINK_HASH && PODS == 4) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t ns2[2] = {ns[2 * h], ns[2 * h + 1]};
+      long long q2[R][2];
+#pragma unroll
+      for (int r = 0; r < R; ++r) { q2[r][0] = q[r][2 * h]; q2[r][1] = q[r][2 * h + 1]; }
+      scatter_pods<R, SINK, 2>(C, ns2, q2);
+    }
+  } else {
+    scatter_pods<R, SINK, PODS>(C, ns, q);
+  }
+}
+
 template <int R, int SINK, bool VEC, int THREADS, int U>
 __global__ void __launch_bounds__(THREADS, 1)
 k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long long* used, uint32_t NS,
-           uint32_t cap, uint32_t wide_mask) {
+           uint32_t cap, uint32_t wide_mask, uint32_t pf_dist) {
   extern __shared__ __align__(16) uint32_t k1_smem[];
   const uint32_t nwide = __popc(wide_mask & ((1u << R) - 1u));
   const uint32_t words = (R + nwide) * cap;
@@ -352,7 +366,6 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long lo
     for (uint32_t i = threadIdx.x; i < cap; i += THREADS) k1_smem[words + i] = kHashEmpty;
   ScatterCtx<R, SINK> C;
   C.used = used; C.NS = NS; C.cap = cap; C.wide_mask = wide_mask;
-  C.hash_shift = 32 - (31 - __clz(cap | 1));
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(k1_smem);
 #pragma unroll
   for (int r = 0; r < R; ++r) {
@@ -368,6 +381,17 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long lo
   size_t g = (size_t)blockIdx.x * THREADS + threadIdx.x;
   // U groups per trip: all loads first (U*(1+R) independent vector requests per thread)
   for (; g + (U - 1) * stride < groups; g += U * stride) {
+    if (pf_dist && (threadIdx.x & 31u) == 0) {  // the warp's tiles pf_dist trips ahead, whole tiles only
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const size_t gp = g + ((size_t)pf_dist * U + u) * stride;
+        if (gp + 32 <= groups) {
+          prefetch_l2_bulk(ns_id + gp * PODS, 32u * PODS * 4u);
+#pragma unroll
+          for (int r = 0; r < R; ++r) prefetch_l2_bulk(req.p[r] + gp * PODS, 32u * PODS * 8u);
+        }
+      }
+    }
     uint32_t ns[U][PODS];
     long long q[U][R][PODS];
 #pragma unroll
@@ -378,7 +402,7 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long lo
       for (int r = 0; r < R; ++r) ldg_req<PODS>(req.p[r] + base, q[u][r]);
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) scatter_pods<R, SINK, PODS>(C, ns[u], q[u]);
+    for (int u = 0; u < U; ++u) scatter_group<R, SINK, PODS>(C, ns[u], q[u]);
   }
   for (; g < groups; g += stride) {
     uint32_t ns[PODS];
@@ -387,7 +411,7 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long lo
     ldg_ns<PODS>(ns_id + base, ns);
 #pragma unroll
     for (int r = 0; r < R; ++r) ldg_req<PODS>(req.p[r] + base, q[r]);
-    scatter_pods<R, SINK, PODS>(C, ns, q);
+    scatter_group<R, SINK, PODS>(C, ns, q);
   }
   // scalar tail (and everything when the columns are not 16/32-byte aligned)
   for (size_t i = groups * PODS + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {

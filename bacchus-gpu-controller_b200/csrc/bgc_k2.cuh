@@ -74,13 +74,22 @@ template <int R, bool HAS_MASK, bool VEC, typename VT>
 __global__ void __launch_bounds__(kK2Threads)
 k2_quota_eval(const uint32_t* __restrict__ ns_id, ReqCols<R> req, const uint8_t* __restrict__ req_mask,
               size_t n, const long long* __restrict__ head, const uint8_t* __restrict__ hard_mask,
-              uint32_t NS, uint32_t compute_mask, VT* __restrict__ verdict) {
+              uint32_t NS, uint32_t compute_mask, VT* __restrict__ verdict, uint32_t pf_dist) {
   constexpr int PODS = R <= 4 ? 4 : 2;
   constexpr int SHIFT = sizeof(VT) == 1 ? 4 : 8;
   const size_t groups = VEC ? n / PODS : 0;
   for (size_t g = (size_t)blockIdx.x * kK2Threads + threadIdx.x; g < groups;
        g += (size_t)gridDim.x * kK2Threads) {
     const size_t base = g * PODS;
+    if (pf_dist && (threadIdx.x & 31u) == 0) {  // L2 bulk prefetch of the warp's tile pf_dist trips ahead
+      const size_t gp = g + (size_t)pf_dist * gridDim.x * kK2Threads;
+      if (gp + 32 <= groups) {
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ns_id + gp * PODS), "r"(32u * PODS * 4u) : "memory");
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(req.p[r] + gp * PODS), "r"(32u * PODS * 8u) : "memory");
+      }
+    }
     uint32_t ns[PODS];
     long long q[R][PODS];
     ldg_ns<PODS>(ns_id + base, ns);

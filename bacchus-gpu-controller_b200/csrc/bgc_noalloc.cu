@@ -18,8 +18,11 @@
 // Things a user must know:
 //   * It works on the CURRENT device (the one the pointers belong to).  The first call on each
 //     device performs a one-time set-up — it asks the runtime for the device address of the
-//     static array (cudaGetSymbolAddress) and opts the kernels into large shared memory.  Make
-//     that first call before starting any stream capture on that device.
+//     static array (cudaGetSymbolAddress), and loads and configures every kernel any later call
+//     can launch (all R, both table kinds, aligned and unaligned builds), so that no later call
+//     triggers a lazy module load.  Make that first call before starting any stream capture on
+//     that device.  The address is cached for the life of the process: after cudaDeviceReset()
+//     on that device it is stale, so do not reset a device this entry point has been used on.
 //   * ns_count above BGC_STATIC_MAX_NS (or R outside 1..4) is rejected with BGC_E_BADARG
 //     and a message in `errbuf`; nothing is launched.
 //   * Every call on a device shares the one array, and the array keeps whatever the previous call
@@ -39,7 +42,7 @@ namespace {
 
 constexpr int kMaxDevices = 64;
 constexpr int kStaticMaxR = 4;  // columns the static table is sized for
-constexpr size_t kStaticSmemBudget = 200 * 1024;
+constexpr size_t kStaticSmemBytes = 227 * 1024;  // per-CTA shared-memory table of the scatter kernel
 
 // The scratch itself: the [R][ns_count] usage table the kernel accumulates into.  In HOST code the
 // name `g_static_used` is only a handle for the runtime (a host-side shadow symbol), not a device
@@ -50,6 +53,7 @@ struct PerDevice {
   bool ready = false;
   long long* used = nullptr;  // device address of g_static_used on this device
   int sm_count = 0;
+  int seg_blocks_per_sm[kStaticMaxR + 1][2] = {};  // occupancy of the segmented kernel, per R and alignment
 };
 PerDevice g_dev[kMaxDevices];
 std::mutex g_mu;
@@ -70,6 +74,22 @@ int say(char* errbuf, size_t cap, int code, const char* fmt, ...) {
     if (e_ != cudaSuccess) return say(errbuf, errbuf_len, BGC_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
   } while (0)
 
+// Everything the entry point can launch for one R: the segmented kernel (grouped input) and the
+// scatter kernel with its direct and hash tables, each in an aligned and an unaligned build.  With
+// CUDA's lazy module loading a kernel is loaded on first use, and loading may allocate or
+// synchronise — so every one of them is touched here, during the one-time set-up, and the
+// per-call path only launches.
+template <int R>
+int prepare_r(PerDevice& d, char* errbuf, size_t errbuf_len) {
+  SCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.seg_blocks_per_sm[R][0], k1_usage_reduce<R, SINK_GLOBAL, false>, 512, 0));
+  SCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.seg_blocks_per_sm[R][1], k1_usage_reduce<R, SINK_GLOBAL, true>, 512, 0));
+  SCU(cudaFuncSetAttribute(k1_scatter<R, SINK_DIRECT, false, 1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStaticSmemBytes));
+  SCU(cudaFuncSetAttribute(k1_scatter<R, SINK_DIRECT, true, 1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStaticSmemBytes));
+  SCU(cudaFuncSetAttribute(k1_scatter<R, SINK_HASH, false, 1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStaticSmemBytes));
+  SCU(cudaFuncSetAttribute(k1_scatter<R, SINK_HASH, true, 1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStaticSmemBytes));
+  return BGC_OK;
+}
+
 // one-time set-up for the current device (called under g_mu)
 int setup_device(int dev, char* errbuf, size_t errbuf_len) {
   PerDevice& d = g_dev[dev];
@@ -77,27 +97,24 @@ int setup_device(int dev, char* errbuf, size_t errbuf_len) {
   SCU(cudaGetSymbolAddress(&p, g_static_used));
   if (!p) return say(errbuf, errbuf_len, BGC_E_CUDA, "cudaGetSymbolAddress returned a null address");
   SCU(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+  int rc;
+  if ((rc = prepare_r<1>(d, errbuf, errbuf_len)) || (rc = prepare_r<2>(d, errbuf, errbuf_len)) ||
+      (rc = prepare_r<3>(d, errbuf, errbuf_len)) || (rc = prepare_r<4>(d, errbuf, errbuf_len)))
+    return rc;
   d.used = static_cast<long long*>(p);
   d.ready = true;
   return BGC_OK;
 }
 
-template <int R, int SINK, bool VEC>
-int launch_reduce(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const long long* const* req, size_t n,
-                  uint32_t NS, uint32_t cap, char* errbuf, size_t errbuf_len) {
+// grouped input: segmented warp-shuffle reduction, one global red per run of equal namespaces
+template <int R, bool VEC>
+int launch_segmented(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const long long* const* req, size_t n,
+                     uint32_t NS, char* errbuf, size_t errbuf_len) {
   ReqCols<R> cols;
   for (int r = 0; r < R; ++r) cols.p[r] = req[r];
-  auto kern = k1_usage_reduce<R, SINK, VEC>;
-  size_t smem = 0;
-  int threads = 512, blocks_per_sm = 1;
-  if (SINK == SINK_GLOBAL) {
-    SCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, threads, 0));
-    if (blocks_per_sm < 1) blocks_per_sm = 1;
-  } else {
-    threads = 1024;
-    smem = (size_t)2 * R * cap * 4 + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
-    SCU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  }
+  const int threads = 512;
+  int blocks_per_sm = d.seg_blocks_per_sm[R][VEC ? 1 : 0];
+  if (blocks_per_sm < 1) blocks_per_sm = 1;
   const size_t tiles = (n + kK1Tile - 1) / kK1Tile;
   const size_t wpb = threads / 32;
   int grid = d.sm_count * blocks_per_sm;
@@ -106,7 +123,26 @@ int launch_reduce(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const
   size_t chunk_tiles = tiles / ((size_t)grid * wpb * 4);
   if (chunk_tiles < 1) chunk_tiles = 1;
   if (chunk_tiles > 32) chunk_tiles = 32;
-  kern<<<grid, threads, smem, st>>>(ns, cols, n, d.used, NS, cap, (uint32_t)chunk_tiles, (1u << R) - 1u);
+  k1_usage_reduce<R, SINK_GLOBAL, VEC><<<grid, threads, 0, st>>>(ns, cols, n, d.used, NS, NS, (uint32_t)chunk_tiles, (1u << R) - 1u);
+  SCU(cudaGetLastError());
+  return BGC_OK;
+}
+
+// arrival-order input: the scatter kernel with a CTA-private shared-memory table (indexed by
+// namespace when the table fits, claim-once hash slots otherwise), flushed into the static array.
+// Every column keeps both 32-bit halves in shared memory (this entry point is not told the units).
+template <int R, int SINK, bool VEC>
+int launch_scatter(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const long long* const* req, size_t n,
+                   uint32_t NS, uint32_t cap, char* errbuf, size_t errbuf_len) {
+  ReqCols<R> cols;
+  for (int r = 0; r < R; ++r) cols.p[r] = req[r];
+  const size_t smem = (size_t)cap * (8 * R + (SINK == SINK_HASH ? 4 : 0));
+  const int threads = 1024;
+  const size_t groups = (n + 1) / 2;
+  int grid = d.sm_count;
+  if ((size_t)grid * threads > groups) grid = (int)((groups + threads - 1) / threads);
+  if (grid < 1) grid = 1;
+  k1_scatter<R, SINK, VEC, 1024, 1><<<grid, threads, smem, st>>>(ns, cols, n, d.used, NS, cap, (1u << R) - 1u, 0u);
   SCU(cudaGetLastError());
   return BGC_OK;
 }
@@ -116,17 +152,15 @@ int reduce_r(const PerDevice& d, cudaStream_t st, const uint32_t* ns, const long
              uint32_t NS, unsigned flags, char* errbuf, size_t errbuf_len) {
   bool vec = (reinterpret_cast<uintptr_t>(ns) & 15) == 0;
   for (int r = 0; r < R; ++r) vec = vec && (reinterpret_cast<uintptr_t>(req[r]) & 31) == 0;
-  const bool direct_fits = (size_t)NS * R * 8 <= kStaticSmemBudget;
   if (flags & BGC_REDUCE_GROUPED)
-    return vec ? launch_reduce<R, SINK_GLOBAL, true>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len)
-               : launch_reduce<R, SINK_GLOBAL, false>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len);
-  if (direct_fits)
-    return vec ? launch_reduce<R, SINK_DIRECT, true>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len)
-               : launch_reduce<R, SINK_DIRECT, false>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len);
-  uint32_t cap = 1;
-  while ((size_t)cap * 2 * (8 * R + 4) <= kStaticSmemBudget) cap *= 2;
-  return vec ? launch_reduce<R, SINK_HASH, true>(d, st, ns, req, n, NS, cap, errbuf, errbuf_len)
-             : launch_reduce<R, SINK_HASH, false>(d, st, ns, req, n, NS, cap, errbuf, errbuf_len);
+    return vec ? launch_segmented<R, true>(d, st, ns, req, n, NS, errbuf, errbuf_len)
+               : launch_segmented<R, false>(d, st, ns, req, n, NS, errbuf, errbuf_len);
+  if ((size_t)NS * R * 8 <= kStaticSmemBytes)
+    return vec ? launch_scatter<R, SINK_DIRECT, true>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len)
+               : launch_scatter<R, SINK_DIRECT, false>(d, st, ns, req, n, NS, NS, errbuf, errbuf_len);
+  const uint32_t cap = (uint32_t)(kStaticSmemBytes / (8 * R + 4));
+  return vec ? launch_scatter<R, SINK_HASH, true>(d, st, ns, req, n, NS, cap, errbuf, errbuf_len)
+             : launch_scatter<R, SINK_HASH, false>(d, st, ns, req, n, NS, cap, errbuf, errbuf_len);
 }
 
 }  // namespace

@@ -49,6 +49,16 @@ def owned_namespaces(NS: int, world: int, rank: int) -> np.ndarray:
     return ids[shard_of(ids, world) == rank]
 
 
+def local_ids(NS: int, world: int, rank: int):
+    """(owned global ids in increasing order, local_of[NS]): the dense per-shard id of every owned
+    namespace (0xFFFFFFFF for namespaces other ranks own).  A shard's tables then have
+    len(owned) ~ NS/world rows instead of NS."""
+    owned = owned_namespaces(NS, world, rank)
+    local_of = np.full(NS, 0xFFFFFFFF, dtype=np.uint32)
+    local_of[owned] = np.arange(owned.shape[0], dtype=np.uint32)
+    return owned, local_of
+
+
 # ---- row N5: the alternative with one exchange step (SURVEY.md §8(e)(b)) ----------------------------
 def index_slice(n_total: int, world: int, rank: int) -> tuple:
     """Pods sharded by INDEX: no host partition pass and perfect balance even under Zipf; every rank

@@ -188,8 +188,9 @@ int bgc_admit_greedy_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *c
  *     device pointers owned by the caller;
  *   - ns_count > BGC_STATIC_MAX_NS or R outside 1..4 → BGC_E_BADARG, message in errbuf
  *     (errbuf may be NULL);
- *   - the first call on a device does a one-time set-up (resolves the array's device address);
- *     make that call before any stream capture on the device;
+ *   - the first call on a device does a one-time set-up (resolves the array's device address and
+ *     loads every kernel a later call can launch); make that call before any stream capture on the
+ *     device, and do not cudaDeviceReset() a device afterwards (the cached address would be stale);
  *   - all calls on a device share the one table, which keeps the last call's contents: each call
  *     clears what it uses first, and calls that overlap on the GPU race — serialise them;
  *   - flags: BGC_REDUCE_GROUPED only. */

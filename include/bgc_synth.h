@@ -34,6 +34,20 @@ typedef struct bgc_synth_params {
 /* fill pods [first, first+count) into device columns; d_req_mask may be NULL */
 int bgc_synth_pods_dev(bgc_ctx *ctx, const bgc_synth_params *p, uint64_t first, size_t count,
                        uint32_t *d_ns_id, int64_t *const *d_req, uint8_t *d_req_mask);
+/* Row E: ONE shard of ONE global stream.  Of pods [first, first+count) of the
+ * stream, keep those whose namespace hashes to this rank — mix32(ns_id) % world == rank, the same
+ * murmur3 finaliser as shard.py — in stream order, and append them at position out_pos of the shard
+ * columns (out_capacity = pods the columns can hold).  d_local_of (optional, u32[ns_count]) rewrites
+ * each kept pod's global namespace id into the shard's dense id (every rank owns about ns_count/world
+ * namespaces: the host flattener would hand each shard its own dense ids); d_src_index (optional)
+ * receives each kept pod's position in the global stream — what the host-side gather of verdicts
+ * needs.  d_ns_id == NULL: count only.  *kept_out = pods kept.  Deterministic: the shard is the
+ * global stream filtered, whatever the grid. */
+int bgc_synth_pods_shard_dev(bgc_ctx *ctx, const bgc_synth_params *p, uint64_t first, size_t count,
+                             uint32_t world, uint32_t rank, const uint32_t *d_local_of,
+                             uint64_t out_pos, size_t out_capacity, uint32_t *d_ns_id,
+                             int64_t *const *d_req, uint8_t *d_req_mask, uint64_t *d_src_index,
+                             uint64_t *kept_out);
 /* policy inputs: op in 0..3, flags in 0..1023 */
 int bgc_synth_policy_dev(bgc_ctx *ctx, uint64_t seed, uint64_t first, size_t count, uint8_t *d_op,
                          uint16_t *d_flags);

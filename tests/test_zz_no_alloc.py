@@ -7,9 +7,11 @@ stall all streams with their device-wide synchronisation.  For them the library 
 point that accumulates into a fixed 512 KiB static device table instead of allocated memory.
 
 What is checked here, through the C ABI: the static-table result is bit-identical to the regular
-bgc_usage_reduce_dev on the same device columns, on two calls in a row with different inputs (the
-second call must not see the first one's sums, since the table persists between calls), and
-oversized requests are refused with a message instead of being launched.  This file sorts last on
+bgc_usage_reduce_dev on the same device columns AND to the CPU oracle's literal loop, on two calls
+in a row with different inputs (the second call must not see the first one's sums, since the table
+persists between calls); the device's free memory is the same before and after a call (the point
+of the entry point: it allocates nothing once its one-time set-up is done); and oversized requests
+are refused with a message instead of being launched.  This file sorts last on
 purpose, so a `-x` run has already executed every other test when it gets here.
 """
 import ctypes as C
@@ -34,8 +36,8 @@ def _static_reduce(bgc, d_ns, d_req, R, n, NS, flags, d_out, stream=0):
     return rc, err.value.decode()
 
 
-@pytest.mark.parametrize("NS,R,grouped", [(10_000, 3, 0), (STATIC_MAX_NS, 4, 0), (300, 2, 0), (10_000, 3, 1)])
-def test_static_table_matches_regular_entry_point_twice_in_a_row(bgc, engine, NS, R, grouped):
+@pytest.mark.parametrize("NS,R,grouped", [(10_000, 3, 0), (STATIC_MAX_NS, 4, 0), (300, 2, 0), (10_000, 3, 1), (STATIC_MAX_NS, 1, 0), (12_000, 3, 0)])
+def test_static_table_matches_regular_entry_point_twice_in_a_row(bgc, engine, oracle, NS, R, grouped):
     import torch
     from workloads import KINDS, UNITS
     n = 700_003
@@ -54,10 +56,19 @@ def test_static_table_matches_regular_entry_point_twice_in_a_row(bgc, engine, NS
         want = torch.empty(R * NS, dtype=torch.int64, device="cuda")
         engine.usage_reduce_dev(d_ns, d_req, grouped, want)        # existing entry point
         got = torch.full((R * NS,), -1, dtype=torch.int64, device="cuda")
+        if call == 1:
+            # the first call did the one-time set-up; from here on a call must leave the device's free
+            # memory exactly as it found it (no cudaMalloc, no lazily loaded module, nothing)
+            torch.cuda.synchronize()
+            free_before = torch.cuda.mem_get_info()[0]
         rc, msg = _static_reduce(bgc, d_ns, d_req, R, n, NS, grouped, got)
         assert rc == 0, msg
         torch.cuda.synchronize()
+        if call == 1:
+            assert torch.cuda.mem_get_info()[0] == free_before, "the allocation-free entry point changed the free device memory"
         assert torch.equal(got, want), f"call {call}: static-table result differs from bgc_usage_reduce_dev"
+        ref = oracle.usage_reduce(d_ns.cpu().numpy().view(np.uint32), [c.cpu().numpy() for c in d_req], NS)
+        assert np.array_equal(got.cpu().numpy().reshape(R, NS), ref), f"call {call}: static-table result differs from the oracle"
     # an empty batch after two full ones must read back all zeros (nothing left over in the table)
     got = torch.full((R * NS,), -1, dtype=torch.int64, device="cuda")
     rc, msg = _static_reduce(bgc, d_ns, d_req, R, 0, NS, 0, got)
