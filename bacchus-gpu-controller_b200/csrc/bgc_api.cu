@@ -59,8 +59,11 @@ struct bgc_ctx {
   // K1
   int k1_forced = BGC_K1_AUTO;
   int k1_shape = 0;                  // scatter kernel launch shape (tuning knob, see bgc_ctx_set_k1_variant)
-  int k1_prefetch = 0;               // L2 bulk-prefetch distance of the scatter kernel in loop trips (BGC_K1_PREFETCH)
-  int k2_prefetch = 0;               // same for K2 (BGC_K2_PREFETCH)
+  // L2 bulk-prefetch distance in loop trips; -1 = automatic (measured, profiles/r02_probe_*): one trip ahead for
+  // the hash-sink scatter kernel (+4..6 %) and for K2 at R >= 3 (86 % -> 99 % on C3), none for the direct sink,
+  // which is HBM-bound already.  BGC_K1_PREFETCH / BGC_K2_PREFETCH override.
+  int k1_prefetch = -1;
+  int k2_prefetch = -1;
   const char* last_k1 = "none";
   // staging for host-pointer calls
   size_t zc_max_pods = kZeroCopyMaxPods;  // BGC_ZEROCOPY_MAX_PODS overrides (0 disables the latency path)
@@ -196,11 +199,14 @@ int launch_k1_scatter(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const l
   const size_t smem = k1_slot_bytes(ctx, R) * cap + (SINK == SINK_HASH ? (size_t)cap * 4 : 0);
   const size_t groups = (n + 1) / 2;
   auto go = [&](auto kern, int threads) -> int {
-    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // always the opt-in maximum: the attribute is per function and process-wide, and the allocation-free
+    // entry point (bgc_noalloc.cu) launches the same kernels with its own table sizes
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMaxDynamic));
     int grid = ctx->sm_count;
     if ((size_t)grid * threads > groups) grid = (int)((groups + threads - 1) / threads);
     if (grid < 1) grid = 1;
-    kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->d_used, ctx->NS, cap, ctx->wide_mask, (uint32_t)ctx->k1_prefetch);
+    kern<<<grid, threads, smem, st>>>(ns, cols, n, ctx->d_used, ctx->NS, cap, ctx->wide_mask,
+                                      (uint32_t)(ctx->k1_prefetch >= 0 ? ctx->k1_prefetch : (SINK == SINK_HASH ? 1 : 0)));
     ctx->head_stale = true;
     ctx->tm.launches++;
     CU(cudaGetLastError());
@@ -358,10 +364,12 @@ int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
   const int grid = grid_for((n + PODS - 1) / PODS, kK2Threads, ctx->sm_count * k2_blocks);
   if (vec)
     k2_quota_eval<R, HAS_MASK, true, VT><<<grid, kK2Threads, 0, st>>>(
-        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict, (uint32_t)ctx->k2_prefetch);
+        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict,
+        (uint32_t)(ctx->k2_prefetch >= 0 ? ctx->k2_prefetch : (R >= 3 ? 1 : 0)));
   else
     k2_quota_eval<R, HAS_MASK, false, VT><<<grid, kK2Threads, 0, st>>>(
-        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict, (uint32_t)ctx->k2_prefetch);
+        ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict,
+        (uint32_t)(ctx->k2_prefetch >= 0 ? ctx->k2_prefetch : (R >= 3 ? 1 : 0)));
   ctx->tm.launches++;
   CU(cudaGetLastError());
   return BGC_OK;
@@ -530,8 +538,8 @@ int bgc_ctx_create(int device, bgc_ctx** out) {
     return e == cudaErrorMemoryAllocation ? BGC_E_OOM : BGC_E_CUDA;
   }
   ctx->stream = ctx->own_stream;
-  if (const char* v = std::getenv("BGC_K1_PREFETCH")) ctx->k1_prefetch = std::atoi(v) < 0 ? 0 : std::atoi(v);
-  if (const char* v = std::getenv("BGC_K2_PREFETCH")) ctx->k2_prefetch = std::atoi(v) < 0 ? 0 : std::atoi(v);
+  if (const char* v = std::getenv("BGC_K1_PREFETCH")) ctx->k1_prefetch = std::atoi(v);
+  if (const char* v = std::getenv("BGC_K2_PREFETCH")) ctx->k2_prefetch = std::atoi(v);
   if (const char* v = std::getenv("BGC_ZEROCOPY_MAX_PODS")) {
     const long long want = std::atoll(v);
     ctx->zc_max_pods = want < 0 ? 0 : ((size_t)want > kZeroCopyMaxPods ? kZeroCopyMaxPods : (size_t)want);

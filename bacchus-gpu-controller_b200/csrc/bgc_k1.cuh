@@ -256,8 +256,6 @@ struct ScatterCtx {
   uint32_t lo_base[R];  // shared-window byte address of column r's low words
   uint32_t hi_base[R];  // ... of its high words (wide columns only)
   uint32_t key_base;
-
-  // slot of a namespace in the CTA-private table, or kHashEmpty when it has none (hash sink, cold)
 };
 
 template <int R, int SINK, int PODS>
@@ -265,8 +263,40 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
                                              const long long (&q)[R][PODS]) {
   uint32_t slot[PODS];
   uint32_t old[R][PODS];
+  if constexpr (SINK == SINK_DIRECT) {
+    // The direct sink is HBM-bound as it is (and its few branches are rarely divergent: a zero GPU
+    // count is the only common skip); the predicated form below costs it registers for nothing.
+#pragma unroll
+    for (int k = 0; k < PODS; ++k) slot[k] = ns[k] < C.NS ? ns[k] : kHashEmpty;
+#pragma unroll
+    for (int k = 0; k < PODS; ++k) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const uint32_t lo = (uint32_t)(unsigned long long)q[r][k];
+        old[r][k] = 0;
+        if (slot[k] != kHashEmpty && lo) old[r][k] = atoms_add_u32(C.lo_base[r] + slot[k] * 4u, lo);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < PODS; ++k) {
+      if (ns[k] >= C.NS) continue;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const unsigned long long v = (unsigned long long)q[r][k];
+        const uint32_t lo = (uint32_t)v;
+        const uint32_t hi = (uint32_t)(v >> 32) + (uint32_t)(old[r][k] + lo < old[r][k]);
+        if (hi) {
+          if ((C.wide_mask >> r) & 1u) reds_add_u32(C.hi_base[r] + slot[k] * 4u, hi);
+          else red_add_i64(used_at(C.used, C.NS, r, ns[k]), (long long)((unsigned long long)hi << 32));
+        }
+      }
+    }
+  } else {
+  bool valid[PODS], hit[PODS];
+#pragma unroll
+  for (int k = 0; k < PODS; ++k) valid[k] = ns[k] < C.NS;  // kBadNs padding and out-of-range ids contribute nothing
   if (SINK == SINK_HASH) {
-    // Two candidate slots per namespace (top and bottom bits of one mixed word): with a single
+    // Two candidate slots per namespace (two multiply-shift reductions of one mixed word): with a single
     // slot, two HOT namespaces landing on the same slot send the loser's millions of pods to one
     // global address.  All key probes of the group are issued before any is examined.
     uint32_t s1[PODS], s2[PODS], k1[PODS], k2[PODS];
@@ -276,33 +306,43 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
       s1[k] = __umulhi(h, C.cap);                 // multiply-shift range reduction: any capacity,
       s2[k] = __umulhi(h * 0x9E3779B1u, C.cap);   // so the table uses all of shared memory
       k1[k] = lds_u32(C.key_base + s1[k] * 4u);
-      k2[k] = lds_u32(C.key_base + s2[k] * 4u);
+    }
+    // The second candidate is probed only when the first slot is somebody else's: the kernel is bound
+    // by shared-memory wavefronts (ncu: L1TEX the busiest unit at 70 %), and most pods of a skewed
+    // stream sit in their first slot, so this saves most of one LDS per pod (measured +7..12 %).
+#pragma unroll
+    for (int k = 0; k < PODS; ++k) {
+      k2[k] = 0;  // placeholder, never a key that matters: k1 already matched
+      if (k1[k] != ns[k]) k2[k] = lds_u32(C.key_base + s2[k] * 4u);
     }
 #pragma unroll
     for (int k = 0; k < PODS; ++k) {
-      uint32_t got = kHashEmpty;
-      if (ns[k] < C.NS) {
-        if (k1[k] == ns[k]) got = s1[k];
-        else if (k2[k] == ns[k]) got = s2[k];
-        else {
-          if (k1[k] == kHashEmpty) {  // claim-once: first namespace to arrive owns the slot
-            const uint32_t o = atoms_cas_u32(C.key_base + s1[k] * 4u, kHashEmpty, ns[k]);
-            if (o == kHashEmpty || o == ns[k]) got = s1[k];
-          }
-          if (got == kHashEmpty && k2[k] == kHashEmpty && s2[k] != s1[k]) {
-            // a namespace never holds two slots: only one thread per namespace can reach this CAS
-            // with s1 refused, because s1's refusal is permanent once its owner is somebody else
-            const uint32_t o = atoms_cas_u32(C.key_base + s2[k] * 4u, kHashEmpty, ns[k]);
-            if (o == kHashEmpty || o == ns[k]) got = s2[k];
-          }
+      uint32_t got = k1[k] == ns[k] ? s1[k] : (k2[k] == ns[k] ? s2[k] : kHashEmpty);
+      // claim-once: the first namespace to arrive owns a slot.  Rare once the table has filled up,
+      // so this is the one real branch of the body.
+      if (got == kHashEmpty && valid[k] && (k1[k] == kHashEmpty || k2[k] == kHashEmpty)) {
+        if (k1[k] == kHashEmpty) {
+          const uint32_t o = atoms_cas_u32(C.key_base + s1[k] * 4u, kHashEmpty, ns[k]);
+          if (o == kHashEmpty || o == ns[k]) got = s1[k];
+        }
+        if (got == kHashEmpty && k2[k] == kHashEmpty && s2[k] != s1[k]) {
+          // a namespace never holds two slots: only one thread per namespace can reach this CAS
+          // with s1 refused, because s1's refusal is permanent once its owner is somebody else
+          const uint32_t o = atoms_cas_u32(C.key_base + s2[k] * 4u, kHashEmpty, ns[k]);
+          if (o == kHashEmpty || o == ns[k]) got = s2[k];
         }
       }
       slot[k] = got;
+      hit[k] = valid[k] && got != kHashEmpty;
     }
   } else {
 #pragma unroll
-    for (int k = 0; k < PODS; ++k) slot[k] = ns[k] < C.NS ? ns[k] : kHashEmpty;
+    for (int k = 0; k < PODS; ++k) { slot[k] = ns[k]; hit[k] = valid[k]; }
   }
+  // (Tried and measured slower, round 2: PTX-predicated atomics — ptxas turns them back into
+  // BSSY/BRA/op/BSYNC — and unconditional atomics with slot-less pods adding into per-lane dummy
+  // words: the kernel is bound by shared-memory atomic wavefronts (ncu: L1TEX 70 %, the busiest
+  // unit), so every skipped zero addend counts for more than the branch that skips it.)
   // phase 1: every low-word atomic of the group is in flight before any result is consumed
 #pragma unroll
   for (int k = 0; k < PODS; ++k) {
@@ -310,17 +350,17 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
     for (int r = 0; r < R; ++r) {
       const uint32_t lo = (uint32_t)(unsigned long long)q[r][k];
       old[r][k] = 0;
-      if (slot[k] != kHashEmpty && lo) old[r][k] = atoms_add_u32(C.lo_base[r] + slot[k] * 4u, lo);
+      if (hit[k] && lo) old[r][k] = atoms_add_u32(C.lo_base[r] + slot[k] * 4u, lo);
     }
   }
   // phase 2: high words and carries
 #pragma unroll
   for (int k = 0; k < PODS; ++k) {
-    if (ns[k] >= C.NS) continue;
+    if (!valid[k]) continue;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const unsigned long long v = (unsigned long long)q[r][k];
-      if (slot[k] == kHashEmpty) {  // cold namespace of the hash sink: straight to the global table
+      if (!hit[k]) {  // cold namespace of the hash sink: straight to the global table
         if (v) red_add_i64(used_at(C.used, C.NS, r, ns[k]), (long long)v);
         continue;
       }
@@ -332,6 +372,7 @@ __device__ __forceinline__ void scatter_pods(const ScatterCtx<R, SINK>& C, const
       }
     }
   }
+  }  // hash sink
 }
 
 // The hash sink keeps two candidate slots, two keys, the chosen slot and R old values per pod live on
@@ -359,8 +400,10 @@ __global__ void __launch_bounds__(THREADS, 1)
 k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long long* used, uint32_t NS,
            uint32_t cap, uint32_t wide_mask, uint32_t pf_dist) {
   extern __shared__ __align__(16) uint32_t k1_smem[];
+  // layout: R low-word columns, then one high-word column per wide resource, then (hash) the keys.
+  const uint32_t colw = cap;
   const uint32_t nwide = __popc(wide_mask & ((1u << R) - 1u));
-  const uint32_t words = (R + nwide) * cap;
+  const uint32_t words = (R + nwide) * colw;
   for (uint32_t i = threadIdx.x; i < words; i += THREADS) k1_smem[i] = 0;
   if (SINK == SINK_HASH)
     for (uint32_t i = threadIdx.x; i < cap; i += THREADS) k1_smem[words + i] = kHashEmpty;
@@ -369,8 +412,8 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long lo
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(k1_smem);
 #pragma unroll
   for (int r = 0; r < R; ++r) {
-    C.lo_base[r] = sbase + (uint32_t)r * cap * 4u;
-    C.hi_base[r] = sbase + (R + __popc(wide_mask & ((1u << r) - 1u))) * cap * 4u;
+    C.lo_base[r] = sbase + (uint32_t)r * colw * 4u;
+    C.hi_base[r] = sbase + (R + __popc(wide_mask & ((1u << r) - 1u))) * colw * 4u;
   }
   C.key_base = sbase + words * 4u;
   __syncthreads();
@@ -425,8 +468,8 @@ k1_scatter(const uint32_t* __restrict__ ns_id, ReqCols<R> req, size_t n, long lo
   __syncthreads();
   for (uint32_t i = threadIdx.x; i < R * cap; i += THREADS) {
     const uint32_t r = i / cap, sl = i - r * cap;
-    const uint32_t hi = ((wide_mask >> r) & 1u) ? k1_smem[(R + __popc(wide_mask & ((1u << r) - 1u))) * cap + sl] : 0u;
-    const unsigned long long v = ((unsigned long long)hi << 32) | k1_smem[i];
+    const uint32_t hi = ((wide_mask >> r) & 1u) ? k1_smem[(R + __popc(wide_mask & ((1u << r) - 1u))) * colw + sl] : 0u;
+    const unsigned long long v = ((unsigned long long)hi << 32) | k1_smem[r * colw + sl];
     if (v) {
       const uint32_t ns = (SINK == SINK_HASH) ? k1_smem[words + sl] : sl;
       red_add_i64(used_at(used, NS, r, ns), (long long)v);
