@@ -43,7 +43,8 @@ EXPORTS = [
     "bgc_ctx_create", "bgc_ctx_destroy", "bgc_last_error", "bgc_ctx_set_stream", "bgc_ctx_reset_stream", "bgc_ctx_sync",
     "bgc_timings_get", "bgc_policy_eval", "bgc_policy_eval_dev", "bgc_quota_table_set",
     "bgc_usage_reduce", "bgc_usage_reduce_dev", "bgc_usage_get", "bgc_usage_set", "bgc_usage_get_dev", "bgc_usage_set_dev", "bgc_quota_eval", "bgc_quota_eval16", "bgc_quota_eval16_dev",
-    "bgc_quota_eval_dev", "bgc_ctx_set_k1_variant", "bgc_last_k1_variant", "bgc_version",
+    "bgc_quota_eval_dev", "bgc_usage_reduce_typed", "bgc_usage_reduce_typed_dev", "bgc_quota_eval_typed", "bgc_quota_eval_typed_dev",
+    "bgc_ctx_set_k1_variant", "bgc_last_k1_variant", "bgc_version",
     "bgc_synth_pods_dev", "bgc_synth_pods_shard_dev", "bgc_synth_policy_dev", "bgc_checksum_u8_dev", "bgc_histogram_u8_dev",
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
     "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
@@ -103,6 +104,37 @@ lib.bgc_synth_pods_shard_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64,
 lib.bgc_synth_policy_dev.argtypes = [_P, C.c_uint64, C.c_uint64, _Z, _P, _P]
 lib.bgc_checksum_u8_dev.argtypes = [_P, _P, C.c_uint64, _Z, C.POINTER(C.c_uint64)]
 lib.bgc_histogram_u8_dev.argtypes = [_P, _P, _Z, _P]
+
+
+T_I64, T_U32, T_U16, T_U8, T_I32 = 0, 1, 2, 3, 4
+_T_OF_NP = {np.dtype(np.int64): T_I64, np.dtype(np.uint32): T_U32, np.dtype(np.uint16): T_U16, np.dtype(np.uint8): T_U8,
+            np.dtype(np.int32): T_I32}
+_T_WIDTH = {T_I64: 8, T_U32: 4, T_U16: 2, T_U8: 1, T_I32: 4}
+
+
+class Col(C.Structure):
+    """bgc_col: one request column of the typed entry points (value = element << shift)."""
+    _fields_ = [("data", C.c_void_p), ("type", C.c_uint8), ("shift", C.c_uint8), ("reserved", C.c_uint8 * 6)]
+
+
+lib.bgc_usage_reduce_typed.argtypes = [_P, _P, C.c_int, C.POINTER(Col), _Z, C.c_uint, _P]
+lib.bgc_usage_reduce_typed_dev.argtypes = [_P, _P, C.c_int, C.POINTER(Col), _Z, C.c_uint, _P]
+lib.bgc_quota_eval_typed.argtypes = [_P, _P, C.c_int, C.POINTER(Col), _P, _Z, _P]
+lib.bgc_quota_eval_typed_dev.argtypes = [_P, _P, C.c_int, C.POINTER(Col), _P, _Z, _P]
+
+
+def _torch_type(t):
+    import torch
+    return {torch.int64: T_I64, torch.int32: T_I32, torch.uint8: T_U8, torch.int16: T_U16, torch.uint16: T_U16,
+            torch.uint32: T_U32}[t.dtype]
+
+
+def make_cols(ptrs_types_shifts):
+    """[(address, BGC_T_*, shift), ...] -> ctypes array of bgc_col"""
+    arr = (Col * max(1, len(ptrs_types_shifts)))()
+    for i, (ptr, typ, sh) in enumerate(ptrs_types_shifts):
+        arr[i].data, arr[i].type, arr[i].shift = ptr, typ, sh
+    return arr
 
 
 class BgcError(RuntimeError):
@@ -267,6 +299,48 @@ class Engine:
         ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
         fn = lib.bgc_quota_eval16_dev if d_verdict.element_size() == 2 else lib.bgc_quota_eval_dev
         self._ck(fn(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask), d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
+
+    # -- rows A3/A4 over narrow columns (bgc_*_typed)
+    def usage_reduce_typed(self, ns_id: np.ndarray, cols: list, shifts=None, flags: int = 0, want_used: bool = True):
+        """ns_id u16/u32, cols any of u8/u16/u32/i32/i64 numpy arrays; value = element << shift."""
+        n = ns_id.shape[0]
+        shifts = shifts or [0] * len(cols)
+        arr = make_cols([(c.ctypes.data, _T_OF_NP[c.dtype], s) for c, s in zip(cols, shifts)])
+        out = np.empty((self.R, self.NS), np.int64) if want_used else None
+        self._ck(lib.bgc_usage_reduce_typed(self._h, _np_ptr(ns_id), _T_OF_NP[ns_id.dtype], arr, n, flags, _np_ptr(out)))
+        return out
+
+    def quota_eval_typed(self, ns_id: np.ndarray, cols: list, shifts=None, req_mask: np.ndarray | None = None) -> np.ndarray:
+        n = ns_id.shape[0]
+        shifts = shifts or [0] * len(cols)
+        arr = make_cols([(c.ctypes.data, _T_OF_NP[c.dtype], s) for c, s in zip(cols, shifts)])
+        verdict = np.empty(n, np.uint8)
+        self._ck(lib.bgc_quota_eval_typed(self._h, _np_ptr(ns_id), _T_OF_NP[ns_id.dtype], arr, _np_ptr(req_mask), n, _np_ptr(verdict)))
+        return verdict
+
+    def usage_reduce_typed_dev(self, d_ns_id, d_cols: list, shifts=None, flags: int = 0, d_used_out=None, n: int | None = None, types=None):
+        """torch device tensors; int16 tensors are read as u16, int32 as i32 unless `types` says otherwise."""
+        shifts = shifts or [0] * len(d_cols)
+        types = types or [_torch_type(t) for t in d_cols]
+        arr = make_cols([(t.data_ptr(), ty, s) for t, ty, s in zip(d_cols, types, shifts)])
+        ns_t = T_U16 if d_ns_id.element_size() == 2 else T_U32
+        self._ck(lib.bgc_usage_reduce_typed_dev(self._h, _dev_ptr(d_ns_id), ns_t, arr, d_ns_id.numel() if n is None else n, flags,
+                                                _dev_ptr(d_used_out)))
+
+    def quota_eval_typed_dev(self, d_ns_id, d_cols: list, shifts, d_req_mask, d_verdict, n: int | None = None, types=None):
+        shifts = shifts or [0] * len(d_cols)
+        types = types or [_torch_type(t) for t in d_cols]
+        arr = make_cols([(t.data_ptr(), ty, s) for t, ty, s in zip(d_cols, types, shifts)])
+        ns_t = T_U16 if d_ns_id.element_size() == 2 else T_U32
+        self._ck(lib.bgc_quota_eval_typed_dev(self._h, _dev_ptr(d_ns_id), ns_t, arr, _dev_ptr(d_req_mask),
+                                              d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
+
+    def usage_reduce_typed_ptr(self, ns_ptr: int, ns_type: int, cols, n: int, flags: int = 0, used_out_ptr: int = 0):
+        """cols = make_cols([...]) over raw (pinned) host addresses"""
+        self._ck(lib.bgc_usage_reduce_typed(self._h, C.c_void_p(ns_ptr), ns_type, cols, n, flags, C.c_void_p(used_out_ptr)))
+
+    def quota_eval_typed_ptr(self, ns_ptr: int, ns_type: int, cols, mask_ptr: int, n: int, verdict_ptr: int):
+        self._ck(lib.bgc_quota_eval_typed(self._h, C.c_void_p(ns_ptr), ns_type, cols, C.c_void_p(mask_ptr), n, C.c_void_p(verdict_ptr)))
 
     # -- K3 (row N1): sequential admission inside the batch; updates the usage table
     def admit_greedy(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None) -> np.ndarray:

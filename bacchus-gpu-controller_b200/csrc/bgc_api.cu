@@ -1305,3 +1305,5 @@ int bgc_histogram_u8_dev(bgc_ctx* ctx, const uint8_t* d_v, size_t count, uint64_
 }
 
 }  // extern "C"
+
+#include "bgc_api_typed.inl"

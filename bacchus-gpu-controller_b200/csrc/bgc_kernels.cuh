@@ -4,6 +4,7 @@
 // K1 usage_reduce : per-namespace wrapping-i64 usage, no reference function        (row A3)  bgc_k1.cuh
 // K2 quota_eval   : snapshot quota verdict per candidate pod, no reference function (row A4)  bgc_k2.cuh
 // K3 admit_greedy : sequential in-batch admission, no reference function           (row N1)  bgc_k3.cuh
+// K1/K2 over narrow (typed) columns: the same kernels with widening loads                  bgc_typed.cuh
 // plus the counter-based synthetic generator and stream checksums                            bgc_synth_kernels.cuh
 //
 // All of them are HBM-streaming integer kernels: no tensor cores, no TMEM.  What matters is
@@ -15,4 +16,5 @@
 #include "bgc_k1.cuh"
 #include "bgc_k2.cuh"
 #include "bgc_k3.cuh"
+#include "bgc_typed.cuh"
 #include "bgc_synth_kernels.cuh"

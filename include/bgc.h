@@ -19,7 +19,13 @@
  *     data themselves (chunked, double-buffered H2D/D2H); `_dev` variants take DEVICE pointers
  *     and only enqueue kernels on the context's stream (see bgc_ctx_set_stream), so a caller can
  *     time or overlap transfers itself;
- *   - there is NO CPU fallback: without a CUDA device bgc_ctx_create fails with BGC_E_CUDA.
+ *   - there is NO CPU fallback: without a CUDA device bgc_ctx_create fails with BGC_E_CUDA;
+ *   - allocation: bgc_quota_table_set (when NS or R change), the first host-pointer call of a context
+ *     and the first one with a larger batch or more columns than any before (staging buffers, up to
+ *     4 Mi pods per stage), and bgc_admit_greedy* with a larger batch call cudaMalloc/cudaFree and
+ *     cudaDeviceSynchronize; every other call only enqueues work.  A caller that cannot allocate at
+ *     call time warms the context up once with its largest batch, or uses the `_dev` forms (which
+ *     never allocate after bgc_quota_table_set), or bgc_usage_reduce_static_dev below.
  */
 #ifndef BGC_H
 #define BGC_H
@@ -166,6 +172,33 @@ int bgc_quota_eval16(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *
                      const uint8_t *req_mask, size_t n, uint16_t *verdict);
 int bgc_quota_eval16_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
                          const uint8_t *d_req_mask, size_t n, uint16_t *d_verdict);
+
+/* ---- rows A3/A4 over NARROW columns ------------------------------------------------------------
+ * Same results as bgc_usage_reduce / bgc_quota_eval, for callers whose flattener (row A5) can emit compact
+ * columns: end to end the path is PCIe-bound (57 bytes per pod-step with int64 columns), and a GPU count
+ * fits u8, cpu millicores u16/u32, memory is a multiple of Mi, a namespace id fits u16 up to 65,536
+ * namespaces — the key set of src/synchronizer.rs:249-281 in 9 bytes per pod instead of 28.
+ *   value of element x of column r = (int64) x << req[r].shift, wrapping; x is zero- (U8/U16/U32) or
+ *   sign-extended (I32); ns_type is BGC_T_U32 or BGC_T_U16 (ids >= NS are unknown namespaces as usual).
+ * The columns are widened inside the kernels' loads (nothing is expanded in memory), so the narrow bytes
+ * are what crosses PCIe and what is read from HBM.  Input order does not matter (arrival-order kernel;
+ * flags: BGC_REDUCE_ACCUMULATE only).  R and the table come from bgc_quota_table_set as for the int64
+ * forms; verdict encoding as bgc_quota_eval (R <= 4). */
+enum { BGC_T_I64 = 0, BGC_T_U32 = 1, BGC_T_U16 = 2, BGC_T_U8 = 3, BGC_T_I32 = 4 };
+typedef struct bgc_col {
+  const void *data; /* n elements of `type` */
+  uint8_t type;     /* BGC_T_* */
+  uint8_t shift;    /* 0..63 */
+  uint8_t reserved[6];
+} bgc_col;
+int bgc_usage_reduce_typed(bgc_ctx *ctx, const void *ns_id, int ns_type, const bgc_col *req, size_t n,
+                           unsigned flags, int64_t *used_out);
+int bgc_usage_reduce_typed_dev(bgc_ctx *ctx, const void *d_ns_id, int ns_type, const bgc_col *d_req,
+                               size_t n, unsigned flags, int64_t *d_used_out);
+int bgc_quota_eval_typed(bgc_ctx *ctx, const void *ns_id, int ns_type, const bgc_col *req,
+                         const uint8_t *req_mask, size_t n, uint8_t *verdict);
+int bgc_quota_eval_typed_dev(bgc_ctx *ctx, const void *d_ns_id, int ns_type, const bgc_col *d_req,
+                             const uint8_t *d_req_mask, size_t n, uint8_t *d_verdict);
 
 /* ---- row N1: K3 admit_greedy — sequential admission inside one batch -----------
  * No reference function; this is what kube-apiserver does one pod at a time against the

@@ -29,6 +29,20 @@ def build(force: bool = False) -> str:
     return _SO
 
 
+def use_native_build() -> str:
+    """Rebuild the C oracle with -march=native ON THIS MACHINE into _build/liboracle_native.so and load that
+    one from now on.  For the timed CPU baseline only (bench.py): the default build targets x86-64-v3 so that
+    the same .so runs on whatever CPU the GPU box has."""
+    global _lib, _SO
+    out = os.path.join(_HERE, "_build", "liboracle_native.so")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    cc = os.environ.get("ORACLE_CC", "/usr/bin/gcc")
+    subprocess.run([cc, "-O3", "-march=native", "-fopenmp", "-fPIC", "-std=c11", "-shared", "-o", out,
+                    os.path.join(_HERE, "policy_ref.c"), os.path.join(_HERE, "quota_ref.c")], check=True, capture_output=True)
+    _SO, _lib = out, None
+    return out
+
+
 class PolicyRequest(C.Structure):
     _fields_ = [("username", C.c_char_p), ("groups", C.POINTER(C.c_char_p)), ("n_groups", C.c_size_t),
                 ("operation", C.c_int), ("has_object", C.c_int), ("name", C.c_char_p),
@@ -181,6 +195,54 @@ def quota_eval16(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask, 
                                  _p(np.ascontiguousarray(used)), _p(np.ascontiguousarray(hard)), _p(hard_mask),
                                  C.c_uint8(compute_mask), _p(verdict), C.c_int(threads))
     return verdict
+
+
+T_I64, T_U32, T_U16, T_U8, T_I32 = 0, 1, 2, 3, 4
+_NP_OF_T = {T_I64: np.int64, T_U32: np.uint32, T_U16: np.uint16, T_U8: np.uint8, T_I32: np.int32}
+_T_OF_NP = {np.dtype(v): k for k, v in _NP_OF_T.items()}
+
+
+def _typed_args(ns_id, cols, shifts):
+    ns_type = _T_OF_NP[ns_id.dtype]
+    assert ns_type in (T_U32, T_U16)
+    types = np.array([_T_OF_NP[c.dtype] for c in cols], np.uint8)
+    sh = np.array(shifts if shifts is not None else [0] * len(cols), np.uint8)
+    return ns_type, types, sh
+
+
+def usage_workspace(NS, R, threads: int = 1):
+    """Private per-thread tables for usage_reduce_typed / usage_reduce_ws, allocated once by the caller."""
+    return np.zeros(max(1, threads) * R * NS, np.uint64)
+
+
+def usage_reduce_typed(ns_id, cols, shifts, NS, threads: int = 1, workspace=None):
+    """Narrow columns: ns_id u16/u32, cols any of u8/u16/u32/i32/i64, value = element << shift."""
+    R = len(cols)
+    ns_type, types, sh = _typed_args(ns_id, cols, shifts)
+    used = np.empty((R, NS), np.int64)
+    lib().quota_ref_usage_reduce_typed(_p(ns_id), C.c_uint32(ns_type), _ptrs(cols), _p(types), _p(sh), C.c_size_t(ns_id.shape[0]),
+                                       C.c_uint32(NS), C.c_uint32(R), _p(used), C.c_int(threads), _p(workspace))
+    return used
+
+
+def quota_eval_typed(ns_id, cols, shifts, req_mask, NS, used, hard, hard_mask, compute_mask, threads: int = 1):
+    R = len(cols)
+    ns_type, types, sh = _typed_args(ns_id, cols, shifts)
+    n = ns_id.shape[0]
+    verdict = np.empty(n, np.uint8)
+    lib().quota_ref_quota_eval_typed(_p(ns_id), C.c_uint32(ns_type), _ptrs(cols), _p(types), _p(sh), _p(req_mask), C.c_size_t(n),
+                                     C.c_uint32(NS), C.c_uint32(R), _p(np.ascontiguousarray(used)), _p(np.ascontiguousarray(hard)),
+                                     _p(hard_mask), C.c_uint8(compute_mask), _p(verdict), C.c_int(threads))
+    return verdict
+
+
+def usage_reduce_ws(ns_id, req, NS, threads, workspace):
+    """usage_reduce with a caller-owned workspace (no allocation inside the timed call)."""
+    R = len(req)
+    used = np.empty((R, NS), np.int64)
+    lib().quota_ref_usage_reduce_ws(_p(ns_id), _ptrs(req), C.c_size_t(ns_id.shape[0]), C.c_uint32(NS), C.c_uint32(R), _p(used),
+                                    C.c_int(threads), _p(workspace))
+    return used
 
 
 def gen_params(seed, set_, NS, dist, grouped, n_total, a, b, cdf, kinds):

@@ -201,3 +201,119 @@ uint64_t gen_ref_checksum_u8(const uint8_t *v, uint64_t first, size_t count) {
   for (size_t k = 0; k < count; ++k) s += sm64((first + k) ^ ((uint64_t)v[k] << 56));
   return s;
 }
+
+/* ------------------------------------------------------------------ typed (narrow) columns
+ * The same two functions over narrow host columns (the compact form the product's *_typed entry points
+ * take): element types u8/u16/u32/i32/i64, value = widened element << shift (wrapping), ns ids u16 or
+ * u32.  A block of pods is widened into a small thread-local buffer that stays in L1, then the loops
+ * above run on it unchanged, so the typed forms decide exactly what the plain ones decide on the
+ * widened columns. */
+enum { QT_BLOCK = 2048 };
+
+static inline int64_t load_typed(const void *col, uint32_t type, size_t i) {
+  switch (type) {
+    case QUOTA_REF_T_U32: return (int64_t)((const uint32_t *)col)[i];
+    case QUOTA_REF_T_U16: return (int64_t)((const uint16_t *)col)[i];
+    case QUOTA_REF_T_U8:  return (int64_t)((const uint8_t *)col)[i];
+    case QUOTA_REF_T_I32: return (int64_t)((const int32_t *)col)[i];
+    default:              return ((const int64_t *)col)[i];
+  }
+}
+
+static void widen_block(const void *ns_id, uint32_t ns_type, const void *const *cols, const uint8_t *type,
+                        const uint8_t *shift, uint32_t R, size_t i0, size_t m, uint32_t *ns_out,
+                        int64_t (*q_out)[QT_BLOCK]) {
+  if (ns_type == QUOTA_REF_T_U16) for (size_t k = 0; k < m; ++k) ns_out[k] = ((const uint16_t *)ns_id)[i0 + k];
+  else for (size_t k = 0; k < m; ++k) ns_out[k] = ((const uint32_t *)ns_id)[i0 + k];
+  for (uint32_t r = 0; r < R; ++r) {
+    const unsigned sh = shift[r] & 63u;
+    switch (type[r]) { /* one tight loop per element type so the compiler can vectorise the widening */
+      case QUOTA_REF_T_U32: for (size_t k = 0; k < m; ++k) q_out[r][k] = (int64_t)((uint64_t)((const uint32_t *)cols[r])[i0 + k] << sh); break;
+      case QUOTA_REF_T_U16: for (size_t k = 0; k < m; ++k) q_out[r][k] = (int64_t)((uint64_t)((const uint16_t *)cols[r])[i0 + k] << sh); break;
+      case QUOTA_REF_T_U8:  for (size_t k = 0; k < m; ++k) q_out[r][k] = (int64_t)((uint64_t)((const uint8_t *)cols[r])[i0 + k] << sh); break;
+      case QUOTA_REF_T_I32: for (size_t k = 0; k < m; ++k) q_out[r][k] = (int64_t)((uint64_t)(int64_t)((const int32_t *)cols[r])[i0 + k] << sh); break;
+      default:              for (size_t k = 0; k < m; ++k) q_out[r][k] = (int64_t)((uint64_t)((const int64_t *)cols[r])[i0 + k] << sh); break;
+    }
+  }
+  (void)load_typed;
+}
+
+/* workspace: threads * R * NS u64 (private tables), or NULL to allocate per call */
+void quota_ref_usage_reduce_typed(const void *ns_id, uint32_t ns_type, const void *const *cols,
+                                  const uint8_t *type, const uint8_t *shift, size_t n, uint32_t NS,
+                                  uint32_t R, int64_t *used, int threads, uint64_t *workspace) {
+  const size_t tab = (size_t)R * NS;
+  const int T = nthreads(threads);
+  uint64_t *priv = workspace ? workspace : (uint64_t *)malloc((size_t)T * tab * sizeof(uint64_t));
+  const long long blocks = (long long)((n + QT_BLOCK - 1) / QT_BLOCK);
+#ifdef _OPENMP
+#pragma omp parallel num_threads(T)
+#endif
+  {
+#ifdef _OPENMP
+    uint64_t *mine = priv + (size_t)omp_get_thread_num() * tab;
+#else
+    uint64_t *mine = priv;
+#endif
+    memset(mine, 0, tab * sizeof(uint64_t));
+    uint32_t ns[QT_BLOCK];
+    int64_t q[QUOTA_REF_MAX_R][QT_BLOCK];
+#ifdef _OPENMP
+#pragma omp for schedule(static)
+#endif
+    for (long long b = 0; b < blocks; ++b) {
+      const size_t i0 = (size_t)b * QT_BLOCK, m = n - i0 < QT_BLOCK ? n - i0 : QT_BLOCK;
+      widen_block(ns_id, ns_type, cols, type, shift, R, i0, m, ns, q);
+      for (size_t k = 0; k < m; ++k) {
+        if (ns[k] >= NS) continue;
+        for (uint32_t r = 0; r < R; ++r) mine[(size_t)r * NS + ns[k]] += (uint64_t)q[r][k];
+      }
+    }
+#ifdef _OPENMP
+#pragma omp for schedule(static)
+#endif
+    for (long long k = 0; k < (long long)tab; ++k) {
+      uint64_t s = 0;
+      for (int t = 0; t < T; ++t) s += priv[(size_t)t * tab + k];
+      used[k] = (int64_t)s;
+    }
+  }
+  if (!workspace) free(priv);
+}
+
+void quota_ref_quota_eval_typed(const void *ns_id, uint32_t ns_type, const void *const *cols,
+                                const uint8_t *type, const uint8_t *shift, const uint8_t *req_mask,
+                                size_t n, uint32_t NS, uint32_t R, const int64_t *used,
+                                const int64_t *hard, const uint8_t *hard_mask, uint8_t compute_mask,
+                                uint8_t *verdict, int threads) {
+  const long long blocks = (long long)((n + QT_BLOCK - 1) / QT_BLOCK);
+#ifdef _OPENMP
+#pragma omp parallel num_threads(nthreads(threads))
+#endif
+  {
+    uint32_t ns[QT_BLOCK];
+    int64_t q[QUOTA_REF_MAX_R][QT_BLOCK];
+    const int64_t *qp[QUOTA_REF_MAX_R];
+    for (uint32_t r = 0; r < QUOTA_REF_MAX_R; ++r) qp[r] = q[r];
+#ifdef _OPENMP
+#pragma omp for schedule(static)
+#endif
+    for (long long b = 0; b < blocks; ++b) {
+      const size_t i0 = (size_t)b * QT_BLOCK, m = n - i0 < QT_BLOCK ? n - i0 : QT_BLOCK;
+      widen_block(ns_id, ns_type, cols, type, shift, R, i0, m, ns, q);
+      for (size_t k = 0; k < m; ++k)
+        verdict[i0 + k] = eval_one(ns[k], qp, req_mask ? req_mask[i0 + k] : 0xFF, k, NS, R, used, hard,
+                                   hard_mask, compute_mask);
+    }
+  }
+}
+
+/* plain-column usage reduction with a caller-owned workspace (threads * R * NS u64): the all-cores
+ * baseline without a calloc of fresh pages inside every timed call */
+void quota_ref_usage_reduce_ws(const uint32_t *ns_id, const int64_t *const *req, size_t n, uint32_t NS,
+                               uint32_t R, int64_t *used, int threads, uint64_t *workspace) {
+  uint8_t type[QUOTA_REF_MAX_R], shift[QUOTA_REF_MAX_R];
+  const void *cols[QUOTA_REF_MAX_R];
+  for (uint32_t r = 0; r < R; ++r) { type[r] = QUOTA_REF_T_I64; shift[r] = 0; cols[r] = req[r]; }
+  quota_ref_usage_reduce_typed(ns_id, QUOTA_REF_T_U32, cols, type, shift, n, NS, R, used, threads, workspace);
+}

@@ -21,6 +21,8 @@ extern "C" {
 
 #define QUOTA_REF_MAX_R 8
 #define QUOTA_REF_VERDICT_BAD_NS 0xFFu
+/* element types of the typed (narrow-column) forms; value = widened element << shift, wrapping */
+enum { QUOTA_REF_T_I64 = 0, QUOTA_REF_T_U32 = 1, QUOTA_REF_T_U16 = 2, QUOTA_REF_T_U8 = 3, QUOTA_REF_T_I32 = 4 };
 
 /* A3: used[r][ns] = sum over pods i with ns_id[i]==ns of req[r][i], wrapping 64-bit.
  * `used` is [R][NS], zeroed here.  Pods with ns_id >= NS contribute nothing. */
@@ -83,6 +85,18 @@ void gen_ref_policy_fill(uint64_t seed, uint64_t first, size_t count, uint8_t *o
                          uint16_t *flags, int threads);
 /* order-independent checksum of a u8 stream: sum_i SM64(i ^ v[i]<<56 ...) */
 uint64_t gen_ref_checksum_u8(const uint8_t *v, uint64_t first, size_t count);
+
+/* typed forms: the same results as the plain functions on the widened columns (quota_ref.c) */
+void quota_ref_usage_reduce_typed(const void *ns_id, uint32_t ns_type, const void *const *cols,
+                                  const uint8_t *type, const uint8_t *shift, size_t n, uint32_t NS,
+                                  uint32_t R, int64_t *used, int threads, uint64_t *workspace);
+void quota_ref_quota_eval_typed(const void *ns_id, uint32_t ns_type, const void *const *cols,
+                                const uint8_t *type, const uint8_t *shift, const uint8_t *req_mask,
+                                size_t n, uint32_t NS, uint32_t R, const int64_t *used,
+                                const int64_t *hard, const uint8_t *hard_mask, uint8_t compute_mask,
+                                uint8_t *verdict, int threads);
+void quota_ref_usage_reduce_ws(const uint32_t *ns_id, const int64_t *const *req, size_t n, uint32_t NS,
+                               uint32_t R, int64_t *used, int threads, uint64_t *workspace);
 
 #ifdef __cplusplus
 }
