@@ -509,7 +509,7 @@ int finish_timings(bgc_ctx* ctx, const Spans& sp) {
 // =============================================================================== C ABI
 extern "C" {
 
-const char* bgc_version(void) { return "bgc 0.1 (sm_100a)"; }
+const char* bgc_version(void) { return "bgc 0.2 (sm_100a)"; }
 
 int bgc_ctx_create(int device, bgc_ctx** out) {
   if (!out) return BGC_E_BADARG;
