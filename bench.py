@@ -348,7 +348,7 @@ def k3_record(torch, bgc, eng, oracle, Q, wl, seed, peak):
         ms = sorted(ts)[1]
         gbs = n * (4 + 8 * R + 1) / ms / 1e6
         out[name] = {"pods": n, "ms": ms, "pods_per_s": n / ms * 1e3, "achieved_GBps": gbs, "frac": gbs / peak,
-                     "admitted_fraction": float((v[: 1 << 20] == 0).float().mean())}
+                     "admitted_fraction": float((v[::101] == 0).float().mean())}
         del ns, req, v
     return {"kernel": "k3_admit_greedy", "algorithmic_bytes_per_pod": 4 + 8 * R + 1, **out,
             "parity": "bit-exact vs the literal loop in tests/test_gpu_greedy.py (not re-checked at this size)"}
