@@ -16,7 +16,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbgc.so")
+LIB_PATH = os.environ.get("BGC_LIB_PATH") or os.path.join(_HERE, "libbgc.so")   # override: development builds only
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

@@ -32,17 +32,17 @@ struct TypedCols {
 
 __device__ __forceinline__ uint32_t ldg_nc_b32(const void* p) {
   uint32_t v;
-  asm("ld.global.nc.L1::no_allocate.b32 %0, [%1];" : "=r"(v) : "l"(p));
+  asm(BGC_LD_STREAM ".b32 %0, [%1];" : "=r"(v) : "l"(p));
   return v;
 }
 __device__ __forceinline__ uint2 ldg_nc_b64(const void* p) {
   uint2 v;
-  asm("ld.global.nc.L1::no_allocate.v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  asm(BGC_LD_STREAM ".v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
   return v;
 }
 __device__ __forceinline__ uint32_t ldg_nc_b16(const void* p) {
   unsigned short v;
-  asm("ld.global.nc.L1::no_allocate.b16 %0, [%1];" : "=h"(v) : "l"(p));
+  asm(BGC_LD_STREAM ".b16 %0, [%1];" : "=h"(v) : "l"(p));
   return v;
 }
 
