@@ -360,6 +360,23 @@ int launch_k2_inst(bgc_ctx* ctx, cudaStream_t st, const uint32_t* ns, const long
     CU(cudaGetLastError());
     ctx->head_stale = false;
   }
+  // one or two resources and a table that fits shared memory: CTA-private copy of the table (see bgc_k2.cuh)
+  if constexpr (R <= 2 && sizeof(VT) == 1) {
+    static const int use_smem = std::getenv("BGC_K2_SMEM") ? std::atoi(std::getenv("BGC_K2_SMEM")) : 1;
+    const size_t smem = (size_t)ctx->NS * 8 * R + ctx->NS;
+    if (use_smem && smem <= kSmemMaxDynamic && n >= (size_t)ctx->sm_count * 1024 * 8) {
+      const uint32_t pf = (uint32_t)(ctx->k2_prefetch >= 0 ? ctx->k2_prefetch : 1);
+      auto go = [&](auto kern) -> int {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMaxDynamic));
+        kern<<<ctx->sm_count, 1024, smem, st>>>(ns, cols, mask, n, ctx->head, ctx->d_hard_mask, ctx->NS, ctx->compute_mask,
+                                                reinterpret_cast<uint8_t*>(verdict), pf);
+        ctx->tm.launches++;
+        CU(cudaGetLastError());
+        return BGC_OK;
+      };
+      return vec ? go(k2_quota_eval_smem<R, HAS_MASK, true>) : go(k2_quota_eval_smem<R, HAS_MASK, false>);
+    }
+  }
   static const int k2_blocks = std::getenv("BGC_K2_BLOCKS") ? std::atoi(std::getenv("BGC_K2_BLOCKS")) : 32;  // tuning knob
   const int grid = grid_for((n + PODS - 1) / PODS, kK2Threads, ctx->sm_count * k2_blocks);
   if (vec)

@@ -130,4 +130,80 @@ k2_quota_eval(const uint32_t* __restrict__ ns_id, ReqCols<R> req, const uint8_t*
   }
 }
 
+// ------------------------------------------------------------------ K2 with the headroom table in shared memory
+// With one or two resources a pod is 12 or 20 bytes of stream but still one 32-byte sector of table gather:
+// the L2 sector rate (~210 G random sectors/s), not HBM, bounds the kernel at 0.47 ms per 10^8 pods (68 % of
+// the roofline at R=2).  When the table is small enough — NS * (8R + 1) bytes <= 227 KB, i.e. 13,600
+// namespaces at R=2 — every CTA keeps its own copy in shared memory instead: one persistent 1024-thread
+// CTA per SM, h[r][ns] as 64-bit words plus the mask bytes, gathers become LDS and only the pod
+// columns touch L2/HBM.
+template <int R, bool HAS_MASK, bool VEC>
+__global__ void __launch_bounds__(1024, 1)
+k2_quota_eval_smem(const uint32_t* __restrict__ ns_id, ReqCols<R> req, const uint8_t* __restrict__ req_mask, size_t n,
+                   const long long* __restrict__ head, const uint8_t* __restrict__ hard_mask, uint32_t NS,
+                   uint32_t compute_mask, uint8_t* __restrict__ verdict, uint32_t pf_dist) {
+  extern __shared__ __align__(16) long long k2_smem[];
+  constexpr int THREADS = 1024;
+  constexpr int W = head_words(R);
+  long long* s_h = k2_smem;                                        // [R][NS]
+  uint8_t* s_m = reinterpret_cast<uint8_t*>(k2_smem + (size_t)R * NS);  // [NS]
+  for (uint32_t i = threadIdx.x; i < NS; i += THREADS) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) s_h[(size_t)r * NS + i] = head[(size_t)i * W + r];
+    s_m[i] = hard_mask[i];
+  }
+  __syncthreads();
+  auto decide = [&](uint32_t ns, const long long (&q)[R], uint32_t rmask) -> uint32_t {
+    if (ns >= NS) return 0xFFu;
+    const uint32_t hm = s_m[ns];
+    uint32_t missing = 0, exceeded = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const long long h = s_h[(size_t)r * NS + ns];
+      const bool constrained = (hm >> r) & 1u;
+      const bool present = (rmask >> r) & 1u;
+      if (constrained && !present && ((compute_mask >> r) & 1u)) missing |= 1u << r;
+      if (constrained && present && q[r] > 0 && q[r] > h) exceeded |= 1u << r;
+    }
+    return (missing << 4) | exceeded;
+  };
+  constexpr int PODS = 4;
+  const size_t groups = VEC ? n / PODS : 0;
+  const size_t stride = (size_t)gridDim.x * THREADS;
+  for (size_t g = (size_t)blockIdx.x * THREADS + threadIdx.x; g < groups; g += stride) {
+    const size_t base = g * PODS;
+    if (pf_dist && (threadIdx.x & 31u) == 0) {
+      const size_t gp = g + (size_t)pf_dist * stride;
+      if (gp + 32 <= groups) {
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ns_id + gp * PODS), "r"(32u * PODS * 4u) : "memory");
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(req.p[r] + gp * PODS), "r"(32u * PODS * 8u) : "memory");
+      }
+    }
+    uint32_t ns[PODS];
+    long long q[R][PODS];
+    ldg_ns<PODS>(ns_id + base, ns);
+#pragma unroll
+    for (int r = 0; r < R; ++r) ldg_req<PODS>(req.p[r] + base, q[r]);
+    uint32_t rm = 0xFFFFFFFFu;
+    if (HAS_MASK) rm = __ldg(reinterpret_cast<const uint32_t*>(req_mask + base));
+    uint32_t w = 0;
+#pragma unroll
+    for (int k = 0; k < PODS; ++k) {
+      long long qk[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) qk[r] = q[r][k];
+      w |= decide(ns[k], qk, (rm >> (8 * k)) & 0xFFu) << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(verdict + base) = w;
+  }
+  for (size_t i = groups * PODS + (size_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
+    long long qk[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) qk[r] = req.p[r][i];
+    verdict[i] = (uint8_t)decide(ns_id[i], qk, HAS_MASK ? req_mask[i] : 0xFFu);
+  }
+}
+
 }  // namespace bgc

@@ -372,3 +372,40 @@ def test_host_entry_point_infers_the_grouping_hint(engine, oracle):
     for ns, expect in ((grouped, "segmented_global_red"), (shuffled, "scatter_smem_direct")):
         assert np.array_equal(engine.usage_reduce(ns, req), oracle.usage_reduce(ns, req, NS, threads=4))
         assert engine.last_k1_variant() == expect
+
+
+@pytest.mark.parametrize("R", [1, 2])
+@pytest.mark.parametrize("with_mask", [False, True])
+@pytest.mark.parametrize("NS,misalign", [(13_000, 0), (5, 0), (9_999, 1)])
+def test_k2_shared_memory_table_variant(bgc, engine, oracle, R, with_mask, NS, misalign):
+    """Large batches with one or two resources take k2_quota_eval_smem (table copied into shared memory):
+    device pointers, 1.6 M pods, aligned and misaligned columns, unknown namespaces, extreme values."""
+    import torch
+    rng = np.random.default_rng(R * 100 + NS)
+    n = 1_600_003
+    engine.use_torch_stream()
+    ns = rng.integers(0, NS, n, dtype=np.uint32)
+    req = [rng.integers(0, 1 << 36, n, dtype=np.int64) for _ in range(R)]
+    used, hard, hm = _table(engine, oracle, (ns, req), NS, R)
+    hm[::5] = rng.integers(0, 1 << R, hm[::5].shape[0], dtype=np.uint8)
+    hard[:, ::7] = np.iinfo(np.int64).max
+    hard[:, 1::11] = np.iinfo(np.int64).min
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(used)
+    cns = rng.integers(0, NS, n, dtype=np.uint32)
+    creq = [rng.integers(-5, 1 << 34, n, dtype=np.int64) for _ in range(R)]
+    creq[0][::1001] = np.iinfo(np.int64).max
+    cns[::53] = NS + 1
+    cns[1::97] = 0xFFFFFFFF
+    mask = rng.integers(0, 256, n, dtype=np.uint8) if with_mask else None
+    want = oracle.quota_eval(cns, creq, mask, NS, used, hard, hm, _compute_mask(UNITS[R]))
+
+    def dev(a):
+        t = torch.from_numpy(a.view(np.int32) if a.dtype == np.uint32 else a)
+        buf = torch.empty(n + 8, dtype=t.dtype, device="cuda")
+        buf[misalign:misalign + n] = t.cuda()
+        return buf[misalign:misalign + n]
+    d_v = torch.empty(n + 8, dtype=torch.uint8, device="cuda")[misalign:misalign + n]
+    engine.quota_eval_dev(dev(cns), [dev(c) for c in creq], dev(mask) if with_mask else None, d_v)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_v.cpu().numpy(), want)
