@@ -84,12 +84,29 @@ def _render(uid: str, resp: _CResponse, message_override, patch) -> str:
     return buf.value.decode()
 
 
+def _parse_all(bodies):
+    """One Review per body, None where the body is not a well-formed AdmissionReview: like the reference's
+    handler, which rejects only the offending request (src/admission.rs:189-197), a bad body must not cost
+    the other requests of the batch their answers."""
+    out = []
+    for b in bodies:
+        try:
+            out.append(Review(b))
+        except ValueError:
+            out.append(None)
+    return out
+
+
+def _invalid(message: str) -> str:
+    return _render("", _CResponse(0, 3, 0, 0, None), message, None)
+
+
 def handle_reviews(engine: Engine, config: AdmissionConfig, bodies: Sequence[bytes | str]) -> list:
     """Batched `mutate_handler`: one response JSON string per request body.  Reviews without a
     `request` are answered `invalid` like src/admission.rs:189-197; everything else is flattened,
     decided in one K0 launch, and rendered."""
-    reviews = [Review(b) for b in bodies]
-    live = [i for i, r in enumerate(reviews) if r.has_request]
+    reviews = _parse_all(bodies)
+    live = [i for i, r in enumerate(reviews) if r is not None and r.has_request]
     creqs = (_CRequest * max(1, len(live)))()
     for k, i in enumerate(live):
         lib.bgc_review_request(reviews[i]._h, C.byref(creqs[k]))
@@ -107,16 +124,17 @@ def handle_reviews(engine: Engine, config: AdmissionConfig, bodies: Sequence[byt
             patch = pbuf.value
         res[i] = _render(reviews[i].uid, out[k], None, patch)
     for i, r in enumerate(reviews):
-        if res[i] is None:
-            bad = _CResponse(0, 3, 0, 0, None)
-            res[i] = _render("", bad, "invalid request: AdmissionReview carries no request", None)
+        if res[i] is None:   # only the offending request is answered `invalid`; the rest of the batch is served
+            res[i] = _invalid("malformed AdmissionReview" if r is None else "invalid request: AdmissionReview carries no request")
     return res
 
 
-def flatten_pod_reviews(bodies: Sequence[bytes | str], quota_keys: Sequence[str], nsmap, intern: bool = False):
-    """Pod-create AdmissionReviews → (ns_id, req[R], req_mask) columns through bgc_flatten_pods."""
+def flatten_pod_reviews(bodies: Sequence[bytes | str], quota_keys: Sequence[str], nsmap, intern: bool = False, reviews=None):
+    """Pod-create AdmissionReviews → (ns_id, req[R], req_mask) columns through bgc_flatten_pods.
+    `reviews`: already parsed Review objects for `bodies` (so a caller that parsed them does not parse twice)."""
     from .pods import QUOTA_KEYS
-    reviews = [Review(b) for b in bodies]
+    if reviews is None:
+        reviews = [Review(b) for b in bodies]
     n = len(reviews)
     arr = (_Pod * max(1, n))()
     for i, r in enumerate(reviews):
@@ -147,13 +165,23 @@ def handle_pod_reviews(engine, bodies: Sequence[bytes | str], quota_keys: Sequen
     R = len(quota_keys)
     if wide is None:
         wide = R > 4
-    reviews = [Review(b) for b in bodies]
-    ns_id, req, mask, _unit = flatten_pod_reviews(bodies, quota_keys, nsmap, intern=False)
+    parsed = _parse_all(bodies)
+    good = []
+    for i, r in enumerate(parsed):   # a body that is malformed, or carries no pod object, is answered `invalid` on its own
+        if r is None:
+            continue
+        try:
+            r.c_pod()
+            good.append(i)
+        except BgcError:
+            pass
+    reviews = [parsed[i] for i in good]
+    ns_id, req, mask, _unit = flatten_pod_reviews(None, quota_keys, nsmap, intern=False, reviews=reviews)
     if ns_id.shape[0] != len(reviews):
         raise ValueError("terminal pods cannot appear in create reviews")
     verdict = engine.quota_eval(ns_id, req, mask, wide=wide) if wide else engine.quota_eval(ns_id, req, mask)
     bad = 0xFFFF if wide else 0xFF
-    out = []
+    answers = {}
     for i, r in enumerate(reviews):
         v = int(verdict[i])
         if v == 0:
@@ -166,5 +194,6 @@ def handle_pod_reviews(engine, bodies: Sequence[bytes | str], quota_keys: Sequen
                 v, nsmap.name(ns), quota_keys, [int(c[i]) for c in req], [int(used[k][ns]) for k in range(R)],
                 [int(hard[k][ns]) for k in range(R)], wide=wide)
             resp = _CResponse(0, 2, 0, 0, None)
-        out.append(_render(r.uid, resp, msg, None))
-    return out
+        answers[good[i]] = _render(r.uid, resp, msg, None)
+    return [answers.get(i) or _invalid("malformed AdmissionReview" if parsed[i] is None else "invalid request: AdmissionReview carries no pod object")
+            for i in range(len(parsed))]

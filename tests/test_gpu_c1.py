@@ -107,3 +107,53 @@ def test_c1_pod_reviews_against_100_namespace_quotas(bgc, engine):
     deny = np.mean(np.array(want) != 0)
     assert 0.05 < deny < 0.999
     assert verdict[17] == bgc.VERDICT_BAD_NS
+
+
+@pytest.mark.parametrize("wide", [False, True])
+def test_pod_reviews_wire_to_wire_on_the_device(bgc, engine, oracle, wide):
+    """review.handle_pod_reviews with the real Engine: AdmissionReview bytes -> parse -> flatten (row A5) -> K2 on
+    the GPU -> response JSON, against the oracle's verdicts on the flattened columns; one malformed body and one
+    body without an object in the middle of the batch are answered `invalid` on their own.  Seam:
+    src/admission.rs:184-204; webhook registration charts/.../templates/webhook.yaml:10-27."""
+    from workloads import C1_KEYS6
+    keys = C1_KEYS6 if wide else C1_KEYS
+    nss = c1_namespaces()
+    m = bgc.pods.NamespaceMap()
+    for ns in nss:
+        m.intern(ns["name"])
+    R = len(keys)
+    hard = np.zeros((R, len(nss)), np.int64)
+    hm = np.zeros(len(nss), np.uint8)
+    for i, ns in enumerate(nss):
+        h, unit = bgc.pods.hard_from_sheet_row(ns["cpu"], ns["memory"], ns["gpu"], ns["storage"], ns["mig"], keys)
+        hard[:, i] = h
+        hm[i] = (1 << R) - 1 if ns["has_quota"] else 0
+    engine.quota_table_set(hard, hm, unit)
+    r_ns, r_req, _, _ = bgc.pods.flatten_pods(c1_pods(10_000, nss, running=True), keys, m, intern=False)
+    used = engine.usage_reduce(r_ns, r_req)
+    assert np.array_equal(used, oracle.usage_reduce(r_ns, r_req, len(nss)))
+    pods = c1_pods(10_000, nss, running=False)
+    pods[5]["metadata"]["namespace"] = "ghost"
+    bodies = [json.dumps({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview",
+                          "request": {"uid": f"u{i}", "operation": "CREATE", "kind": {"kind": "Pod"}, "namespace": p["metadata"]["namespace"], "object": p}})
+              for i, p in enumerate(pods)]
+    bodies[100] = '{"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview", "request": {"uid": '      # truncated JSON
+    bodies[200] = json.dumps({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview", "request": {"uid": "u200", "operation": "DELETE"}})
+    outs = bgc.review.handle_pod_reviews(engine, bodies, keys, m, used, hard, wide=wide)
+    assert len(outs) == len(bodies)
+    keep = [i for i in range(len(pods)) if i not in (100, 200)]
+    c_ns, c_req, c_mask, _ = bgc.pods.flatten_pods([pods[i] for i in keep], keys, m, intern=False)
+    cm = sum(1 << r for r, u in enumerate(unit) if u)
+    want = (oracle.quota_eval16 if wide else oracle.quota_eval)(c_ns, c_req, c_mask, len(nss), used, hard, hm, cm)
+    kinds = set()
+    for k, i in enumerate(keep):
+        resp = json.loads(outs[i])["response"]
+        assert resp["uid"] == f"u{i}" and resp["allowed"] == (want[k] == 0), i
+        if want[k] != 0 and i != 5:
+            kinds.add(resp["status"]["message"].split(":")[0])
+    assert kinds == {"exceeded quota", "failed quota"}
+    assert "not known" in json.loads(outs[5])["response"]["status"]["message"]
+    for i in (100, 200):
+        resp = json.loads(outs[i])["response"]
+        assert resp["allowed"] is False and resp["status"]["reason"] == "InvalidRequest" and resp["uid"] == ""
+    assert 0.02 < float(np.mean(want != 0)) < 0.999

@@ -125,7 +125,11 @@ def test_pod_reviews_wire_to_wire_with_a_stand_in_engine(bgc, oracle):
         bodies = [json.dumps({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview",
                               "request": {"uid": f"u{i}", "operation": "CREATE", "kind": {"kind": "Pod"}, "namespace": p["metadata"]["namespace"], "object": p}})
                   for i, p in enumerate(pods)]
+        bodies.append("{")        # a malformed body costs only itself an answer (per-body parse failures)
         outs = bgc.review.handle_pod_reviews(StandIn(), bodies, keys, m, used, hard, wide=wide)
+        bad = json.loads(outs.pop())["response"]
+        assert bad["allowed"] is False and bad["status"]["reason"] == "InvalidRequest"
+        bodies.pop()
         c_ns, c_req, c_mask, _ = bgc.pods.flatten_pods(pods, keys, m, intern=False)
         verdict = StandIn().quota_eval(c_ns, c_req, c_mask, wide=wide)
         seen = set()
