@@ -9,11 +9,11 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/bgc.h"
 #include "../../include/bgc_synth.h"
-#include <cub/device/device_radix_sort.cuh>
 
 #include "bgc_kernels.cuh"
 
@@ -75,15 +75,25 @@ struct bgc_ctx {
   unsigned long long* d_scratch = nullptr;  // 256 x u64
   // greedy admission (row N1): grouping buffers, grown on demand
   uint32_t *g_keys = nullptr, *g_keys_sorted = nullptr, *g_idx = nullptr, *g_order = nullptr, *g_seg = nullptr;
-  void* g_temp = nullptr;
+  uint32_t* g_hist = nullptr;  // digit-major histogram of the grouping sort: 256 x tiles
   long long* g_req[kMaxR] = {};  // request columns in grouped order
   uint8_t* g_mask = nullptr;
   int g_R = 0;
-  size_t g_cap = 0, g_temp_bytes = 0, g_seg_cap = 0;
+  // device copies of a host batch for bgc_admit_greedy (host-pointer form), grown on demand
+  uint32_t* gh_ns = nullptr;
+  long long* gh_req[kMaxR] = {};
+  uint8_t *gh_mask = nullptr, *gh_v = nullptr;
+  size_t gh_cap = 0;
+  int gh_R = 0;
+  size_t g_cap = 0, g_hist_cap = 0, g_seg_cap = 0;
   // latency path: small host batches are read by the kernel straight over PCIe (zero-copy) from
   // the caller's pinned buffers, or from this pinned, device-mapped staging area
   uint8_t* zc_host = nullptr;
   uint8_t* zc_dev = nullptr;
+  // pinned bounce ring for PAGEABLE callers of the host-pointer entry points (two slots, grown on demand)
+  uint8_t* bounce[2] = {nullptr, nullptr};
+  size_t bounce_bytes = 0;
+  int bounce_threads = 0;
   // one-shard-of-a-global-stream generator (row E): per-tile counts and offsets of one chunk
   uint32_t* sh_tile_count = nullptr;
   unsigned long long* sh_tile_off = nullptr;  // [kShardChunkTiles] offsets + 1 total
@@ -521,6 +531,90 @@ int finish_timings(bgc_ctx* ctx, const Spans& sp) {
   return BGC_OK;
 }
 
+// ---- pageable callers ------------------------------------------------------------------------------
+// cudaMemcpyAsync from pageable memory is staged by the driver through its own small pinned buffer, on
+// the calling thread, at a fraction of the PCIe rate (round 1: the GPU never beat the host cores from
+// pageable memory).  A real caller at the mutate_handler seam (reference src/admission.rs:184-187) holds
+// serde-owned heap buffers, i.e. pageable ones.  For them a large host batch is cut into 4 Mi-pod pieces;
+// while the pinned pipeline works on piece j out of one pinned slot, a helper thread — itself fanning out
+// over a few cores — memcpys piece j+1 from the caller's memory into the other slot.
+struct BounceCol {
+  const void* src;
+  size_t width;
+};
+struct BounceOut {
+  void* dst;
+  size_t width;
+};
+constexpr size_t kBouncePods = size_t(4) << 20;
+constexpr int kBounceMaxCols = kMaxR + 3;
+
+bool is_pageable(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return true;
+  }
+  return a.type == cudaMemoryTypeUnregistered;
+}
+
+bool wants_bounce(const bgc_ctx* ctx, const void* first_column, size_t n) {
+  // below ~1 Mi pods the driver's own staging is as fast (measured, profiles/r02_crossover_c4.md)
+  return ctx->bounce_threads > 0 && n > ctx->zc_max_pods && n > kBouncePods / 4 && is_pageable(first_column);
+}
+
+template <class Call>
+int bounced(bgc_ctx* ctx, const BounceCol* cols, int ncols, const BounceOut* outs, int nouts, size_t n, Call&& call) {
+  size_t col_off[kBounceMaxCols], out_off[4], bytes = 0;
+  for (int c = 0; c < ncols; ++c) { col_off[c] = bytes; bytes += (kBouncePods * cols[c].width + 255) & ~size_t(255); }
+  for (int o = 0; o < nouts; ++o) { out_off[o] = bytes; bytes += (kBouncePods * outs[o].width + 255) & ~size_t(255); }
+  if (bytes > ctx->bounce_bytes) {
+    cudaFreeHost(ctx->bounce[0]); cudaFreeHost(ctx->bounce[1]);
+    ctx->bounce[0] = ctx->bounce[1] = nullptr;
+    ctx->bounce_bytes = 0;
+    CU(cudaHostAlloc(&ctx->bounce[0], bytes, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&ctx->bounce[1], bytes, cudaHostAllocDefault));
+    ctx->bounce_bytes = bytes;
+  }
+  const int T = ctx->bounce_threads;
+  auto fill = [&](int slot, size_t off, size_t m) {
+    // (column, slice) pairs over T threads: every thread streams a contiguous piece
+    const int pieces = ncols * T;
+#pragma omp parallel for num_threads(T) schedule(static)
+    for (int k = 0; k < pieces; ++k) {
+      const int c = k / T, part = k % T;
+      const size_t total = m * cols[c].width;
+      const size_t lo = total * part / T, hi = total * (part + 1) / T;
+      std::memcpy(ctx->bounce[slot] + col_off[c] + lo, static_cast<const char*>(cols[c].src) + off * cols[c].width + lo, hi - lo);
+    }
+  };
+  // fixed 4 Mi-pod pieces: smaller ones were measured slower (every piece pays a pipeline fill and the helper
+  // thread's start-up), so a batch up to 4 Mi pods is one parallel copy followed by one pinned call
+  const size_t piece = kBouncePods;
+  fill(0, 0, n < piece ? n : piece);
+  int rc = BGC_OK;
+  size_t j = 0;
+  for (size_t off = 0; off < n; off += piece, ++j) {
+    const size_t m = n - off < piece ? n - off : piece;
+    const int slot = (int)(j & 1);
+    std::thread next;
+    if (off + piece < n) {
+      const size_t off2 = off + piece, m2 = n - off2 < piece ? n - off2 : piece;
+      next = std::thread(fill, slot ^ 1, off2, m2);
+    }
+    const void* in[kBounceMaxCols];
+    void* out[4];
+    for (int c = 0; c < ncols; ++c) in[c] = ctx->bounce[slot] + col_off[c];
+    for (int o = 0; o < nouts; ++o) out[o] = ctx->bounce[slot] + out_off[o];
+    rc = call(in, out, m, j == 0);
+    if (rc == BGC_OK)
+      for (int o = 0; o < nouts; ++o) std::memcpy(static_cast<char*>(outs[o].dst) + off * outs[o].width, out[o], m * outs[o].width);
+    if (next.joinable()) next.join();
+    if (rc) break;
+  }
+  return rc;
+}
+
 }  // namespace
 
 // =============================================================================== C ABI
@@ -557,6 +651,11 @@ int bgc_ctx_create(int device, bgc_ctx** out) {
   ctx->stream = ctx->own_stream;
   if (const char* v = std::getenv("BGC_K1_PREFETCH")) ctx->k1_prefetch = std::atoi(v);
   if (const char* v = std::getenv("BGC_K2_PREFETCH")) ctx->k2_prefetch = std::atoi(v);
+  {
+    const unsigned hw = std::thread::hardware_concurrency();
+    ctx->bounce_threads = hw >= 16 ? 8 : hw >= 4 ? (int)hw / 2 : 1;
+    if (const char* v = std::getenv("BGC_BOUNCE_THREADS")) ctx->bounce_threads = std::atoi(v) > 0 ? std::atoi(v) : 0;  // 0 disables the bounce pipeline
+  }
   if (const char* v = std::getenv("BGC_ZEROCOPY_MAX_PODS")) {
     const long long want = std::atoll(v);
     ctx->zc_max_pods = want < 0 ? 0 : ((size_t)want > kZeroCopyMaxPods ? kZeroCopyMaxPods : (size_t)want);
@@ -582,9 +681,12 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   cudaFree(ctx->d_hard_mask);
   cudaFree(ctx->d_scratch);
   cudaFree(ctx->sh_tile_count); cudaFree(ctx->sh_tile_off);
+  cudaFreeHost(ctx->bounce[0]); cudaFreeHost(ctx->bounce[1]);
   cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order);
-  cudaFree(ctx->g_seg); cudaFree(ctx->g_temp); cudaFree(ctx->g_mask);
+  cudaFree(ctx->g_seg); cudaFree(ctx->g_hist); cudaFree(ctx->g_mask);
   for (auto q : ctx->g_req) cudaFree(q);
+  cudaFree(ctx->gh_ns); cudaFree(ctx->gh_mask); cudaFree(ctx->gh_v);
+  for (auto q : ctx->gh_req) cudaFree(q);
   cudaFreeHost(ctx->zc_host);
   cudaStreamDestroy(ctx->own_stream);
   cudaStreamDestroy(ctx->h2d_stream);
@@ -651,6 +753,14 @@ int bgc_policy_eval(bgc_ctx* ctx, const uint8_t* op, const uint16_t* flags, size
   ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   if (n == 0) return BGC_OK;
+  if (wants_bounce(ctx, op, n)) {  // pageable caller: pinned bounce ring, copies overlapped with the pipeline
+    const BounceCol cols[2] = {{op, 1}, {flags, 2}};
+    const BounceOut outs[2] = {{code, 1}, {patch_mask, 1}};
+    return bounced(ctx, cols, 2, outs, 2, n, [&](const void* const* in, void* const* out, size_t m, bool) {
+      return bgc_policy_eval(ctx, static_cast<const uint8_t*>(in[0]), static_cast<const uint16_t*>(in[1]), m,
+                             static_cast<uint8_t*>(out[0]), static_cast<uint8_t*>(out[1]));
+    });
+  }
   if (n <= ctx->zc_max_pods) {  // latency path: one launch, no staged copies
     ZcCursor cur;
     uint8_t *b0, *b1;
@@ -836,6 +946,18 @@ int bgc_usage_reduce(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
   ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   int rc;
+  if (wants_bounce(ctx, ns_id, n)) {  // pageable caller: pinned bounce ring; pieces after the first accumulate
+    BounceCol cols[kBounceMaxCols];
+    cols[0] = {ns_id, 4};
+    for (int r = 0; r < R; ++r) cols[1 + r] = {req[r], 8};
+    rc = bounced(ctx, cols, 1 + R, nullptr, 0, n, [&](const void* const* in, void* const*, size_t m, bool first) {
+      const int64_t* rq[kMaxR];
+      for (int r = 0; r < R; ++r) rq[r] = static_cast<const int64_t*>(in[1 + r]);
+      return bgc_usage_reduce(ctx, static_cast<const uint32_t*>(in[0]), rq, m, first ? flags : (flags | BGC_REDUCE_ACCUMULATE), nullptr);
+    });
+    if (rc) return rc;
+    return used_out ? bgc_usage_get(ctx, used_out) : BGC_OK;
+  }
   if (!(flags & BGC_REDUCE_ACCUMULATE) && (rc = clear_used(ctx, ctx->own_stream))) return rc;
   // The columns are in host memory here, so the grouping hint can be inferred for free: 1,024
   // evenly spaced neighbour pairs; if nearly all of them share a namespace the segmented kernel is
@@ -923,6 +1045,20 @@ int quota_eval_host_impl(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* con
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   if (n == 0) return BGC_OK;
   int rc;
+  if (wants_bounce(ctx, ns_id, n)) {  // pageable caller: pinned bounce ring
+    BounceCol cols[kBounceMaxCols];
+    int nc = 0;
+    cols[nc++] = {ns_id, 4};
+    for (int r = 0; r < R; ++r) cols[nc++] = {req[r], 8};
+    if (req_mask) cols[nc++] = {req_mask, 1};
+    const BounceOut outs[1] = {{verdict, sizeof(VT)}};
+    return bounced(ctx, cols, nc, outs, 1, n, [&](const void* const* in, void* const* out, size_t m, bool) {
+      const int64_t* rq[kMaxR];
+      for (int r = 0; r < R; ++r) rq[r] = static_cast<const int64_t*>(in[1 + r]);
+      return quota_eval_host_impl<VT>(ctx, static_cast<const uint32_t*>(in[0]), rq,
+                                      req_mask ? static_cast<const uint8_t*>(in[1 + R]) : nullptr, m, static_cast<VT*>(out[0]));
+    });
+  }
   if (n <= ctx->zc_max_pods) {  // latency path: one launch, the kernel reads/writes host memory itself
     ZcCursor cur;
     uint8_t* bounce;
@@ -1050,7 +1186,7 @@ int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const long long* const* req_in, c
   return BGC_OK;
 }
 
-int ensure_greedy_buffers(bgc_ctx* ctx, size_t n, int end_bit) {
+int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
   if (n > ctx->g_cap || ctx->R > ctx->g_R) {
     CU(cudaDeviceSynchronize());
     cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order); cudaFree(ctx->g_mask);
@@ -1075,14 +1211,13 @@ int ensure_greedy_buffers(bgc_ctx* ctx, size_t n, int end_bit) {
     CU(cudaMalloc(&ctx->g_seg, ((size_t)ctx->NS + 2) * 4));
     ctx->g_seg_cap = (size_t)ctx->NS + 2;
   }
-  size_t need = 0;
-  CU(cub::DeviceRadixSort::SortPairs(nullptr, need, ctx->g_keys, ctx->g_keys_sorted, ctx->g_idx, ctx->g_order,
-                                     (long long)n, 0, end_bit));
-  if (need > ctx->g_temp_bytes) {
+  size_t hist_need = (size_t)256 * ((n + kSortTile - 1) / kSortTile);
+  hist_need += (hist_need + kScanBlock - 1) / kScanBlock + 1;  // + the block totals of the scan
+  if (hist_need > ctx->g_hist_cap) {
     CU(cudaDeviceSynchronize());
-    cudaFree(ctx->g_temp); ctx->g_temp = nullptr; ctx->g_temp_bytes = 0;
-    CU(cudaMalloc(&ctx->g_temp, need));
-    ctx->g_temp_bytes = need;
+    cudaFree(ctx->g_hist); ctx->g_hist = nullptr; ctx->g_hist_cap = 0;
+    CU(cudaMalloc(&ctx->g_hist, hist_need * 4));
+    ctx->g_hist_cap = hist_need;
   }
   return BGC_OK;
 }
@@ -1105,16 +1240,38 @@ extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const
   CU(cudaSetDevice(ctx->device));
   int end_bit = 1;
   while ((1ull << end_bit) <= (unsigned long long)ctx->NS) ++end_bit;  // keys are 0..NS
-  int rc = ensure_greedy_buffers(ctx, n, end_bit);
+  int rc = ensure_greedy_buffers(ctx, n);
   if (rc) return rc;
   cudaStream_t st = ctx->stream;
-  const int g1 = grid_for(n, 256, ctx->sm_count * 8);
-  k_greedy_keys<<<g1, 256, 0, st>>>(d_ns_id, n, ctx->NS, ctx->g_keys, ctx->g_idx);
-  ctx->tm.launches++;
-  CU(cudaGetLastError());
-  size_t tb = ctx->g_temp_bytes;
-  CU(cub::DeviceRadixSort::SortPairs(ctx->g_temp, tb, ctx->g_keys, ctx->g_keys_sorted, ctx->g_idx, ctx->g_order,
-                                     (long long)n, 0, end_bit, st));  // stable: arrival order kept inside a namespace
+  {
+    // stable grouping by namespace: LSD radix passes of 8 bits over the end_bit significant key bits; buffers
+    // ping-pong so that the last pass lands in (g_keys_sorted, g_order)
+    const int passes = (end_bit + 7) / 8;
+    const uint32_t ntile = (uint32_t)((n + kSortTile - 1) / kSortTile);
+    const int grid = (int)(ntile < (uint32_t)ctx->sm_count * 8 ? ntile : (uint32_t)ctx->sm_count * 8);
+    const uint32_t *kin = nullptr, *iin = nullptr;
+    CU(cudaFuncSetAttribute(k_rsort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 8));
+    for (int p = 0; p < passes; ++p) {
+      const bool to_final = ((passes - 1 - p) % 2) == 0;
+      uint32_t* kout = to_final ? ctx->g_keys_sorted : ctx->g_keys;
+      uint32_t* iout = to_final ? ctx->g_order : ctx->g_idx;
+      k_rsort_hist<<<grid, kSortThreads, 0, st>>>(kin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile);
+      {
+        const size_t cnt = (size_t)256 * ntile;
+        const unsigned blocks = (unsigned)((cnt + kScanBlock - 1) / kScanBlock);
+        uint32_t* totals = ctx->g_hist + cnt;  // room reserved behind the histogram
+        k_scan_blocks<<<blocks, 1024, 0, st>>>(ctx->g_hist, cnt, totals);
+        k_scan_u32<<<1, 1024, 0, st>>>(totals, blocks);
+        k_scan_add<<<blocks, 1024, 0, st>>>(ctx->g_hist, cnt, totals);
+        ctx->tm.launches += 2;
+      }
+      k_rsort_scatter<<<grid, kSortThreads, (size_t)kSortTile * 8, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout);
+      ctx->tm.launches += 3;
+      CU(cudaGetLastError());
+      kin = kout;
+      iin = iout;
+    }
+  }
   const int g2 = grid_for((size_t)ctx->NS + 2, 256, ctx->sm_count * 4);
   k_greedy_segments<<<g2, 256, 0, st>>>(ctx->g_keys_sorted, n, ctx->NS, ctx->g_seg);
   ctx->tm.launches++;
@@ -1141,40 +1298,43 @@ extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64
   if (n == 0) return BGC_OK;
   CU(cudaSetDevice(ctx->device));
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
-  // the whole batch must be resident for the grouping pass: one-shot buffers, released on return
-  uint32_t* d_ns = nullptr;
-  long long* d_req[kMaxR] = {};
-  uint8_t *d_mask = nullptr, *d_v = nullptr;
-  auto cleanup = [&] {
-    cudaFree(d_ns); cudaFree(d_mask); cudaFree(d_v);
-    for (auto p : d_req) cudaFree(p);
-  };
+  // the whole batch must be resident for the grouping pass: device copies owned by the context, grown on
+  // demand and kept (a call with a batch no larger than an earlier one allocates nothing)
+  if (n > ctx->gh_cap || R > ctx->gh_R) {
+    CU(cudaDeviceSynchronize());
+    cudaFree(ctx->gh_ns); cudaFree(ctx->gh_mask); cudaFree(ctx->gh_v);
+    for (auto& q : ctx->gh_req) { cudaFree(q); q = nullptr; }
+    ctx->gh_ns = nullptr; ctx->gh_mask = ctx->gh_v = nullptr;
+    const size_t cap = n > ctx->gh_cap ? n : ctx->gh_cap;
+    const int RR = R > ctx->gh_R ? R : ctx->gh_R;
+    ctx->gh_cap = 0; ctx->gh_R = 0;
+    CU(cudaMalloc(&ctx->gh_ns, cap * 4));
+    for (int r = 0; r < RR; ++r) CU(cudaMalloc(&ctx->gh_req[r], cap * 8));
+    CU(cudaMalloc(&ctx->gh_mask, cap));
+    CU(cudaMalloc(&ctx->gh_v, cap));
+    ctx->gh_cap = cap; ctx->gh_R = RR;
+  }
   cudaStream_t keep = ctx->stream;
   ctx->stream = ctx->own_stream;
   int rc = BGC_OK;
-  cudaError_t e = cudaMalloc(&d_ns, n * 4);
-  for (int r = 0; r < R && e == cudaSuccess; ++r) e = cudaMalloc(&d_req[r], n * 8);
-  if (e == cudaSuccess && req_mask) e = cudaMalloc(&d_mask, n);
-  if (e == cudaSuccess) e = cudaMalloc(&d_v, n);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(d_ns, ns_id, n * 4, cudaMemcpyHostToDevice, ctx->own_stream);
+  cudaError_t e = cudaMemcpyAsync(ctx->gh_ns, ns_id, n * 4, cudaMemcpyHostToDevice, ctx->own_stream);
   for (int r = 0; r < R && e == cudaSuccess; ++r)
-    e = cudaMemcpyAsync(d_req[r], req[r], n * 8, cudaMemcpyHostToDevice, ctx->own_stream);
-  if (e == cudaSuccess && req_mask) e = cudaMemcpyAsync(d_mask, req_mask, n, cudaMemcpyHostToDevice, ctx->own_stream);
+    e = cudaMemcpyAsync(ctx->gh_req[r], req[r], n * 8, cudaMemcpyHostToDevice, ctx->own_stream);
+  if (e == cudaSuccess && req_mask) e = cudaMemcpyAsync(ctx->gh_mask, req_mask, n, cudaMemcpyHostToDevice, ctx->own_stream);
   if (e != cudaSuccess) {
-    rc = fail(ctx, e == cudaErrorMemoryAllocation ? BGC_E_OOM : BGC_E_CUDA, "greedy staging: %s", cudaGetErrorString(e));
+    rc = fail(ctx, BGC_E_CUDA, "greedy staging: %s", cudaGetErrorString(e));
   } else {
     const int64_t* cols[kMaxR];
-    for (int r = 0; r < kMaxR; ++r) cols[r] = reinterpret_cast<const int64_t*>(d_req[r]);
-    rc = bgc_admit_greedy_dev(ctx, d_ns, cols, d_mask, n, d_v);
+    for (int r = 0; r < kMaxR; ++r) cols[r] = reinterpret_cast<const int64_t*>(ctx->gh_req[r]);
+    rc = bgc_admit_greedy_dev(ctx, ctx->gh_ns, cols, req_mask ? ctx->gh_mask : nullptr, n, ctx->gh_v);
     if (rc == BGC_OK) {
-      e = cudaMemcpyAsync(verdict, d_v, n, cudaMemcpyDeviceToHost, ctx->own_stream);
+      e = cudaMemcpyAsync(verdict, ctx->gh_v, n, cudaMemcpyDeviceToHost, ctx->own_stream);
       if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->own_stream);
       if (e != cudaSuccess) rc = fail(ctx, BGC_E_CUDA, "greedy copy-out: %s", cudaGetErrorString(e));
     }
   }
   cudaStreamSynchronize(ctx->own_stream);
   ctx->stream = keep;
-  cleanup();
   return rc;
 }
 

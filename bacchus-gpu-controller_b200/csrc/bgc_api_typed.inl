@@ -223,6 +223,18 @@ int bgc_usage_reduce_typed(bgc_ctx* ctx, const void* ns_id, int ns_type, const b
   CU(cudaSetDevice(ctx->device));
   ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
+  if (wants_bounce(ctx, ns_id, n)) {  // pageable caller: pinned bounce ring; pieces after the first accumulate
+    BounceCol cols[kBounceMaxCols];
+    cols[0] = {ns_id, type_width(a.ns_type)};
+    for (int r = 0; r < ctx->R; ++r) cols[1 + r] = {req[r].data, type_width(req[r].type)};
+    rc = bounced(ctx, cols, 1 + ctx->R, nullptr, 0, n, [&](const void* const* in, void* const*, size_t m, bool first) {
+      bgc_col c2[kMaxR];
+      for (int r = 0; r < ctx->R; ++r) { c2[r] = req[r]; c2[r].data = in[1 + r]; }
+      return bgc_usage_reduce_typed(ctx, in[0], ns_type, c2, m, first ? flags : (flags | BGC_REDUCE_ACCUMULATE), nullptr);
+    });
+    if (rc) return rc;
+    return used_out ? bgc_usage_get(ctx, used_out) : BGC_OK;
+  }
   if (!(flags & BGC_REDUCE_ACCUMULATE) && (rc = clear_used(ctx, ctx->own_stream))) return rc;
   if (n && (rc = typed_host_pipeline(ctx, a, nullptr, n, nullptr))) return rc;
   if (used_out) {
@@ -244,6 +256,20 @@ int bgc_quota_eval_typed(bgc_ctx* ctx, const void* ns_id, int ns_type, const bgc
   ctx->tm.h2d_ns = ctx->tm.kernel_ns = ctx->tm.d2h_ns = 0;
   if (ctx->stream != ctx->own_stream) CU(cudaStreamSynchronize(ctx->stream));
   if (n == 0) return BGC_OK;
+  if (wants_bounce(ctx, ns_id, n)) {  // pageable caller: pinned bounce ring
+    BounceCol cols[kBounceMaxCols];
+    int nc = 0;
+    cols[nc++] = {ns_id, type_width(a.ns_type)};
+    for (int r = 0; r < ctx->R; ++r) cols[nc++] = {req[r].data, type_width(req[r].type)};
+    if (req_mask) cols[nc++] = {req_mask, 1};
+    const BounceOut outs[1] = {{verdict, 1}};
+    return bounced(ctx, cols, nc, outs, 1, n, [&](const void* const* in, void* const* out, size_t m, bool) {
+      bgc_col c2[kMaxR];
+      for (int r = 0; r < ctx->R; ++r) { c2[r] = req[r]; c2[r].data = in[1 + r]; }
+      return bgc_quota_eval_typed(ctx, in[0], ns_type, c2, req_mask ? static_cast<const uint8_t*>(in[1 + ctx->R]) : nullptr, m,
+                                  static_cast<uint8_t*>(out[0]));
+    });
+  }
   return typed_host_pipeline(ctx, a, req_mask, n, verdict);
 }
 

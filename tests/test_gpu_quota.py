@@ -409,3 +409,27 @@ def test_k2_shared_memory_table_variant(bgc, engine, oracle, R, with_mask, NS, m
     engine.quota_eval_dev(dev(cns), [dev(c) for c in creq], dev(mask) if with_mask else None, d_v)
     torch.cuda.synchronize()
     assert np.array_equal(d_v.cpu().numpy(), want)
+
+
+def test_pageable_host_batches_take_the_bounce_pipeline(engine, oracle):
+    """Host batches in ordinary (pageable) numpy memory larger than one 4 Mi-pod piece go through the pinned
+    bounce ring (helper thread copying piece j+1 while piece j is in the pipeline): K0, K1 (pieces after the
+    first accumulate) and K2 (with and without masks) must still equal the oracle, ragged tail included."""
+    rng = np.random.default_rng(99)
+    n, NS, R = (4 << 20) * 2 + 54_321, 9_000, 3
+    ns = rng.integers(0, NS + 2, n, dtype=np.uint32)
+    req = [rng.integers(0, 1 << 33, n, dtype=np.int64) for _ in range(R)]
+    mask = rng.integers(0, 256, n, dtype=np.uint8)
+    engine.quota_table_set(np.full((R, NS), 1 << 50, np.int64), np.full(NS, 7, np.uint8), UNITS[R])
+    want_used = oracle.usage_reduce(ns, req, NS, threads=8)
+    assert np.array_equal(engine.usage_reduce(ns, req), want_used)
+    hard = want_used + rng.integers(-(1 << 33), 1 << 33, want_used.shape)
+    hm = np.full(NS, 7, np.uint8)
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(want_used)
+    for mk in (None, mask):
+        assert np.array_equal(engine.quota_eval(ns, req, mk), oracle.quota_eval(ns, req, mk, NS, want_used, hard, hm, _compute_mask(UNITS[R]), threads=8))
+    op, fl = oracle.gen_policy_fill(5, 0, n, threads=8)
+    code, pm = engine.policy_eval(op, fl)
+    rc, rp = oracle.policy_bits(op, fl, threads=8)
+    assert np.array_equal(code, rc) and np.array_equal(pm, rp)
