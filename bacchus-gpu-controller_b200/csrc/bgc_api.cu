@@ -76,8 +76,9 @@ struct bgc_ctx {
   // greedy admission (row N1): grouping buffers, grown on demand
   uint32_t *g_keys = nullptr, *g_keys_sorted = nullptr, *g_idx = nullptr, *g_order = nullptr, *g_seg = nullptr;
   uint32_t* g_hist = nullptr;  // digit-major histogram of the grouping sort: 256 x tiles
-  long long* g_req[kMaxR] = {};  // request columns in grouped order
-  uint8_t* g_mask = nullptr;
+  long long* g_req[kMaxR] = {};  // request columns in grouped order (the sort's last pass writes them)
+  long long* g_req2[kMaxR] = {}; // ... and their ping-pong partners for the passes in between
+  uint8_t *g_mask = nullptr, *g_mask2 = nullptr;
   int g_R = 0;
   // device copies of a host batch for bgc_admit_greedy (host-pointer form), grown on demand
   uint32_t* gh_ns = nullptr;
@@ -683,8 +684,9 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   cudaFree(ctx->sh_tile_count); cudaFree(ctx->sh_tile_off);
   cudaFreeHost(ctx->bounce[0]); cudaFreeHost(ctx->bounce[1]);
   cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order);
-  cudaFree(ctx->g_seg); cudaFree(ctx->g_hist); cudaFree(ctx->g_mask);
+  cudaFree(ctx->g_seg); cudaFree(ctx->g_hist); cudaFree(ctx->g_mask); cudaFree(ctx->g_mask2);
   for (auto q : ctx->g_req) cudaFree(q);
+  for (auto q : ctx->g_req2) cudaFree(q);
   cudaFree(ctx->gh_ns); cudaFree(ctx->gh_mask); cudaFree(ctx->gh_v);
   for (auto q : ctx->gh_req) cudaFree(q);
   cudaFreeHost(ctx->zc_host);
@@ -1147,19 +1149,11 @@ namespace {
 template <int R>
 int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const long long* const* req_in, const uint8_t* mask_in, size_t n,
                 uint8_t* verdict) {
-  // permute the request columns into grouped order once, in parallel
-  ReqCols<R> src, cols;
-  ReqColsOut<R> dst;
-  for (int r = 0; r < R; ++r) {
-    src.p[r] = req_in[r];
-    dst.p[r] = ctx->g_req[r];
-    cols.p[r] = ctx->g_req[r];
-  }
-  const int gg = grid_for(n, 256, ctx->sm_count * 16);
-  if (mask_in) k_greedy_gather<R, true><<<gg, 256, 0, st>>>(ctx->g_order, src, mask_in, n, dst, ctx->g_mask);
-  else k_greedy_gather<R, false><<<gg, 256, 0, st>>>(ctx->g_order, src, mask_in, n, dst, ctx->g_mask);
-  ctx->tm.launches++;
-  CU(cudaGetLastError());
+  // the grouping sort already left the request columns (and masks) in grouped order in the context's buffers
+  ReqCols<R> cols;
+  for (int r = 0; r < R; ++r) cols.p[r] = ctx->g_req[r];
+  (void)req_in;
+  (void)n;
   const uint8_t* mask = mask_in ? ctx->g_mask : nullptr;
   int grid = ctx->sm_count * 8;
   const int warps_per_block = 256 / 32;
@@ -1189,8 +1183,10 @@ int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const long long* const* req_in, c
 int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
   if (n > ctx->g_cap || ctx->R > ctx->g_R) {
     CU(cudaDeviceSynchronize());
-    cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order); cudaFree(ctx->g_mask);
+    cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order); cudaFree(ctx->g_mask); cudaFree(ctx->g_mask2);
     for (auto& q : ctx->g_req) { cudaFree(q); q = nullptr; }
+    for (auto& q : ctx->g_req2) { cudaFree(q); q = nullptr; }
+    ctx->g_mask2 = nullptr;
     ctx->g_keys = ctx->g_keys_sorted = ctx->g_idx = ctx->g_order = nullptr;
     ctx->g_mask = nullptr;
     if (n < ctx->g_cap) n = ctx->g_cap;
@@ -1201,7 +1197,9 @@ int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
     CU(cudaMalloc(&ctx->g_idx, n * 4));
     CU(cudaMalloc(&ctx->g_order, n * 4));
     CU(cudaMalloc(&ctx->g_mask, n));
+    CU(cudaMalloc(&ctx->g_mask2, n));
     for (int r = 0; r < ctx->R; ++r) CU(cudaMalloc(&ctx->g_req[r], n * 8));
+    for (int r = 0; r < ctx->R; ++r) CU(cudaMalloc(&ctx->g_req2[r], n * 8));
     ctx->g_cap = n;
     ctx->g_R = ctx->R;
   }
@@ -1250,7 +1248,7 @@ extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const
     const uint32_t ntile = (uint32_t)((n + kSortTile - 1) / kSortTile);
     const int grid = (int)(ntile < (uint32_t)ctx->sm_count * 8 ? ntile : (uint32_t)ctx->sm_count * 8);
     const uint32_t *kin = nullptr, *iin = nullptr;
-    CU(cudaFuncSetAttribute(k_rsort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 8));
+    CU(cudaFuncSetAttribute(k_rsort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 10));
     for (int p = 0; p < passes; ++p) {
       const bool to_final = ((passes - 1 - p) % 2) == 0;
       uint32_t* kout = to_final ? ctx->g_keys_sorted : ctx->g_keys;
@@ -1265,7 +1263,17 @@ extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const
         k_scan_add<<<blocks, 1024, 0, st>>>(ctx->g_hist, cnt, totals);
         ctx->tm.launches += 2;
       }
-      k_rsort_scatter<<<grid, kSortThreads, (size_t)kSortTile * 8, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout);
+      SortPayload P{};
+      P.R = ctx->R;
+      for (int r = 0; r < ctx->R; ++r) {
+        P.in[r] = p == 0 ? cols[r] : (to_final ? ctx->g_req2[r] : ctx->g_req[r]);   // the previous pass wrote the other set
+        P.out[r] = to_final ? ctx->g_req[r] : ctx->g_req2[r];
+      }
+      if (d_req_mask) {
+        P.mask_in = p == 0 ? d_req_mask : (to_final ? ctx->g_mask2 : ctx->g_mask);
+        P.mask_out = to_final ? ctx->g_mask : ctx->g_mask2;
+      }
+      k_rsort_scatter<<<grid, kSortThreads, (size_t)kSortTile * 10, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
       ctx->tm.launches += 3;
       CU(cudaGetLastError());
       kin = kout;

@@ -121,6 +121,18 @@ static __global__ void __launch_bounds__(1024) k_scan_add(uint32_t* a, size_t co
     if (base + k < count) a[base + k] += add;
 }
 
+// The request columns (and masks) travel with the pairs through every pass, so that the last pass leaves
+// them in grouped order for the walkers: a separate gather by the final permutation reads one 32-byte
+// sector per 8-byte value from all over a multi-GB array (6.7 ms per 10^8 pods, measured), whereas here
+// every read stays inside the tile's own 64 KB window of a column (L2 hits) and every write is a run.
+struct SortPayload {
+  const long long* in[kMaxR];
+  long long* out[kMaxR];
+  const uint8_t* mask_in;
+  uint8_t* mask_out;
+  int R;
+};
+
 // One tile per trip: the tile is sorted by digit INSIDE shared memory first (in-order ranks as described
 // above), then written out — every digit's elements of the tile are consecutive in shared memory and go to
 // consecutive global positions, so the writes are whole 32-byte sectors instead of one 4-byte element per
@@ -129,10 +141,11 @@ static __global__ void __launch_bounds__(1024) k_scan_add(uint32_t* a, size_t co
 static __global__ void __launch_bounds__(kSortThreads)
 k_rsort_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ ns_id,
                 uint32_t NS, size_t n, int shift, const uint32_t* __restrict__ offs, uint32_t ntile,
-                uint32_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out) {
+                uint32_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out, SortPayload P) {
   extern __shared__ __align__(16) uint32_t rs_smem[];
   uint32_t* s_key = rs_smem;                    // [kSortTile] the tile, grouped by digit
   uint32_t* s_idx = rs_smem + kSortTile;        // [kSortTile]
+  unsigned short* s_src = reinterpret_cast<unsigned short*>(rs_smem + 2 * kSortTile);  // [kSortTile] where in the tile it came from
   __shared__ uint32_t s_warp[kSortThreads / 32][256];  // per-warp digit counts of the current round, then bases
   __shared__ uint32_t s_run[256];                      // cursor of each digit inside the tile
   __shared__ uint32_t s_lbase[256];                    // first tile position of each digit
@@ -192,6 +205,7 @@ k_rsort_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
         const uint32_t pos = s_warp[warp][digit] + rank;
         s_key[pos] = key;
         s_idx[pos] = idx_in ? idx_in[i] : (uint32_t)i;
+        s_src[pos] = (unsigned short)(r * kSortThreads + threadIdx.x);
       }
       __syncthreads();
     }
@@ -201,6 +215,9 @@ k_rsort_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
       const uint32_t gpos = s_goff[d] + (j - s_lbase[d]);
       keys_out[gpos] = key;
       idx_out[gpos] = s_idx[j];
+      const size_t src = base + s_src[j];
+      for (int q = 0; q < P.R; ++q) P.out[q][gpos] = P.in[q][src];
+      if (P.mask_in) P.mask_out[gpos] = P.mask_in[src];
     }
     __syncthreads();
   }
@@ -225,41 +242,6 @@ static __global__ void k_greedy_bad_ns(const uint32_t* __restrict__ order, const
   const size_t beg = seg[NS], end = seg[NS + 1];
   for (size_t i = beg + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += (size_t)gridDim.x * blockDim.x)
     verdict[order[i]] = 0xFFu;
-}
-
-// requests permuted into grouped order, so the sequential walkers below stream contiguous memory
-template <int R, bool HAS_MASK>
-static __global__ void __launch_bounds__(256)
-k_greedy_gather(const uint32_t* __restrict__ order, ReqCols<R> req, const uint8_t* __restrict__ req_mask, size_t n,
-                ReqColsOut<R> out, uint8_t* __restrict__ mask_out) {
-  // four pods per thread, all 4R random loads issued before the first store: the gather is latency-bound
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  for (; i + 3 * stride < n; i += 4 * stride) {
-    uint32_t idx[4];
-    long long v[R][4];
-    uint8_t m[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) idx[k] = order[i + k * stride];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) v[r][k] = req.p[r][idx[k]];
-      if (HAS_MASK) m[k] = req_mask[idx[k]];
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) out.p[r][i + k * stride] = v[r][k];
-      if (HAS_MASK) mask_out[i + k * stride] = m[k];
-    }
-  }
-  for (; i < n; i += stride) {
-    const uint32_t idx = order[i];
-#pragma unroll
-    for (int r = 0; r < R; ++r) out.p[r][i] = req.p[r][idx];
-    if (HAS_MASK) mask_out[i] = req_mask[idx];
-  }
 }
 
 template <int R>
