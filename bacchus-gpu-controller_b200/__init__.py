@@ -49,7 +49,7 @@ EXPORTS = [
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
     "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
     "bgc_nsmap_intern", "bgc_nsmap_lookup", "bgc_nsmap_size", "bgc_nsmap_name", "bgc_flatten_pods",
-    "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev", "bgc_admit_greedy", "bgc_admit_greedy_dev",
+    "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev", "bgc_admit_greedy", "bgc_admit_greedy_dev", "bgc_admit_greedy16", "bgc_admit_greedy16_dev",
     "bgc_sheet_infer_header", "bgc_sheet_parse_csv", "bgc_sheet_destroy", "bgc_sheet_row_count", "bgc_sheet_skipped_rows",
     "bgc_sheet_get_row", "bgc_sheet_match", "bgc_sheet_row_quota",
     "bgc_review_parse", "bgc_review_destroy", "bgc_review_has_request", "bgc_review_uid", "bgc_review_kind",
@@ -98,6 +98,8 @@ lib.bgc_quota_eval16.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_quota_eval16_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_admit_greedy.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_admit_greedy_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_admit_greedy16.argtypes = [_P, _P, _P, _P, _Z, _P]
+lib.bgc_admit_greedy16_dev.argtypes = [_P, _P, _P, _P, _Z, _P]
 lib.bgc_synth_pods_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64, _Z, _P, _P, _P]
 lib.bgc_synth_pods_shard_dev.argtypes = [_P, C.POINTER(SynthParams), C.c_uint64, _Z, C.c_uint32, C.c_uint32, _P, C.c_uint64, _Z,
                                          _P, _P, _P, _P, C.POINTER(C.c_uint64)]
@@ -343,7 +345,7 @@ class Engine:
         self._ck(lib.bgc_quota_eval_typed(self._h, C.c_void_p(ns_ptr), ns_type, cols, C.c_void_p(mask_ptr), n, C.c_void_p(verdict_ptr)))
 
     # -- K3 (row N1): sequential admission inside the batch; updates the usage table
-    def admit_greedy(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None) -> np.ndarray:
+    def admit_greedy(self, ns_id: np.ndarray, req: list, req_mask: np.ndarray | None = None, wide: bool = False) -> np.ndarray:
         n = ns_id.shape[0]
         _check_np(ns_id, np.uint32, name="ns_id")
         for r, c in enumerate(req):
@@ -353,14 +355,15 @@ class Engine:
         if len(req) != self.R:
             raise ValueError(f"expected {self.R} request columns")
         ptrs = (C.c_void_p * len(req))(*[c.ctypes.data for c in req])
-        verdict = np.empty(n, np.uint8)
-        self._ck(lib.bgc_admit_greedy(self._h, _np_ptr(ns_id), ptrs, _np_ptr(req_mask), n, _np_ptr(verdict)))
+        verdict = np.empty(n, np.uint16 if wide else np.uint8)      # wide: u16 verdicts, any R <= 8
+        fn = lib.bgc_admit_greedy16 if wide else lib.bgc_admit_greedy
+        self._ck(fn(self._h, _np_ptr(ns_id), ptrs, _np_ptr(req_mask), n, _np_ptr(verdict)))
         return verdict
 
     def admit_greedy_dev(self, d_ns_id, d_req: list, d_req_mask, d_verdict, n: int | None = None):
         ptrs = (C.c_void_p * len(d_req))(*[t.data_ptr() for t in d_req])
-        self._ck(lib.bgc_admit_greedy_dev(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask),
-                                          d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
+        fn = lib.bgc_admit_greedy16_dev if d_verdict.element_size() == 2 else lib.bgc_admit_greedy_dev
+        self._ck(fn(self._h, _dev_ptr(d_ns_id), ptrs, _dev_ptr(d_req_mask), d_ns_id.numel() if n is None else n, _dev_ptr(d_verdict)))
 
     # -- raw-pointer variants (host pinned buffers, slices of larger allocations)
     def usage_reduce_ptr(self, ns_ptr: int, req_ptrs: list, n: int, flags: int = 0, used_out_ptr: int = 0):

@@ -1146,14 +1146,11 @@ int bgc_quota_eval16(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
 // ---------------------------------------------------------------- K3 (row N1): greedy in-batch admission
 namespace {
 
-template <int R>
-int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const long long* const* req_in, const uint8_t* mask_in, size_t n,
-                uint8_t* verdict) {
+template <int R, typename VT>
+int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const uint8_t* mask_in, VT* verdict) {
   // the grouping sort already left the request columns (and masks) in grouped order in the context's buffers
   ReqCols<R> cols;
   for (int r = 0; r < R; ++r) cols.p[r] = ctx->g_req[r];
-  (void)req_in;
-  (void)n;
   const uint8_t* mask = mask_in ? ctx->g_mask : nullptr;
   int grid = ctx->sm_count * 8;
   const int warps_per_block = 256 / 32;
@@ -1161,23 +1158,19 @@ int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const long long* const* req_in, c
   // short segments: one warp per namespace; long ones (Zipf heads): one 1024-thread CTA per namespace
   int team_grid = ctx->sm_count;
   if ((uint32_t)team_grid > ctx->NS) team_grid = (int)ctx->NS;
-  const size_t ring = (size_t)kGreedyDepth * R * kGreedyTeam * 8;
-  if (mask) {
-    CU(cudaFuncSetAttribute(k3_admit_greedy_team<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
-    k3_admit_greedy<R, true><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
-                                                   ctx->NS, ctx->compute_mask, verdict, kGreedyTeamMin);
-    k3_admit_greedy_team<R, true><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard,
-                                                                       ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
-  } else {
-    CU(cudaFuncSetAttribute(k3_admit_greedy_team<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
-    k3_admit_greedy<R, false><<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
-                                                    ctx->NS, ctx->compute_mask, verdict, kGreedyTeamMin);
-    k3_admit_greedy_team<R, false><<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard,
-                                                                        ctx->d_hard_mask, ctx->NS, ctx->compute_mask, verdict);
-  }
-  ctx->tm.launches += 2;
-  CU(cudaGetLastError());
-  return BGC_OK;
+  const size_t ring = greedy_team_smem(R);
+  auto go = [&](auto warp_kern, auto team_kern) -> int {
+    CU(cudaFuncSetAttribute(team_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
+    warp_kern<<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask, ctx->NS,
+                                    ctx->compute_mask, verdict, kGreedyTeamMin);
+    team_kern<<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
+                                                    ctx->NS, ctx->compute_mask, verdict);
+    ctx->tm.launches += 2;
+    CU(cudaGetLastError());
+    return BGC_OK;
+  };
+  return mask ? go(k3_admit_greedy<R, true, VT>, k3_admit_greedy_team<R, true, VT>)
+              : go(k3_admit_greedy<R, false, VT>, k3_admit_greedy_team<R, false, VT>);
 }
 
 int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
@@ -1222,13 +1215,15 @@ int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
 
 }  // namespace
 
-extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
-                                    const uint8_t* d_req_mask, size_t n, uint8_t* d_verdict) {
+namespace {
+template <typename VT>
+int admit_greedy_dev_impl(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req,
+                          const uint8_t* d_req_mask, size_t n, VT* d_verdict) {
   if (!ctx) return BGC_E_BADARG;
   if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (d_ns_id && d_req && d_verdict), "null column pointer");
   NEED(n < (size_t(1) << 31), "greedy admission handles fewer than 2^31 pods per call");
-  NEED(ctx->R <= kMaxR8, "greedy admission is built for R <= 4 (u8 verdicts)");
+  NEED(sizeof(VT) == 2 || ctx->R <= kMaxR8, "u8 verdicts hold at most 4 resources: use bgc_admit_greedy16 for more");
   const long long* cols[kMaxR] = {};
   for (int r = 0; r < ctx->R && n; ++r) {
     NEED(d_req[r], "null request column");
@@ -1284,20 +1279,31 @@ extern "C" int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const
   k_greedy_segments<<<g2, 256, 0, st>>>(ctx->g_keys_sorted, n, ctx->NS, ctx->g_seg);
   ctx->tm.launches++;
   CU(cudaGetLastError());
-  k_greedy_bad_ns<<<ctx->sm_count, 256, 0, st>>>(ctx->g_order, ctx->g_seg, ctx->NS, d_verdict);
+  k_greedy_bad_ns<VT><<<ctx->sm_count, 256, 0, st>>>(ctx->g_order, ctx->g_seg, ctx->NS, d_verdict);
   ctx->tm.launches++;
   CU(cudaGetLastError());
   ctx->head_stale = true;
   switch (ctx->R) {
-    case 1: return launch_k3_r<1>(ctx, st, cols, d_req_mask, n, d_verdict);
-    case 2: return launch_k3_r<2>(ctx, st, cols, d_req_mask, n, d_verdict);
-    case 3: return launch_k3_r<3>(ctx, st, cols, d_req_mask, n, d_verdict);
-    default: return launch_k3_r<4>(ctx, st, cols, d_req_mask, n, d_verdict);
+    case 1: return launch_k3_r<1, VT>(ctx, st, d_req_mask, d_verdict);
+    case 2: return launch_k3_r<2, VT>(ctx, st, d_req_mask, d_verdict);
+    case 3: return launch_k3_r<3, VT>(ctx, st, d_req_mask, d_verdict);
+    case 4: return launch_k3_r<4, VT>(ctx, st, d_req_mask, d_verdict);
+    default: break;
   }
+  if constexpr (sizeof(VT) == 2) {
+    switch (ctx->R) {
+      case 5: return launch_k3_r<5, VT>(ctx, st, d_req_mask, d_verdict);
+      case 6: return launch_k3_r<6, VT>(ctx, st, d_req_mask, d_verdict);
+      case 7: return launch_k3_r<7, VT>(ctx, st, d_req_mask, d_verdict);
+      default: return launch_k3_r<8, VT>(ctx, st, d_req_mask, d_verdict);
+    }
+  }
+  return fail(ctx, BGC_E_BADARG, "R out of range");
 }
 
-extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
-                                const uint8_t* req_mask, size_t n, uint8_t* verdict) {
+template <typename VT>
+int admit_greedy_host_impl(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req,
+                           const uint8_t* req_mask, size_t n, VT* verdict) {
   if (!ctx) return BGC_E_BADARG;
   if (!ctx->d_used) return fail(ctx, BGC_E_STATE, "quota table not set");
   NEED(n == 0 || (ns_id && req && verdict), "null column pointer");
@@ -1319,7 +1325,7 @@ extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64
     CU(cudaMalloc(&ctx->gh_ns, cap * 4));
     for (int r = 0; r < RR; ++r) CU(cudaMalloc(&ctx->gh_req[r], cap * 8));
     CU(cudaMalloc(&ctx->gh_mask, cap));
-    CU(cudaMalloc(&ctx->gh_v, cap));
+    CU(cudaMalloc(&ctx->gh_v, cap * 2));
     ctx->gh_cap = cap; ctx->gh_R = RR;
   }
   cudaStream_t keep = ctx->stream;
@@ -1334,9 +1340,9 @@ extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64
   } else {
     const int64_t* cols[kMaxR];
     for (int r = 0; r < kMaxR; ++r) cols[r] = reinterpret_cast<const int64_t*>(ctx->gh_req[r]);
-    rc = bgc_admit_greedy_dev(ctx, ctx->gh_ns, cols, req_mask ? ctx->gh_mask : nullptr, n, ctx->gh_v);
+    rc = admit_greedy_dev_impl<VT>(ctx, ctx->gh_ns, cols, req_mask ? ctx->gh_mask : nullptr, n, reinterpret_cast<VT*>(ctx->gh_v));
     if (rc == BGC_OK) {
-      e = cudaMemcpyAsync(verdict, ctx->gh_v, n, cudaMemcpyDeviceToHost, ctx->own_stream);
+      e = cudaMemcpyAsync(verdict, ctx->gh_v, n * sizeof(VT), cudaMemcpyDeviceToHost, ctx->own_stream);
       if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->own_stream);
       if (e != cudaSuccess) rc = fail(ctx, BGC_E_CUDA, "greedy copy-out: %s", cudaGetErrorString(e));
     }
@@ -1345,6 +1351,26 @@ extern "C" int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64
   ctx->stream = keep;
   return rc;
 }
+}  // namespace
+
+extern "C" {
+int bgc_admit_greedy_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req, const uint8_t* d_req_mask, size_t n,
+                         uint8_t* d_verdict) {
+  return admit_greedy_dev_impl<uint8_t>(ctx, d_ns_id, d_req, d_req_mask, n, d_verdict);
+}
+int bgc_admit_greedy16_dev(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* const* d_req, const uint8_t* d_req_mask, size_t n,
+                           uint16_t* d_verdict) {
+  return admit_greedy_dev_impl<uint16_t>(ctx, d_ns_id, d_req, d_req_mask, n, d_verdict);
+}
+int bgc_admit_greedy(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req, const uint8_t* req_mask, size_t n,
+                     uint8_t* verdict) {
+  return admit_greedy_host_impl<uint8_t>(ctx, ns_id, req, req_mask, n, verdict);
+}
+int bgc_admit_greedy16(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* req, const uint8_t* req_mask, size_t n,
+                       uint16_t* verdict) {
+  return admit_greedy_host_impl<uint16_t>(ctx, ns_id, req, req_mask, n, verdict);
+}
+}  // extern "C"
 
 extern "C" {
 // ---------------------------------------------------------------- synthetic inputs / checksums

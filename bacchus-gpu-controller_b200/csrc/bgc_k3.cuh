@@ -237,11 +237,13 @@ static __global__ void k_greedy_segments(const uint32_t* __restrict__ sorted_key
   }
 }
 
+// VT = uint8_t: verdict = missing << 4 | exceeded (R <= 4); VT = uint16_t: missing << 8 | exceeded (R <= 8)
+template <typename VT>
 static __global__ void k_greedy_bad_ns(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg,
-                                       uint32_t NS, uint8_t* verdict) {
+                                       uint32_t NS, VT* verdict) {
   const size_t beg = seg[NS], end = seg[NS + 1];
   for (size_t i = beg + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += (size_t)gridDim.x * blockDim.x)
-    verdict[order[i]] = 0xFFu;
+    verdict[order[i]] = (VT)~(VT)0;
 }
 
 template <int R>
@@ -251,7 +253,7 @@ struct GreedyPod {
 };
 
 // verdict of one pod against usage T
-template <int R>
+template <int R, int SHIFT>
 __device__ __forceinline__ uint32_t greedy_verdict(const GreedyPod<R>& p, const long long (&T)[R],
                                                    const long long (&H)[R], uint32_t hm, uint32_t compute_mask) {
   uint32_t missing = 0, exceeded = 0;
@@ -261,15 +263,16 @@ __device__ __forceinline__ uint32_t greedy_verdict(const GreedyPod<R>& p, const 
     if (constrained && !present && ((compute_mask >> r) & 1u)) missing |= 1u << r;
     if (constrained && present && p.q[r] > 0 && p.q[r] > sat_sub_i64(H[r], T[r])) exceeded |= 1u << r;
   }
-  return (missing << 4) | exceeded;
+  return (missing << SHIFT) | exceeded;
 }
 
-template <int R, bool HAS_MASK>
+template <int R, bool HAS_MASK, typename VT>
 __global__ void __launch_bounds__(256)
 k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg, ReqCols<R> req,
                 const uint8_t* __restrict__ req_mask, long long* used, const long long* __restrict__ hard,
                 const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask,
-                uint8_t* __restrict__ verdict, uint32_t team_min) {
+                VT* __restrict__ verdict, uint32_t team_min) {
+  constexpr int SHIFT = sizeof(VT) == 1 ? 4 : 8;
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t warps_total = gridDim.x * (blockDim.x >> 5);
   // heavy namespaces first would be ideal; a strided walk at least spreads neighbours over warps
@@ -312,7 +315,7 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
         for (int r = 0; r < R; ++r) S0[r] = S[r];
         uint32_t live = __ballot_sync(0xFFFFFFFFu, valid), admitted = 0;
         while (live) {
-          const uint32_t v_alone = greedy_verdict<R>(p, S, H, hm, compute_mask);
+          const uint32_t v_alone = greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask);
           live &= ~__ballot_sync(0xFFFFFFFFu, v_alone != 0);
           if (!live) break;
           const bool mine = (live >> lane) & 1u;
@@ -333,7 +336,7 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
             E[r] = incl[r] - (mine ? p.q[r] : 0);
             T[r] = S[r] + E[r];
           }
-          const uint32_t fail = __ballot_sync(0xFFFFFFFFu, mine && greedy_verdict<R>(p, T, H, hm, compute_mask) != 0);
+          const uint32_t fail = __ballot_sync(0xFFFFFFFFu, mine && greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask) != 0);
           if (!fail) {
             admitted |= live;
 #pragma unroll
@@ -361,7 +364,7 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
         }
 #pragma unroll
         for (int r = 0; r < R; ++r) T[r] = S0[r] + incl[r] - (adm ? p.q[r] : 0);
-        my_verdict = adm ? 0u : greedy_verdict<R>(p, T, H, hm, compute_mask);
+        my_verdict = adm ? 0u : greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
         pos = 32;
       }
       while (pos < 32) {
@@ -383,7 +386,7 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
           E[r] = (long long)((unsigned long long)incl[r] - (unsigned long long)((valid && lane >= pos) ? p.q[r] : 0));
           T[r] = (long long)((unsigned long long)S[r] + (unsigned long long)E[r]);
         }
-        const uint32_t v_run = greedy_verdict<R>(p, T, H, hm, compute_mask);
+        const uint32_t v_run = greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
         const uint32_t fail = __ballot_sync(0xFFFFFFFFu, valid && lane >= pos && v_run != 0);
         if (fail == 0) {  // everyone left in the tile is admitted
 #pragma unroll
@@ -399,7 +402,7 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
         pos = v + 1;
         if (pos >= 32) break;
         // ---- reject-run: usage stands still at S until somebody fits on their own
-        const uint32_t v_alone = greedy_verdict<R>(p, S, H, hm, compute_mask);
+        const uint32_t v_alone = greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask);
         const uint32_t later = 0xFFFFFFFFu << pos;
         const uint32_t fits = __ballot_sync(0xFFFFFFFFu, valid && v_alone == 0) & later;
         const uint32_t stop = fits ? (__ffs(fits) - 1u) : 32u;
@@ -407,7 +410,7 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
         pos = stop;
         if (pos >= 32) break;
       }
-      if (valid) verdict[order[t + lane]] = (uint8_t)my_verdict;
+      if (valid) verdict[order[t + lane]] = (VT)my_verdict;
     }
     if (lane == 0) {
 #pragma unroll
@@ -422,18 +425,23 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
 // exclusive scan and a shared-memory atomicMin to find the first rejection / first fit.
 constexpr uint32_t kGreedyTeamMin = 32768;
 constexpr int kGreedyTeam = 1024;
-constexpr int kGreedyDepth = 4;  // tiles of requests in flight per CTA (ring of R * 8 KB per tile)
+// tiles of requests in flight per CTA (ring of R * 8 KB per tile; the ring and the R * 8 KB scan scratch share
+// the 227 KB of dynamic shared memory)
+__host__ __device__ constexpr int greedy_depth(int R) { return R <= 4 ? 4 : R <= 6 ? 3 : 2; }
+__host__ __device__ constexpr size_t greedy_team_smem(int R) { return (size_t)(greedy_depth(R) + 1) * R * kGreedyTeam * 8; }
 
-template <int R, bool HAS_MASK>
+template <int R, bool HAS_MASK, typename VT>
 __global__ void __launch_bounds__(kGreedyTeam, 1)
 k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg, ReqCols<R> req,
                      const uint8_t* __restrict__ req_mask, long long* used, const long long* __restrict__ hard,
                      const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask,
-                     uint8_t* __restrict__ verdict) {
-  extern __shared__ __align__(16) long long g_ring[];  // [kGreedyDepth][R][kGreedyTeam]
+                     VT* __restrict__ verdict) {
+  constexpr int SHIFT = sizeof(VT) == 1 ? 4 : 8;
+  constexpr int kGreedyDepth = greedy_depth(R);
+  extern __shared__ __align__(16) long long g_ring[];  // [kGreedyDepth][R][kGreedyTeam], then s_E[R][kGreedyTeam]
   __shared__ long long s_wtot[R][32];    // per-warp totals, then their exclusive prefix
   __shared__ long long s_total[R];
-  __shared__ long long s_E[R][kGreedyTeam];
+  long long (*s_E)[kGreedyTeam] = reinterpret_cast<long long (*)[kGreedyTeam]>(g_ring + (size_t)kGreedyDepth * R * kGreedyTeam);
   __shared__ uint32_t s_first[2], s_fit[2];
   const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   constexpr uint32_t BIG = 0xFFFFFFFFu;
@@ -538,7 +546,7 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
         for (int r = 0; r < R; ++r) S0[r] = S[r];
         bool live = valid, adm = false;
         while (true) {
-          if (live && greedy_verdict<R>(p, S, H, hm, compute_mask) != 0) live = false;  // can never fit again
+          if (live && greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask) != 0) live = false;  // can never fit again
           if (!__syncthreads_or(live)) break;  // saturated: nobody left to consider
           const uint32_t par = iter & 1u;
           ++iter;
@@ -549,7 +557,7 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
           block_exclusive(x, E);  // its barriers also publish the reset of s_first[par]
 #pragma unroll
           for (int r = 0; r < R; ++r) T[r] = S[r] + E[r];
-          const uint32_t fail = __ballot_sync(0xFFFFFFFFu, live && greedy_verdict<R>(p, T, H, hm, compute_mask) != 0);
+          const uint32_t fail = __ballot_sync(0xFFFFFFFFu, live && greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask) != 0);
           if (fail && lane == (uint32_t)(__ffs(fail) - 1)) atomicMin(&s_first[par], tid);
           __syncthreads();
           const uint32_t v = s_first[par];
@@ -571,9 +579,9 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
           block_exclusive(x, E);
 #pragma unroll
           for (int r = 0; r < R; ++r) T[r] = S0[r] + E[r];
-          my_verdict = adm ? 0u : greedy_verdict<R>(p, T, H, hm, compute_mask);
+          my_verdict = adm ? 0u : greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
         } else {                      // nothing admitted in this tile: usage never moved
-          my_verdict = valid ? greedy_verdict<R>(p, S0, H, hm, compute_mask) : 0u;
+          my_verdict = valid ? greedy_verdict<R, SHIFT>(p, S0, H, hm, compute_mask) : 0u;
         }
         pos = kGreedyTeam;
         __syncthreads();  // s_E / s_wtot are reused by the next tile
@@ -621,7 +629,7 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
           T[r] = (long long)((unsigned long long)S[r] + (unsigned long long)E[r]);
           s_E[r][tid] = E[r];
         }
-        const uint32_t v_run = greedy_verdict<R>(p, T, H, hm, compute_mask);
+        const uint32_t v_run = greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
         const uint32_t fail = __ballot_sync(0xFFFFFFFFu, valid && tid >= pos && v_run != 0);
         if (fail && lane == (uint32_t)(__ffs(fail) - 1)) atomicMin(&s_first[par], tid);
         __syncthreads();
@@ -637,7 +645,7 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
         pos = v + 1;
         if (pos >= (uint32_t)kGreedyTeam) break;
         // ---- reject-run: usage stands still at S until somebody fits on their own
-        const uint32_t v_alone = greedy_verdict<R>(p, S, H, hm, compute_mask);
+        const uint32_t v_alone = greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask);
         const uint32_t fits = __ballot_sync(0xFFFFFFFFu, valid && tid >= pos && v_alone == 0);
         if (fits && lane == (uint32_t)(__ffs(fits) - 1)) atomicMin(&s_fit[par], tid);
         __syncthreads();
@@ -646,7 +654,7 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
         pos = stop;
         if (pos >= (uint32_t)kGreedyTeam) break;
       }
-      if (valid) verdict[order[t + tid]] = (uint8_t)my_verdict;
+      if (valid) verdict[order[t + tid]] = (VT)my_verdict;
     }
     if (tid == 0) {
 #pragma unroll

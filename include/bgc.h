@@ -205,11 +205,18 @@ int bgc_quota_eval_typed_dev(bgc_ctx *ctx, const void *d_ns_id, int ns_type, con
  * ResourceQuota the reference writes (src/controller.rs:89-110): per namespace, in arrival order, a
  * pod is admitted iff its verdict (same encoding and rules as bgc_quota_eval) against the CURRENT
  * usage is 0, and only admitted pods add their requests to the usage table, which is updated in
- * place.  Order-dependent, so the checker is the literal loop.  n < 2^31, R <= 4. */
+ * place.  Order-dependent, so the checker is the literal loop.  n < 2^31, R <= 4 (u8 verdicts; see the u16
+ * form below).  Pods are grouped by namespace with the library's own stable radix sort (no CUB). */
 int bgc_admit_greedy(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *req,
                      const uint8_t *req_mask, size_t n, uint8_t *verdict);
 int bgc_admit_greedy_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
                          const uint8_t *d_req_mask, size_t n, uint8_t *d_verdict);
+/* u16 form (verdict = missing << 8 | exceeded) for up to BGC_MAX_R resources — the six pod-relevant keys of
+ * src/synchronizer.rs:249-281 in one pass; works for any R <= 8, the u8 entry points refuse R > 4 */
+int bgc_admit_greedy16(bgc_ctx *ctx, const uint32_t *ns_id, const int64_t *const *req,
+                       const uint8_t *req_mask, size_t n, uint16_t *verdict);
+int bgc_admit_greedy16_dev(bgc_ctx *ctx, const uint32_t *d_ns_id, const int64_t *const *d_req,
+                           const uint8_t *d_req_mask, size_t n, uint16_t *d_verdict);
 
 /* ---- allocation-free usage reduction ---------------------------------------------------------
  * No counterpart in the reference.  For callers that cannot allocate device memory when they

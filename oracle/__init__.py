@@ -187,6 +187,17 @@ def admit_greedy(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask):
     return verdict, u
 
 
+def admit_greedy16(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask):
+    """u16 verdicts (missing << 8 | exceeded), any R <= 8.  Returns (verdict, used_after)."""
+    R = len(req)
+    n = ns_id.shape[0]
+    verdict = np.empty(n, np.uint16)
+    u = np.ascontiguousarray(used, dtype=np.int64).copy()
+    lib().quota_ref_admit_greedy16(_p(ns_id), _ptrs(req), _p(req_mask), C.c_size_t(n), C.c_uint32(NS), C.c_uint32(R), _p(u),
+                                   _p(np.ascontiguousarray(hard)), _p(hard_mask), C.c_uint8(compute_mask), _p(verdict))
+    return verdict, u
+
+
 def quota_eval16(ns_id, req, req_mask, NS, used, hard, hard_mask, compute_mask, threads: int = 1):
     R = len(req)
     n = ns_id.shape[0]

@@ -121,6 +121,22 @@ void quota_ref_admit_greedy(const uint32_t *ns_id, const int64_t *const *req,
   }
 }
 
+/* the same literal loop with u16 verdicts (missing << 8 | exceeded), any R <= 8 */
+void quota_ref_admit_greedy16(const uint32_t *ns_id, const int64_t *const *req,
+                              const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
+                              int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
+                              uint8_t compute_mask, uint16_t *verdict) {
+  for (size_t j = 0; j < n; ++j) {
+    const uint32_t ns = ns_id[j];
+    const uint32_t b = eval_bits(ns, req, req_mask ? req_mask[j] : 0xFF, j, NS, R, used, hard, hard_mask, compute_mask);
+    const uint16_t v = b == 0xFFFFFFFFu ? 0xFFFF : (uint16_t)(((b & 0xFF) << 8) | (b >> 8));
+    verdict[j] = v;
+    if (v == 0)
+      for (uint32_t r = 0; r < R; ++r)
+        used[(size_t)r * NS + ns] = (int64_t)((uint64_t)used[(size_t)r * NS + ns] + (uint64_t)req[r][j]);
+  }
+}
+
 /* ------------------------------------------------------------------ generator spec */
 static inline uint64_t sm64(uint64_t x) {
   x += 0x9E3779B97F4A7C15ull;

@@ -86,6 +86,10 @@ void gen_ref_policy_fill(uint64_t seed, uint64_t first, size_t count, uint8_t *o
 /* order-independent checksum of a u8 stream: sum_i SM64(i ^ v[i]<<56 ...) */
 uint64_t gen_ref_checksum_u8(const uint8_t *v, uint64_t first, size_t count);
 
+void quota_ref_admit_greedy16(const uint32_t *ns_id, const int64_t *const *req,
+                              const uint8_t *req_mask, size_t n, uint32_t NS, uint32_t R,
+                              int64_t *used, const int64_t *hard, const uint8_t *hard_mask,
+                              uint8_t compute_mask, uint16_t *verdict);
 /* typed forms: the same results as the plain functions on the widened columns (quota_ref.c) */
 void quota_ref_usage_reduce_typed(const void *ns_id, uint32_t ns_type, const void *const *cols,
                                   const uint8_t *type, const uint8_t *shift, size_t n, uint32_t NS,

@@ -110,3 +110,35 @@ def test_greedy_monotone_fast_path_long_segments(engine, oracle, R, n, NS):
     assert np.array_equal(engine.admit_greedy(ns, req, mask), want_v)
     assert np.array_equal(engine.usage_get(), want_u)
     assert 0.01 < np.mean(want_v == 0) < 0.99
+
+
+@pytest.mark.parametrize("R", [2, 5, 6, 8])
+@pytest.mark.parametrize("with_mask", [False, True])
+@pytest.mark.parametrize("n,NS", [(33, 2), (50_000, 300), (200_003, 70_000), (70_000, 1)])
+def test_greedy_wide_u16_verdicts_up_to_eight_resources(engine, oracle, R, with_mask, n, NS):
+    """bgc_admit_greedy16: the six pod-relevant keys of src/synchronizer.rs:249-281 (and up to 8 columns) in one
+    pass, u16 verdicts; warp walker, CTA-team walker (one 70,000-pod namespace) and the 3-pass sort (70,000
+    namespaces need 17 key bits) against the literal loop."""
+    rng = np.random.default_rng(R * 13 + n)
+    ns = rng.integers(0, NS, n, dtype=np.uint32)
+    req = [rng.integers(0, 1 << 30, n, dtype=np.int64) for _ in range(R)]
+    for r in range(R):
+        req[r][::9] = 0
+        if n < 60_000:
+            req[r][3::41] = -rng.integers(1, 1000, req[r][3::41].shape[0])
+    if n > 100:
+        ns[5] = NS
+        ns[n // 3] = 0xFFFFFFFF
+    mask = rng.integers(0, 256, n, dtype=np.uint8) | np.uint8(0b0110) if with_mask else None
+    used0 = oracle.usage_reduce(ns[: n // 4 + 1], [c[: n // 4 + 1] for c in req], NS)
+    hard, hm = make_hard(used0 * 4 + 1000, 3)
+    hm[::6] = rng.integers(0, 1 << R, hm[::6].shape[0], dtype=np.uint8)
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(used0)
+    want_v, want_u = oracle.admit_greedy16(ns, req, mask, NS, used0, hard, hm, _cm(UNITS[R]))
+    got_v = engine.admit_greedy(ns, req, mask, wide=True)
+    assert np.array_equal(got_v, want_v)
+    assert np.array_equal(engine.usage_get(), want_u)
+    if R > 4:
+        with pytest.raises(Exception):
+            engine.admit_greedy(ns, req, mask)          # u8 verdicts cannot hold more than 4 resources
