@@ -109,8 +109,17 @@ def _parses_as_userbootstrap(obj) -> bool:
         rr = rb.get("role_ref")
         if not isinstance(rr, dict) or not all(isinstance(rr.get(k), str) for k in ("apiGroup", "kind", "name")):
             return False
-        if not isinstance(rb.get("subjects", []), (list, type(None))):
-            return False
+        subs = rb.get("subjects")
+        if subs is not None:
+            if not isinstance(subs, list):
+                return False
+            if not all(isinstance(x, dict) and isinstance(x.get("kind"), str) and isinstance(x.get("name"), str) for x in subs):
+                return False             # k8s-openapi Subject: kind and name are required
+    quota = spec.get("quota")
+    if isinstance(quota, dict) and quota.get("hard") is not None:
+        hard = quota["hard"]
+        if not isinstance(hard, dict) or not all(isinstance(v, (str, int, float)) and not isinstance(v, bool) for v in hard.values()):
+            return False                 # a Quantity deserialises from a string or a number
     return True
 
 

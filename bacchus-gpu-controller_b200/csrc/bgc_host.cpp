@@ -882,7 +882,20 @@ bool parses_as_userbootstrap(const JVal& obj) {
     const JVal* rr = rb->get_obj("role_ref");
     if (!rr || !rr->get_str("apiGroup") || !rr->get_str("kind") || !rr->get_str("name")) return false;
     const JVal* subs = rb->get("subjects");
-    if (subs && subs->kind != JVal::Null && subs->kind != JVal::Arr) return false;
+    if (subs && subs->kind != JVal::Null) {
+      if (subs->kind != JVal::Arr) return false;
+      for (const auto& sub : subs->arr)  // k8s-openapi Subject: `kind` and `name` are required strings
+        if (sub.kind != JVal::Obj || !sub.get_str("kind") || !sub.get_str("name")) return false;
+    }
+  }
+  // ResourceQuotaSpec.hard: a map of Quantity, which deserialises from a string or a number
+  if (const JVal* quota = spec->get("quota"); quota && quota->kind == JVal::Obj) {
+    const JVal* hard = quota->get("hard");
+    if (hard && hard->kind != JVal::Null) {
+      if (hard->kind != JVal::Obj) return false;
+      for (const auto& kv : hard->obj)
+        if (kv.second.kind != JVal::Str && kv.second.kind != JVal::Num) return false;
+    }
   }
   return true;
 }
@@ -933,6 +946,20 @@ bgc_review* bgc_review_parse(const char* json, size_t len, char* err, size_t err
     return nullptr;
   }
   r->request = r->doc.get_obj("request");
+  // serde would reject the whole AdmissionReview for a wrong-typed userInfo.groups (Option<Vec<String>>): so does
+  // this parser, instead of quietly dropping the odd entries
+  if (r->request) {
+    const JVal* ui = r->request->get_obj("userInfo");
+    const JVal* groups = ui ? ui->get("groups") : nullptr;
+    bool bad = groups && groups->kind != JVal::Null && groups->kind != JVal::Arr;
+    if (groups && groups->kind == JVal::Arr)
+      for (const auto& g : groups->arr) bad = bad || g.kind != JVal::Str;
+    if (bad) {
+      if (err && err_len) snprintf(err, err_len, "request.userInfo.groups must be an array of strings");
+      delete r;
+      return nullptr;
+    }
+  }
   return r;
 }
 

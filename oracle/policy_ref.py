@@ -92,8 +92,20 @@ def _parses_as_userbootstrap(obj: dict) -> bool:
         if not isinstance(rr, dict) or not all(isinstance(rr.get(k), str) for k in ("apiGroup", "kind", "name")):
             return False
         subs = rb.get("subjects")
-        if subs is not None and not isinstance(subs, list):
+        if subs is not None:
+            if not isinstance(subs, list):
+                return False
+            for sub in subs:   # k8s-openapi 0.18 Subject: `kind` and `name` are required
+                if not isinstance(sub, dict) or not isinstance(sub.get("kind"), str) or not isinstance(sub.get("name"), str):
+                    return False
+    quota = spec.get("quota")
+    if isinstance(quota, dict) and quota.get("hard") is not None:   # BTreeMap<String, Quantity>; Quantity <- string | number
+        hard = quota["hard"]
+        if not isinstance(hard, dict):
             return False
+        for v in hard.values():
+            if isinstance(v, bool) or not isinstance(v, (str, int, float)):
+                return False
     return True
 
 

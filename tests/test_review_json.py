@@ -146,3 +146,29 @@ def test_pod_reviews_wire_to_wire_with_a_stand_in_engine(bgc, oracle):
                 assert msg.startswith(f"exceeded quota: {ns_name}, requested: ") or msg.startswith(f"failed quota: {ns_name}: must specify ")
                 seen.add(msg.split(":")[0])
         assert seen == {"exceeded quota", "failed quota"}
+
+
+def test_parser_is_as_strict_as_serde_on_groups_subjects_and_quota(bgc):
+    """a wrong-typed userInfo.groups fails the whole review (AdmissionReview deserialisation,
+    src/admission.rs:186); an object whose rolebinding subjects lack kind/name, or whose quota.hard holds
+    non-quantities, does not parse as UserBootstrap (src/admission.rs:341-347 answers `invalid`)."""
+    from bacchus_helpers import ub_review
+    for groups in ("gpu", ["gpu", 7], [None]):
+        with pytest.raises(ValueError):
+            bgc.review.Review(json.dumps(ub_review(groups=groups)))
+    assert bgc.review.Review(json.dumps(ub_review(groups=None))).request_fields()["groups"] is None
+    good_rb = {"role_ref": {"apiGroup": "rbac.authorization.k8s.io", "kind": "ClusterRole", "name": "edit"},
+               "subjects": [{"kind": "User", "name": "alice"}]}
+    cases = [({"rolebinding": good_rb}, True),
+             ({"rolebinding": {**good_rb, "subjects": [{"kind": "User"}]}}, False),
+             ({"rolebinding": {**good_rb, "subjects": ["alice"]}}, False),
+             ({"rolebinding": {**good_rb, "subjects": None}}, True),
+             ({"quota": {"hard": {"requests.cpu": "8", "requests.nvidia.com/gpu": 2}}}, True),
+             ({"quota": {"hard": {"requests.cpu": ["8"]}}}, False),
+             ({"quota": {"hard": "lots"}}, False)]
+    for spec, ok in cases:
+        rv = ub_review(spec=spec)
+        f = bgc.review.Review(json.dumps(rv)).request_fields()
+        assert f["parse_ok"] is ok, spec
+        assert P._parses_as_userbootstrap(rv["request"]["object"]) is ok, spec
+        assert bgc.admission._parses_as_userbootstrap(rv["request"]["object"]) is ok, spec
