@@ -861,6 +861,29 @@ def main():
     # ---- sub-records: the other kernels under the same clock, the in-run crossover, and C5 as one job
     eng.use_torch_stream()
     subs = {}
+    if rank == 0 and world == 1 and not args.no_sub and e2e is not None:
+        # the same step on the compact columns RESIDENT in HBM (the typed _dev entry points): what the kernels do
+        # when the bytes per pod drop from 28 to 9 — no longer HBM-bound but bound by the shared-memory atomics
+        try:
+            d_rns, d_cns = hr_ns.to(dev), hc_ns.to(dev)
+            d_rc, d_cc = [h.to(dev) for h in hr_cols], [h.to(dev) for h in hc_cols]
+            types = [tt[np.dtype(t)][1] for t, _ in plan]
+            shifts = [sft for _, sft in plan]
+            d_v2 = torch.empty(n, dtype=torch.uint8, device=dev)
+            eng.quota_table_set(hard, hard_mask, UNITS[R])
+            k1t = _median_ms(torch, lambda: eng.usage_reduce_typed_dev(d_rns, d_rc, shifts, 0, None, types=types), 7, 2)
+            k2t = _median_ms(torch, lambda: eng.quota_eval_typed_dev(d_cns, d_cc, shifts, None, d_v2, types=types), 7, 2)
+            same = bool(np.array_equal(eng.usage_get(), used0)) and eng.checksum_u8_dev(d_v2[n - cnt:], n - cnt) == oracle.checksum_u8(v_tail, n - cnt)
+            subs["compact_columns_device_resident"] = {
+                "entry_points": "bgc_usage_reduce_typed_dev + bgc_quota_eval_typed_dev", "bytes_per_pod": {"k1": bpp, "k2": bpp + 1},
+                "k1_ms": k1t, "k2_ms": k2t, "pods_per_s": n / ((k1t + k2t) * 1e-3),
+                "k1_GBps": n * bpp / k1t / 1e6, "k1_frac_of_hbm_peak": n * bpp / k1t / 1e6 / peak,
+                "k2_GBps": n * (bpp + 1) / k2t / 1e6, "k2_frac_of_hbm_peak": n * (bpp + 1) / k2t / 1e6 / peak,
+                "verified_vs_oracle": same}
+            del d_rns, d_cns, d_rc, d_cc, d_v2
+        except Exception as e:  # noqa: BLE001
+            subs["compact_columns_device_resident"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        torch.cuda.empty_cache()
     if rank == 0 and world == 1 and not args.no_sub:
         for name, fn in (("k0", lambda: k0_record(torch, bgc, eng, oracle, peak)),
                          ("k3", lambda: k3_record(torch, bgc, eng, oracle, Q, wl, seed, peak)),
