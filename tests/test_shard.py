@@ -147,3 +147,20 @@ def test_two_rank_gloo_shards_need_no_collective_on_the_data_path():
     for p in procs:
         p.join(60)
     assert res == [(0, True), (1, True)]
+
+
+def test_local_ids_are_dense_and_cover_every_namespace_once(bgc):
+    """Row E: every rank's dense per-shard ids (shard.local_ids) — what bench.py's one-job C5 run and
+    bgc_synth_pods_shard_dev use — partition the namespace space: each global id is owned by exactly one rank and
+    maps to a distinct local id below that rank's table size."""
+    S = bgc.shard
+    for NS, world in ((1000, 1), (1000, 2), (12_345, 8)):
+        seen = np.zeros(NS, np.int64)
+        for g in range(world):
+            owned, local_of = S.local_ids(NS, world, g)
+            assert np.array_equal(owned, np.sort(owned)) and np.array_equal(S.shard_of(owned, world), np.full(owned.shape, g, np.uint32))
+            assert np.array_equal(local_of[owned], np.arange(owned.shape[0], dtype=np.uint32))
+            others = np.setdiff1d(np.arange(NS), owned)
+            assert np.all(local_of[others] == 0xFFFFFFFF)
+            seen[owned] += 1
+        assert np.all(seen == 1)
