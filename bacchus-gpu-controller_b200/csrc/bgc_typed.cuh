@@ -179,8 +179,10 @@ k1_scatter_typed(TypedCols<R> in, size_t n, long long* used, uint32_t NS, uint32
 }
 
 // ------------------------------------------------------------------ K2 over typed columns
+// (min 4 CTAs per SM: left alone the generic widening code takes 114 registers and two CTAs per SM — ncu showed
+// 23 % of the warp slots occupied and the kernel at half the speed of the int64 one)
 template <int R, bool HAS_MASK, typename VT>
-__global__ void __launch_bounds__(kK2Threads)
+__global__ void __launch_bounds__(kK2Threads, 4)
 k2_quota_eval_typed(TypedCols<R> in, const uint8_t* __restrict__ req_mask, size_t n, const long long* __restrict__ head,
                     const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask, VT* __restrict__ verdict,
                     uint32_t pf_dist, uint32_t vec) {

@@ -59,6 +59,24 @@ int main(void) {
   }
   printf("used gpu=[%lld,%lld] cpu=[%lld,%lld]; verdicts = %u %u %u (0 = allow, bit r = resource r exceeded)\n",
          (long long)used[0], (long long)used[1], (long long)used[2], (long long)used[3], verdict[0], verdict[1], verdict[2]);
+
+  /* the same pods as narrow columns (bgc_*_typed): u16 namespace ids, u8 gpu counts, u16 cpu millicores —
+   * 5 bytes per pod instead of 20 across PCIe; values are (int64) element << shift */
+  const uint16_t run_ns16[3] = {0, 0, 1}, cand_ns16[3] = {0, 0, 1};
+  const uint8_t run_gpu8[3] = {1, 0, 1}, cand_gpu8[3] = {1, 2, 1};
+  const uint16_t run_cpu16[3] = {2000, 4000, 1000}, cand_cpu16[3] = {2000, 1000, 500};
+  const bgc_col run_cols[2] = {{run_gpu8, BGC_T_U8, 0, {0}}, {run_cpu16, BGC_T_U16, 0, {0}}};
+  const bgc_col cand_cols[2] = {{cand_gpu8, BGC_T_U8, 0, {0}}, {cand_cpu16, BGC_T_U16, 0, {0}}};
+  int64_t used_t[4];
+  uint8_t verdict_t[3];
+  rc = bgc_usage_reduce_typed(ctx, run_ns16, BGC_T_U16, run_cols, 3, 0, used_t);
+  if (rc == BGC_OK) rc = bgc_quota_eval_typed(ctx, cand_ns16, BGC_T_U16, cand_cols, NULL, 3, verdict_t);
+  if (rc != BGC_OK) {
+    fprintf(stderr, "narrow-column path: %s\n", bgc_last_error(ctx));
+    return 1;
+  }
+  printf("narrow columns: used gpu=[%lld,%lld] cpu=[%lld,%lld]; verdicts = %u %u %u\n", (long long)used_t[0], (long long)used_t[1],
+         (long long)used_t[2], (long long)used_t[3], verdict_t[0], verdict_t[1], verdict_t[2]);
   bgc_ctx_destroy(ctx);
   return 0;
 }

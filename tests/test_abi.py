@@ -99,3 +99,4 @@ def test_c_example_runs_on_the_device(tmp_path):
     assert "request 0: allowed=1 class=1" in out.stdout and "user is not in authorized group" in out.stdout
     assert "request 2: allowed=1 class=0 reason=12" in out.stdout
     assert "used gpu=[1,1] cpu=[6000,1000]; verdicts = 0 1 1" in out.stdout
+    assert "narrow columns: used gpu=[1,1] cpu=[6000,1000]; verdicts = 0 1 1" in out.stdout
