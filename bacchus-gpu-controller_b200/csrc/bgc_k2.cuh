@@ -70,8 +70,10 @@ constexpr int kK2Threads = 256;
 
 // PODS pods per thread (4 for R <= 4, 2 above): one vector ns load, R vector request loads, one
 // HeadRow gather per pod (one or two 32-byte sectors), one packed verdict store.
+// (min 4 CTAs per SM = 64 registers: at 68 the kernel ran three CTAs per SM; the fourth one's gathers in flight are
+// worth 82 % -> 92 % of the HBM roofline at 10^6 namespaces and 99 % -> 101 % on C3)
 template <int R, bool HAS_MASK, bool VEC, typename VT>
-__global__ void __launch_bounds__(kK2Threads)
+__global__ void __launch_bounds__(kK2Threads, 4)
 k2_quota_eval(const uint32_t* __restrict__ ns_id, ReqCols<R> req, const uint8_t* __restrict__ req_mask,
               size_t n, const long long* __restrict__ head, const uint8_t* __restrict__ hard_mask,
               uint32_t NS, uint32_t compute_mask, VT* __restrict__ verdict, uint32_t pf_dist) {
