@@ -142,3 +142,35 @@ def test_greedy_wide_u16_verdicts_up_to_eight_resources(engine, oracle, R, with_
     if R > 4:
         with pytest.raises(Exception):
             engine.admit_greedy(ns, req, mask)          # u8 verdicts cannot hold more than 4 resources
+
+
+@pytest.mark.parametrize("R,wide", [(1, False), (3, False), (4, False), (6, True), (8, True)])
+def test_greedy_long_segments_in_and_out_of_the_monotone_range(engine, oracle, R, wide):
+    """Four namespaces of ~60k pods each (all above the 32,768-pod threshold of the CTA-wide walker): ns 0 stays
+    inside the monotone fast path (requests in [0, 2^40], usage in [0, 2^62]); ns 1 has one negative request (that
+    tile takes the exact alternating path); ns 2 starts with usage above 2^62 (exact path throughout); ns 3 has no
+    quota object and its usage crosses 2^62 half-way (fast path first, exact path after).  Verdicts and final usage
+    against the literal loop."""
+    rng = np.random.default_rng(R)
+    n, NS = 240_017, 4
+    ns = rng.integers(0, NS, n, dtype=np.uint32)
+    req = [rng.choice(np.array([0, 1, 2, 250, 4000, 1 << 20, 1 << 33, 1 << 40], np.int64), n) for _ in range(R)]
+    mask = rng.integers(0, 256, n, dtype=np.uint8) | np.uint8(0b0110)
+    neg = np.nonzero(ns == 1)[0][777]
+    req[0][neg] = -5
+    used0 = np.zeros((R, NS), np.int64)
+    used0[:, 2] = (1 << 62) + 12345
+    used0[:, 3] = (1 << 62) - (30_000 << 40)                # crossed after ~30k admitted 2^40-byte requests
+    hard = np.full((R, NS), np.iinfo(np.int64).max, np.int64)
+    hard[:, 0] = 7 * (1 << 40)
+    hard[:, 1] = 5 * (1 << 40)
+    hm = np.array([(1 << R) - 1, (1 << R) - 1, (1 << R) - 1, 0], np.uint8)   # ns 3 has no quota object: everything is admitted
+    req[0][ns == 3] = 1 << 40
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(used0)
+    f = oracle.admit_greedy16 if wide else oracle.admit_greedy
+    want_v, want_u = f(ns, req, mask, NS, used0, hard, hm, _cm(UNITS[R]))
+    got_v = engine.admit_greedy(ns, req, mask, wide=wide)
+    assert np.array_equal(got_v, want_v)
+    assert np.array_equal(engine.usage_get(), want_u)
+    assert 0.0 < np.mean(want_v[ns == 0] == 0) < 1.0 and np.all(want_v[ns == 3] == 0)
