@@ -90,6 +90,49 @@ while time.time() < t_end:
             assert np.array_equal(eng.admit_greedy(ns, req, mask), gv), f"K3 verdict mismatch seed={seed} R={R} NS={NS} n={n}"
             assert np.array_equal(eng.usage_get(), gu), f"K3 usage mismatch seed={seed}"
             stats["k3"] = stats.get("k3", 0) + 1
+    elif it % 3 == 0:      # R = 5..8: the u16 form of the greedy walkers
+        h2 = hard + np.abs(hard) // 4 + 100
+        eng.quota_table_set(h2, hm, units); eng.usage_set(want)
+        gv, gu = oracle.admit_greedy16(ns, req, mask, NS, want, h2, hm, cm)
+        assert np.array_equal(eng.admit_greedy(ns, req, mask, wide=True), gv), f"K3/16 verdict mismatch seed={seed} R={R} NS={NS} n={n}"
+        assert np.array_equal(eng.usage_get(), gu), f"K3/16 usage mismatch seed={seed}"
+        stats["k3_u16"] = stats.get("k3_u16", 0) + 1
+    if R <= 4 and it % 2 == 0:   # narrow columns: random element types and shifts, u16 ids when they fit
+        kinds = [str(rng.choice(["u8", "u16", "u32", "i32", "i64"])) for _ in range(R)]
+        npt = {"u8": np.uint8, "u16": np.uint16, "u32": np.uint32, "i32": np.int32, "i64": np.int64}
+        shifts = [int(rng.integers(0, 64)) if rng.random() < 0.3 else int(rng.integers(0, 24)) for _ in range(R)]
+        tcols = [c.astype(npt[k]) for c, k in zip(req, kinds)]          # truncating casts: any bit pattern is a valid input
+        tns = ns.astype(np.uint16) if NS <= 65536 and rng.random() < 0.7 else ns
+        eng.quota_table_set(hard, hm, units)
+        eng.set_k1_variant(int(rng.choice([0, 3])))
+        tu = oracle.usage_reduce_typed(tns, tcols, shifts, NS, threads=4)
+        assert np.array_equal(eng.usage_reduce_typed(tns, tcols, shifts), tu), f"typed K1 mismatch seed={seed} kinds={kinds} shifts={shifts}"
+        tv = oracle.quota_eval_typed(tns, tcols, shifts, mask, NS, tu, hard, hm, cm, threads=4)
+        assert np.array_equal(eng.quota_eval_typed(tns, tcols, shifts, mask), tv), f"typed K2 mismatch seed={seed} kinds={kinds} shifts={shifts}"
+        stats["typed"] = stats.get("typed", 0) + 1
+    if it % 7 == 0:        # one shard of a global stream = the oracle's stream filtered on the host
+        from oracle import quota_ref as Q
+        world = int(rng.choice([1, 2, 3, 8])); g = int(rng.integers(0, world))
+        Rg = min(R, 4); kinds_g = [int(x) for x in rng.integers(0, 4, Rg)]
+        dist = int(rng.integers(0, 2)); m = int(rng.integers(1, 150_000))
+        a, b = Q.scramble_params(NS)
+        cdf = Q.zipf_cdf(NS, 1.1) if dist else None
+        d_cdf = torch.from_numpy(cdf.view(np.int64)).cuda() if dist else None
+        first = int(rng.integers(0, 1 << 40))
+        src = oracle.gen_fill(oracle.gen_params(seed, 1, NS, dist, 0, first + m, a, b, cdf, kinds_g), first, m, want_mask=True)
+        owned, local_of = bgc.shard.local_ids(NS, world, g)
+        sp = bgc.synth_params(seed, 1, NS, dist, 0, first + m, a, b, d_cdf, kinds_g)
+        kept = eng.synth_pods_shard_dev(sp, first, m, world, g)
+        keep = np.nonzero(bgc.shard.shard_of(src[0], world) == g)[0]
+        assert kept == keep.shape[0], f"shard count mismatch seed={seed}"
+        if kept:
+            d_ns = torch.empty(kept, dtype=torch.int32, device="cuda"); d_rq = [torch.empty(kept, dtype=torch.int64, device="cuda") for _ in range(Rg)]
+            d_mk = torch.empty(kept, dtype=torch.uint8, device="cuda"); d_sx = torch.empty(kept, dtype=torch.int64, device="cuda")
+            eng.synth_pods_shard_dev(sp, first, m, world, g, torch.from_numpy(local_of.view(np.int32)).cuda(), 0, d_ns, d_rq, d_mk, d_sx)
+            torch.cuda.synchronize()
+            assert np.array_equal(d_ns.cpu().numpy().view(np.uint32), local_of[src[0][keep]]) and np.array_equal(d_sx.cpu().numpy(), keep + first)
+            assert all(np.array_equal(d_rq[r].cpu().numpy(), src[1][r][keep]) for r in range(Rg)) and np.array_equal(d_mk.cpu().numpy(), src[2][keep])
+        stats["shard_gen"] = stats.get("shard_gen", 0) + 1
     if it % 5 == 0:
         m = int(rng.integers(1, 200_000))
         op = rng.integers(0, 256, m, dtype=np.uint8); fl = rng.integers(0, 65536, m, dtype=np.uint16)
