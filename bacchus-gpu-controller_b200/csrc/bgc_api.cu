@@ -599,9 +599,14 @@ int bounced(bgc_ctx* ctx, const BounceCol* cols, int ncols, const BounceOut* out
     const size_t m = n - off < piece ? n - off : piece;
     const int slot = (int)(j & 1);
     std::thread next;
+    bool next_filled = true;
     if (off + piece < n) {
       const size_t off2 = off + piece, m2 = n - off2 < piece ? n - off2 : piece;
-      next = std::thread(fill, slot ^ 1, off2, m2);
+      try {  // no exception may cross the C boundary: if a thread cannot be started the copy simply is not overlapped
+        next = std::thread(fill, slot ^ 1, off2, m2);
+      } catch (...) {
+        next_filled = false;
+      }
     }
     const void* in[kBounceMaxCols];
     void* out[4];
@@ -612,6 +617,10 @@ int bounced(bgc_ctx* ctx, const BounceCol* cols, int ncols, const BounceOut* out
       for (int o = 0; o < nouts; ++o) std::memcpy(static_cast<char*>(outs[o].dst) + off * outs[o].width, out[o], m * outs[o].width);
     if (next.joinable()) next.join();
     if (rc) break;
+    if (!next_filled) {
+      const size_t off2 = off + piece, m2 = n - off2 < piece ? n - off2 : piece;
+      fill(slot ^ 1, off2, m2);
+    }
   }
   return rc;
 }
