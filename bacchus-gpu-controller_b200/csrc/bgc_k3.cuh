@@ -178,17 +178,25 @@ k_rsort_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
       s_run[threadIdx.x] = before;
       s_goff[threadIdx.x] = off;
     }
+    // every load of the tile is issued before the first round (ncu: with one load per thread per round the kernel
+    // sat in long-scoreboard stalls at 13 % issue utilisation, a tile taking ~100 us of exposed latency)
+    uint32_t keys[kSortRounds], idxs[kSortRounds];
+#pragma unroll
+    for (int r = 0; r < kSortRounds; ++r) {
+      const size_t i = base + (size_t)r * kSortThreads + threadIdx.x;
+      keys[r] = i < n ? sort_key_at(keys_in, ns_id, NS, i) : 0u;
+      idxs[r] = i < n ? (idx_in ? idx_in[i] : (uint32_t)i) : 0u;
+    }
+#pragma unroll
     for (int r = 0; r < kSortRounds; ++r) {
 #pragma unroll
       for (int w = 0; w < kSortThreads / 32; ++w) s_warp[w][threadIdx.x] = 0;
       __syncthreads();
       const size_t i = base + (size_t)r * kSortThreads + threadIdx.x;
       const bool live = i < n;
-      uint32_t key = 0, digit = 0x100u + lane;  // dead lanes get digits nobody else has
-      if (live) {
-        key = sort_key_at(keys_in, ns_id, NS, i);
-        digit = (key >> shift) & 0xFFu;
-      }
+      const uint32_t key = keys[r];
+      uint32_t digit = 0x100u + lane;  // dead lanes get digits nobody else has
+      if (live) digit = (key >> shift) & 0xFFu;
       const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit);
       const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
       if (live && rank == 0) s_warp[warp][digit] = __popc(peers);  // the first lane of each group publishes its size
@@ -207,20 +215,47 @@ k_rsort_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
       if (live) {
         const uint32_t pos = s_warp[warp][digit] + rank;
         s_key[pos] = key;
-        s_idx[pos] = idx_in ? idx_in[i] : (uint32_t)i;
+        s_idx[pos] = idxs[r];
         s_src[pos] = (unsigned short)(r * kSortThreads + threadIdx.x);
       }
       __syncthreads();
     }
-    for (uint32_t j = threadIdx.x; j < live_n; j += kSortThreads) {
-      const uint32_t key = s_key[j];
-      const uint32_t d = (key >> shift) & 0xFFu;
-      const uint32_t gpos = s_goff[d] + (j - s_lbase[d]);
-      keys_out[gpos] = key;
-      idx_out[gpos] = s_idx[j];
-      const size_t src = base + s_src[j];
-      for (int q = 0; q < P.R; ++q) P.out[q][gpos] = P.in[q][src];
-      if (P.mask_in) P.mask_out[gpos] = P.mask_in[src];
+    // write-out, kWB elements per thread at a time: all of a batch's payload loads are issued before its stores (the
+    // compiler cannot hoist them itself, input and output columns may alias as far as it knows)
+    constexpr int kWB = 8;
+    for (uint32_t j0 = threadIdx.x; j0 < live_n; j0 += kSortThreads * kWB) {
+      uint32_t gpos[kWB];
+      size_t src[kWB];
+      bool on[kWB];
+#pragma unroll
+      for (int u = 0; u < kWB; ++u) {
+        const uint32_t j = j0 + (uint32_t)u * kSortThreads;
+        on[u] = j < live_n;
+        const uint32_t key = on[u] ? s_key[j] : 0u;
+        const uint32_t d = (key >> shift) & 0xFFu;
+        gpos[u] = on[u] ? s_goff[d] + (j - s_lbase[d]) : 0u;
+        src[u] = base + (on[u] ? s_src[j] : 0u);
+        if (on[u]) {
+          keys_out[gpos[u]] = key;
+          idx_out[gpos[u]] = s_idx[j];
+        }
+      }
+      for (int q = 0; q < P.R; ++q) {
+        long long v[kWB];
+#pragma unroll
+        for (int u = 0; u < kWB; ++u) v[u] = on[u] ? P.in[q][src[u]] : 0;
+#pragma unroll
+        for (int u = 0; u < kWB; ++u)
+          if (on[u]) P.out[q][gpos[u]] = v[u];
+      }
+      if (P.mask_in) {
+        uint8_t m[kWB];
+#pragma unroll
+        for (int u = 0; u < kWB; ++u) m[u] = on[u] ? P.mask_in[src[u]] : (uint8_t)0;
+#pragma unroll
+        for (int u = 0; u < kWB; ++u)
+          if (on[u]) P.mask_out[gpos[u]] = m[u];
+      }
     }
     __syncthreads();
   }
