@@ -297,6 +297,74 @@ def _median_ms(torch, fn, reps, warm=2):
     return ts[len(ts) // 2]
 
 
+def c2_record(torch, bgc, eng, oracle, Q):
+    """BASELINE.json configs[1] under the driver's clock: 2^20 pods x 1e4 namespaces, uniform, R=2 (gpu, cpu), one
+    K1+K2 step on device-resident columns.  20 MB of input: L2-resident and launch-bound, so the step is timed two
+    ways — launched call by call through the C ABI, and replayed from a CUDA graph captured around the same calls
+    (four nodes: clear, K1, headroom rebuild, K2)."""
+    from workloads import KINDS, UNITS, make_hard
+    n, NS, R, seed = 1 << 20, 10_000, 2, SEED["c2"]
+    a, b = Q.scramble_params(NS)
+    run_ns = torch.empty(n, dtype=torch.int32, device="cuda"); run_req = [torch.empty(n, dtype=torch.int64, device="cuda") for _ in range(R)]
+    c_ns = torch.empty(n, dtype=torch.int32, device="cuda"); c_req = [torch.empty(n, dtype=torch.int64, device="cuda") for _ in range(R)]
+    v = torch.empty(n, dtype=torch.uint8, device="cuda")
+    eng.synth_pods_dev(bgc.synth_params(seed, 0, NS, 0, 0, n, a, b, None, KINDS[R]), 0, n, run_ns, run_req)
+    eng.synth_pods_dev(bgc.synth_params(seed, 1, NS, 0, 0, n, a, b, None, KINDS[R]), 0, n, c_ns, c_req)
+    eng.quota_table_set(np.zeros((R, NS), np.int64), np.zeros(NS, np.uint8), UNITS[R])
+    eng.usage_reduce_dev(run_ns, run_req, 0)
+    torch.cuda.synchronize()
+    used0 = eng.usage_get()
+    hard, hm = make_hard(used0, seed)
+    eng.quota_table_set(hard, hm, UNITS[R])
+
+    def step():
+        eng.usage_reduce_dev(run_ns, run_req, 0)
+        eng.quota_eval_dev(c_ns, c_req, None, v)
+    for _ in range(5):
+        step()
+    torch.cuda.synchronize()
+    reps = 200
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        step()
+    e1.record(); torch.cuda.synchronize()
+    eager_us = e0.elapsed_time(e1) / reps * 1e3
+    rns, rreq, _ = oracle.gen_fill(oracle.gen_params(seed, 0, NS, 0, 0, n, a, b, None, KINDS[R]), 0, n, threads=8)
+    cns, creq, _ = oracle.gen_fill(oracle.gen_params(seed, 1, NS, 0, 0, n, a, b, None, KINDS[R]), 0, n, threads=8)
+    want_u = oracle.usage_reduce(rns, rreq, NS, threads=8)
+    want_v = oracle.quota_eval(cns, creq, None, NS, want_u, hard, hm, 0b10, threads=8)
+    ok = bool(np.array_equal(eng.usage_get(), want_u)) and bool(np.array_equal(v.cpu().numpy(), want_v))
+    graph_us = None
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            eng.use_torch_stream()
+            step()                                   # every kernel already loaded and configured before capture
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                step()
+            for _ in range(5):
+                g.replay()
+            side.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(side)
+            for _ in range(reps):
+                g.replay()
+            e1.record(side); side.synchronize()
+            graph_us = e0.elapsed_time(e1) / reps * 1e3
+            ok = ok and bool(np.array_equal(v.cpu().numpy(), want_v))
+    except Exception as e:  # noqa: BLE001
+        graph_us = f"capture failed: {type(e).__name__}: {e}"[:200]
+    finally:
+        eng.use_torch_stream()
+    return {"config": "C2: 2^20 pods x 1e4 namespaces, uniform, R=2 (gpu, cpu); 21 MB per step, L2-resident, launch-bound",
+            "step_us_call_by_call": eager_us, "pods_per_s_call_by_call": n / eager_us * 1e6,
+            "step_us_cuda_graph_replay": graph_us, "pods_per_s_cuda_graph_replay": (n / graph_us * 1e6) if isinstance(graph_us, float) else None,
+            "verified_vs_oracle": ok, "verified_scope": "full usage table and every verdict vs the oracle"}
+
+
 def k0_record(torch, bgc, eng, oracle, peak):
     """Row A1 under the driver's clock: 2^30 requests through bgc_policy_eval_dev (5 B per request: 3 read, 2 written)."""
     m = 1 << 30
@@ -885,7 +953,8 @@ def main():
             subs["compact_columns_device_resident"] = {"error": f"{type(e).__name__}: {e}"[:300]}
         torch.cuda.empty_cache()
     if rank == 0 and world == 1 and not args.no_sub:
-        for name, fn in (("k0", lambda: k0_record(torch, bgc, eng, oracle, peak)),
+        for name, fn in (("c2", lambda: c2_record(torch, bgc, eng, oracle, Q)),
+                         ("k0", lambda: k0_record(torch, bgc, eng, oracle, peak)),
                          ("k3", lambda: k3_record(torch, bgc, eng, oracle, Q, wl, seed, peak)),
                          ("crossover", lambda: crossover_record(torch, bgc, eng, oracle, Q, SEED["c2"] + 2, cpu_info()[0]))):
             try:
