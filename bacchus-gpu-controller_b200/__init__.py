@@ -49,7 +49,7 @@ EXPORTS = [
     "bgc_split_groups", "bgc_flatten_requests", "bgc_reason_message", "bgc_mutate_batch",
     "bgc_render_patch", "bgc_parse_quantity", "bgc_nsmap_create", "bgc_nsmap_destroy",
     "bgc_nsmap_intern", "bgc_nsmap_lookup", "bgc_nsmap_size", "bgc_nsmap_name", "bgc_flatten_pods",
-    "bgc_hard_from_sheet_row", "bgc_usage_reduce_static_dev", "bgc_admit_greedy", "bgc_admit_greedy_dev", "bgc_admit_greedy16", "bgc_admit_greedy16_dev",
+    "bgc_hard_from_sheet_row", "bgc_compact_plan", "bgc_compact_column", "bgc_compact_ns_ids", "bgc_usage_reduce_static_dev", "bgc_admit_greedy", "bgc_admit_greedy_dev", "bgc_admit_greedy16", "bgc_admit_greedy16_dev",
     "bgc_sheet_infer_header", "bgc_sheet_parse_csv", "bgc_sheet_destroy", "bgc_sheet_row_count", "bgc_sheet_skipped_rows",
     "bgc_sheet_get_row", "bgc_sheet_match", "bgc_sheet_row_quota",
     "bgc_review_parse", "bgc_review_destroy", "bgc_review_has_request", "bgc_review_uid", "bgc_review_kind",

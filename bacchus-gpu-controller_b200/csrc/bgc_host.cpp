@@ -4,6 +4,7 @@
 // 312-386) become the (op, flags) columns K0 consumes.  Row A5: pod specs become the
 // (ns_id, req[r], req_mask) columns K1/K2 consume.  Plain C++17, no CUDA in this file; the only
 // device work is reached through the C ABI (bgc_policy_eval).
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -289,6 +290,62 @@ long bgc_render_patch(const bgc_admission_config* cfg, const bgc_admission_reque
 }
 
 // ------------------------------------------------------------------------------ row A5
+// ---- compact columns (what the narrow-column entry points take) ------------------------------------
+int bgc_compact_plan(const int64_t* col, size_t n, uint8_t* type_out, uint8_t* shift_out) {
+  if ((!col && n) || !type_out || !shift_out) return BGC_E_BADARG;
+  uint64_t any = 0;
+  int64_t lo = 0, hi = 0;
+#pragma omp parallel for schedule(static) reduction(| : any) reduction(min : lo) reduction(max : hi) if (n >= (1u << 16))
+  for (long long i = 0; i < (long long)n; ++i) {
+    any |= (uint64_t)col[i];
+    lo = col[i] < lo ? col[i] : lo;
+    hi = col[i] > hi ? col[i] : hi;
+  }
+  int shift = any ? __builtin_ctzll(any) : 0;
+  // (arithmetic shift keeps the sign: value >> shift is exact because the low bits are zero)
+  const int64_t slo = lo >> shift, shi = hi >> shift;
+  uint8_t type;
+  if (slo >= 0 && shi <= 0xFF) type = BGC_T_U8;
+  else if (slo >= 0 && shi <= 0xFFFF) type = BGC_T_U16;
+  else if (slo >= 0 && shi <= 0xFFFFFFFFll) type = BGC_T_U32;
+  else if (slo >= INT32_MIN && shi <= INT32_MAX) type = BGC_T_I32;
+  else { type = BGC_T_I64; shift = 0; }
+  *type_out = type;
+  *shift_out = (uint8_t)shift;
+  return BGC_OK;
+}
+
+int bgc_compact_column(const int64_t* col, size_t n, uint8_t type, uint8_t shift, void* out) {
+  if ((n && (!col || !out)) || type > BGC_T_I32 || shift > 63) return BGC_E_BADARG;
+  int bad = 0;
+#pragma omp parallel for schedule(static) reduction(| : bad) if (n >= (1u << 16))
+  for (long long i = 0; i < (long long)n; ++i) {
+    const int64_t v = col[i], x = v >> shift;
+    int64_t back;
+    switch (type) {
+      case BGC_T_U8: static_cast<uint8_t*>(out)[i] = (uint8_t)x; back = (int64_t)(uint8_t)x; break;
+      case BGC_T_U16: static_cast<uint16_t*>(out)[i] = (uint16_t)x; back = (int64_t)(uint16_t)x; break;
+      case BGC_T_U32: static_cast<uint32_t*>(out)[i] = (uint32_t)x; back = (int64_t)(uint32_t)x; break;
+      case BGC_T_I32: static_cast<int32_t*>(out)[i] = (int32_t)x; back = (int64_t)(int32_t)x; break;
+      default: static_cast<int64_t*>(out)[i] = x; back = x; break;
+    }
+    bad |= (int64_t)((uint64_t)back << shift) != v;
+  }
+  return bad ? BGC_E_BADARG : BGC_OK;
+}
+
+int bgc_compact_ns_ids(const uint32_t* ns_id, size_t n, uint32_t ns_count, void* out) {
+  if (n && (!ns_id || !out)) return BGC_E_BADARG;
+  if (ns_count > 65535) {
+    if (out != ns_id) std::memcpy(out, ns_id, n * 4);
+    return BGC_T_U32;
+  }
+#pragma omp parallel for schedule(static) if (n >= (1u << 16))
+  for (long long i = 0; i < (long long)n; ++i)
+    static_cast<uint16_t*>(out)[i] = ns_id[i] < ns_count ? (uint16_t)ns_id[i] : (uint16_t)0xFFFF;  // any id >= ns_count is "unknown"
+  return BGC_T_U16;
+}
+
 int bgc_parse_quantity(const char* s, int unit, int64_t* out) {
   if (!s || !out) return BGC_E_BADARG;
   const char* p = s;

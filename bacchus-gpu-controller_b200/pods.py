@@ -171,3 +171,32 @@ def hard_from_sheet_row(cpu: int, memory_gi: int, gpu: int, storage_gi: int, mig
     if rc != OK:
         raise BgcError(rc, "bgc_hard_from_sheet_row: unknown quota key")
     return hard, unit
+
+
+# ---- compact columns for the narrow-column entry points (bgc_compact_*, include/bgc_host.h) -----------------
+lib.bgc_compact_plan.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]
+lib.bgc_compact_column.argtypes = [C.c_void_p, C.c_size_t, C.c_uint8, C.c_uint8, C.c_void_p]
+lib.bgc_compact_ns_ids.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p]
+_NP_OF_T = {0: np.int64, 1: np.uint32, 2: np.uint16, 3: np.uint8, 4: np.int32}
+
+
+def compact_columns(ns_id: np.ndarray, req: Sequence[np.ndarray], ns_count: int):
+    """int64 columns (what flatten_pods returns) -> (ns ids u16/u32, [narrow columns], [shifts]) for
+    Engine.usage_reduce_typed / quota_eval_typed: per column the largest common shift and the narrowest exact type."""
+    n = ns_id.shape[0]
+    cols, shifts = [], []
+    for c in req:
+        c = np.ascontiguousarray(c, dtype=np.int64)
+        t, sh = C.c_uint8(), C.c_uint8()
+        if lib.bgc_compact_plan(C.c_void_p(c.ctypes.data), n, C.byref(t), C.byref(sh)) != OK:
+            raise BgcError(-1, "bgc_compact_plan")
+        out = np.empty(n, _NP_OF_T[t.value])
+        if lib.bgc_compact_column(C.c_void_p(c.ctypes.data), n, t, sh, C.c_void_p(out.ctypes.data)) != OK:
+            raise BgcError(-1, "bgc_compact_column: a value does not fit the planned representation")
+        cols.append(out); shifts.append(int(sh.value))
+    ns_id = np.ascontiguousarray(ns_id, dtype=np.uint32)
+    if ns_count > 65535:          # ids stay u32
+        return ns_id, cols, shifts
+    ns16 = np.empty(n, np.uint16)
+    lib.bgc_compact_ns_ids(C.c_void_p(ns_id.ctypes.data), n, ns_count, C.c_void_p(ns16.ctypes.data))
+    return ns16, cols, shifts

@@ -143,6 +143,19 @@ int bgc_flatten_pods(const bgc_pod_spec *pods, size_t n, const char *const *quot
                      const uint8_t *unit, uint32_t R, bgc_nsmap *map, int intern, uint32_t *ns_id,
                      int64_t *const *req, uint8_t *req_mask, size_t *n_out);
 
+/* ---- compact columns for the narrow-column entry points (bgc_*_typed, bgc.h) -----------------------
+ * No counterpart in the reference.  The columns bgc_flatten_pods emits are int64; what crosses PCIe should not
+ * be.  bgc_compact_plan picks, for one column, the largest shift (trailing zero bits common to every value, so
+ * memory quantities written as <n>Mi / <n>Gi — src/synchronizer.rs:257,265 — lose 20-30 bits) and then the
+ * narrowest element type (BGC_T_U8 / U16 / U32 for non-negative values, BGC_T_I32, else BGC_T_I64 with shift 0)
+ * that represents every value exactly; bgc_compact_column writes the column in a given representation and
+ * returns BGC_E_BADARG if some value would not survive (int64)element << shift.  An all-zero column is U8 / 0. */
+int bgc_compact_plan(const int64_t *col, size_t n, uint8_t *type_out, uint8_t *shift_out);
+int bgc_compact_column(const int64_t *col, size_t n, uint8_t type, uint8_t shift, void *out);
+/* the same for namespace ids: u16 when every id (including the unknown-namespace marker 0xFFFFFFFF, which becomes
+ * 0xFFFF) stays distinguishable, i.e. ns_count <= 65535; returns the element type chosen (BGC_T_U16 / BGC_T_U32) */
+int bgc_compact_ns_ids(const uint32_t *ns_id, size_t n, uint32_t ns_count, void *out);
+
 /* the `hard` values the reference's synchronizer writes for one sheet row
  * (src/synchronizer.rs:249-281), in canonical units, for the given quota keys:
  * cpu → cpu_request*1000 millicores, memory/storage → <n>Gi bytes, gpu/mig → count.

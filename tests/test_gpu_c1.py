@@ -157,3 +157,36 @@ def test_pod_reviews_wire_to_wire_on_the_device(bgc, engine, oracle, wide):
         resp = json.loads(outs[i])["response"]
         assert resp["allowed"] is False and resp["status"]["reason"] == "InvalidRequest" and resp["uid"] == ""
     assert 0.02 < float(np.mean(want != 0)) < 0.999
+
+
+def test_c1_pods_through_compact_columns(bgc, engine, oracle):
+    """The whole host-to-device route a caller with pod objects would take for the narrow-column ABI: pod JSON ->
+    bgc_flatten_pods (int64 columns) -> bgc_compact_plan/column (narrowest exact representation) ->
+    bgc_usage_reduce_typed / bgc_quota_eval_typed; results equal the int64 entry points and the oracle."""
+    nss = c1_namespaces()
+    m = bgc.pods.NamespaceMap()
+    for ns in nss:
+        m.intern(ns["name"])
+    R = len(C1_KEYS)
+    hard = np.zeros((R, len(nss)), np.int64)
+    hm = np.zeros(len(nss), np.uint8)
+    for i, ns in enumerate(nss):
+        h, unit = bgc.pods.hard_from_sheet_row(ns["cpu"], ns["memory"], ns["gpu"], ns["storage"], ns["mig"], C1_KEYS)
+        hard[:, i] = h
+        hm[i] = (1 << R) - 1 if ns["has_quota"] else 0
+    engine.quota_table_set(hard, hm, unit)
+    r_ns, r_req, _, _ = bgc.pods.flatten_pods(c1_pods(10_000, nss, running=True), C1_KEYS, m, intern=False)
+    cands = c1_pods(10_000, nss, running=False)
+    cands[3]["metadata"]["namespace"] = "nowhere"
+    c_ns, c_req, c_mask, _ = bgc.pods.flatten_pods(cands, C1_KEYS, m, intern=False)
+    rn, rc, rs = bgc.pods.compact_columns(r_ns, r_req, len(nss))
+    cn, cc, cs = bgc.pods.compact_columns(c_ns, c_req, len(nss))
+    assert rn.dtype == np.uint16 and sum(c.dtype.itemsize for c in rc) < 8 * R     # narrower than int64 columns
+    used = engine.usage_reduce(r_ns, r_req)
+    assert np.array_equal(engine.usage_reduce_typed(rn, rc, rs), used)
+    assert np.array_equal(used, oracle.usage_reduce(r_ns, r_req, len(nss)))
+    want = engine.quota_eval(c_ns, c_req, c_mask)
+    got = engine.quota_eval_typed(cn, cc, cs, c_mask)
+    assert np.array_equal(got, want) and got[3] == bgc.VERDICT_BAD_NS
+    cm = sum(1 << r for r, u in enumerate(unit) if u)
+    assert np.array_equal(got, oracle.quota_eval(c_ns, c_req, c_mask, len(nss), used, hard, hm, cm))

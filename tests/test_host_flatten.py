@@ -207,3 +207,38 @@ def test_parse_quantity_property_vs_exact_fractions(bgc):
     # decimal exponents
     for text, unit, want in [("1e3", 0, 1000), ("12e-1", 0, 2), ("5e-1", 1, 500), ("1.5e3", 2, 1500), ("25e-4", 1, 3)]:
         assert bgc.pods.parse_quantity(text, unit) == want
+
+
+def test_compact_columns_plan_and_round_trip(bgc, oracle):
+    """bgc_compact_plan / bgc_compact_column / bgc_compact_ns_ids (the host step between the flattener and the
+    narrow-column entry points): the narrowest exact type and the largest common shift per column, lossless round
+    trip, and the oracle's typed forms decide on the compact columns what they decide on the int64 ones."""
+    rng = np.random.default_rng(3)
+    n, NS = 100_003, 5_000
+    cols = [rng.choice(np.array([0, 1, 2, 4, 8], np.int64), n),                     # gpu counts      -> u8, shift 0
+            250 << rng.integers(0, 7, n).astype(np.int64),                          # cpu millicores  -> u16 << 1 (250 = 125 * 2)
+            np.int64(1) << rng.integers(28, 37, n).astype(np.int64),                # memory bytes    -> u16 << 28
+            rng.integers(0, 1 << 31, n).astype(np.int64) * 3,                       #                 -> i64 or u32
+            rng.integers(-1000, 1000, n).astype(np.int64) << 4,                     # negatives       -> i32 << 4
+            np.zeros(n, np.int64),                                                  # all zero        -> u8, 0
+            rng.integers(-(1 << 62), 1 << 62, n).astype(np.int64) | 1]              # full range, odd -> i64, 0
+    ns = rng.integers(0, NS, n).astype(np.uint32)
+    ns[::97] = 0xFFFFFFFF
+    ns[1::101] = NS + 3
+    ns2, ccols, shifts = bgc.pods.compact_columns(ns, cols, NS)
+    want = [(np.uint8, 0), (np.uint16, 1), (np.uint16, 28), None, (np.int32, 4), (np.uint8, 0), (np.int64, 0)]
+    for c, d, sh, w in zip(cols, ccols, shifts, want):
+        assert np.array_equal(d.astype(np.int64) << sh, c)
+        if w is not None:
+            assert (d.dtype, sh) == (np.dtype(w[0]), w[1]), (d.dtype, sh, w)
+    assert ccols[3].dtype in (np.dtype(np.uint32), np.dtype(np.int64))
+    assert ns2.dtype == np.uint16 and np.array_equal(ns2 == 0xFFFF, ns >= NS) and np.array_equal(ns2[ns < NS], ns[ns < NS])
+    assert bgc.pods.compact_columns(ns, cols[:1], 70_000)[0].dtype == np.uint32
+    # a representation that does not hold the values is refused, not silently truncated
+    import ctypes as C
+    out = np.empty(n, np.uint8)
+    assert bgc.lib.bgc_compact_column(C.c_void_p(cols[2].ctypes.data), n, 3, 20, C.c_void_p(out.ctypes.data)) == bgc.E_BADARG
+    R = 4
+    used_a = oracle.usage_reduce(np.where(ns < NS, ns, 0xFFFFFFFF).astype(np.uint32), cols[:R], NS)
+    used_b = oracle.usage_reduce_typed(ns2, ccols[:R], shifts[:R], NS)
+    assert np.array_equal(used_a, used_b)
