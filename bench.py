@@ -620,13 +620,23 @@ def c5_record(torch, dist, bgc, eng, oracle, Q, rank, world, steps, n_total, NS,
         tns, treq, _ = oracle.gen_fill(p1, hi - T2, T2, threads=8)
         tv = oracle.quota_eval(tns, treq, None, NS, used_now, hard, hm, cm, threads=8)
         ok = ok and oracle.checksum_u8(tv, 0) == eng.checksum_u8_dev(d_v[m - T2:], 0, T2)
+        if verify_full:   # the summed table against the oracle streamed over the WHOLE global running set
+            p0 = oracle.gen_params(seed, 0, NS, 1, 0, n_total, a, b, cdf, KINDS[R])
+            acc = np.zeros((R, NS), np.int64)
+            cores_v = os.cpu_count() or 1
+            for lo2 in range(0, n_total, 1 << 24):
+                rns, rreq, _ = oracle.gen_fill(p0, lo2, min(1 << 24, n_total - lo2), threads=cores_v)
+                with np.errstate(over="ignore"):
+                    acc += oracle.usage_reduce(rns, rreq, NS, threads=cores_v)
+            ok = ok and bool(np.array_equal(acc, used_now))
         rec["index_allreduce"] = {
             "sharding": f"rank g takes pods [g*n/G, (g+1)*n/G) of the same stream; every rank reduces into a full {R}x{NS} table; "
                         f"ONE NCCL int64 all-reduce of {8 * R * NS} bytes per step; each rank evaluates its own slice",
             "pods_per_rank": gather_counts(m), "imbalance_max_over_mean": 1.0,
             "ms_per_step": tot, "k1_plus_exchange_ms": k1, "k2_ms": k2, "allreduce_alone_ms": ar_ms, "pods_per_s": n_total / (tot * 1e-3),
             "k1_variant": eng.last_k1_variant(), "verified_vs_oracle": all_ok(ok),
-            "verified_scope": f"summed usage table stable across steps + verdict checksum of the last {T2} candidates of each slice vs the oracle on the global usage",
+            "verified_scope": ("summed usage table vs the oracle streamed over the whole global stream + " if verify_full else "summed usage table stable across steps + ")
+                              + f"verdict checksum of the last {T2} candidates of each slice vs the oracle on the global usage",
         }
         del r_ns, r_req, c_ns, c_req, d_v, d_used
         torch.cuda.empty_cache()
