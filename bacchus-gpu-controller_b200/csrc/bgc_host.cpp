@@ -4,6 +4,7 @@
 // 312-386) become the (op, flags) columns K0 consumes.  Row A5: pod specs become the
 // (ns_id, req[r], req_mask) columns K1/K2 consume.  Plain C++17, no CUDA in this file; the only
 // device work is reached through the C ABI (bgc_policy_eval).
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -201,7 +202,8 @@ int bgc_flatten_requests(const bgc_admission_config* cfg, const bgc_admission_re
                          uint8_t* op, uint16_t* flags) {
   if (!cfg || !cfg->oidc_username_prefix || (n && (!reqs || !op || !flags))) return BGC_E_BADARG;
   const std::string_view prefix(cfg->oidc_username_prefix);
-  for (size_t i = 0; i < n; ++i) {
+#pragma omp parallel for schedule(static) if (n >= 4096)
+  for (long long i = 0; i < (long long)n; ++i) {
     const bgc_admission_request& q = reqs[i];
     unsigned f = 0;
     NameParts who{false, {}};
@@ -1282,3 +1284,85 @@ int bgc_plan_item(const bgc_plan* p, size_t i, const char** kind, const char** n
 int bgc_plan_requeue_seconds(int failed) { return failed ? 3 : 30; }  // src/controller.rs:154,174
 
 }  // extern "C"
+
+// ---- the batched mutate_handler, wire bytes to wire bytes (reference src/admission.rs:184-204) ----------------
+extern "C" int bgc_handle_reviews(bgc_ctx* ctx, const bgc_admission_config* cfg, const char* const* bodies, const size_t* body_len,
+                       size_t n, char* out, size_t out_cap, size_t* out_off, uint64_t* stage_ns) {
+  if (!ctx || !cfg || (n && (!bodies || !body_len)) || !out_off || (!out && out_cap)) return BGC_E_BADARG;
+  using clk = std::chrono::steady_clock;
+  auto ns_since = [](clk::time_point t0) { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - t0).count(); };
+  auto t0 = clk::now();
+  std::vector<bgc_review*> rv(n, nullptr);
+#pragma omp parallel for schedule(dynamic, 64) if (n >= 256)
+  for (long long i = 0; i < (long long)n; ++i) rv[i] = bodies[i] ? bgc_review_parse(bodies[i], body_len[i], nullptr, 0) : nullptr;
+  const uint64_t t_parse = ns_since(t0);
+  t0 = clk::now();
+  std::vector<size_t> live;
+  live.reserve(n);
+  for (size_t i = 0; i < n; ++i)
+    if (rv[i] && bgc_review_has_request(rv[i])) live.push_back(i);
+  std::vector<bgc_admission_request> reqs(live.size());
+  std::vector<bgc_admission_response> resp(live.size());
+#pragma omp parallel for schedule(static) if (live.size() >= 256)
+  for (long long k = 0; k < (long long)live.size(); ++k) bgc_review_request(rv[live[k]], &reqs[k]);
+  int rc = live.empty() ? BGC_OK : bgc_mutate_batch(ctx, cfg, reqs.data(), live.size(), resp.data());
+  const uint64_t t_decide = ns_since(t0);
+  uint64_t t_patch = 0, t_render = 0;
+  int bad_render = 0;
+  std::vector<std::string> text(n);
+  if (rc == BGC_OK) {
+    t0 = clk::now();
+    std::vector<std::string> patch(live.size());
+#pragma omp parallel for schedule(static) if (live.size() >= 256)
+    for (long long k = 0; k < (long long)live.size(); ++k)
+      if (resp[k].patch_mask) {
+        std::string buf(1024, '\0');
+        long m;
+        while ((m = bgc_render_patch(cfg, &reqs[k], resp[k].patch_mask, &buf[0], buf.size())) == BGC_E_BADARG && buf.size() < (1u << 24))
+          buf.resize(buf.size() * 4);
+        if (m > 0) patch[k].assign(buf.data(), (size_t)m);
+        else
+#pragma omp atomic write
+          bad_render = 1;  // a patch that was asked for and did not come out fails the call, never a response without it
+      }
+    t_patch = ns_since(t0);
+    t0 = clk::now();
+    std::vector<long long> slot(n, -1);
+    for (size_t k = 0; k < live.size(); ++k) slot[live[k]] = (long long)k;
+#pragma omp parallel for schedule(static) if (n >= 256)
+    for (long long i = 0; i < (long long)n; ++i) {
+      std::string buf(1024, '\0');
+      long m;
+      for (;;) {
+        if (slot[i] >= 0) {
+          const size_t k = (size_t)slot[i];
+          m = bgc_render_review_response(bgc_review_uid(rv[i]), &resp[k], nullptr, patch[k].empty() ? nullptr : patch[k].c_str(), &buf[0], buf.size());
+        } else {
+          const bgc_admission_response bad = {0, BGC_INVALID, 0, 0, nullptr};
+          m = bgc_render_review_response("", &bad, rv[i] ? "invalid request: AdmissionReview carries no request" : "malformed AdmissionReview",
+                                         nullptr, &buf[0], buf.size());
+        }
+        if (m != BGC_E_BADARG || buf.size() >= (1u << 24)) break;
+        buf.resize(buf.size() * 4);
+      }
+      if (m > 0) text[i].assign(buf.data(), (size_t)m);
+    }
+    t_render = ns_since(t0);
+  }
+  t0 = clk::now();
+#pragma omp parallel for schedule(dynamic, 64) if (n >= 256)
+  for (long long i = 0; i < (long long)n; ++i) bgc_review_destroy(rv[i]);  // the parsed trees: as many frees as the parse made allocations
+  if (rc) return rc;
+  if (bad_render) return BGC_E_BADARG;
+  size_t need = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (text[i].empty()) return BGC_E_BADARG;  // a response did not fit the render buffer
+    out_off[i] = need;
+    need += text[i].size() + 1;
+  }
+  out_off[n] = need;
+  if (need > out_cap) return BGC_E_BADARG;
+  for (size_t i = 0; i < n; ++i) std::memcpy(out + out_off[i], text[i].c_str(), text[i].size() + 1);
+  if (stage_ns) { stage_ns[0] = t_parse; stage_ns[1] = t_decide; stage_ns[2] = t_patch; stage_ns[3] = t_render; stage_ns[4] = ns_since(t0); }
+  return BGC_OK;
+}

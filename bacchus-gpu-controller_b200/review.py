@@ -24,6 +24,9 @@ lib.bgc_review_kind.argtypes = [C.c_void_p]
 lib.bgc_review_request.argtypes = [C.c_void_p, C.POINTER(_CRequest)]
 lib.bgc_review_pod.argtypes = [C.c_void_p, C.POINTER(_Pod)]
 lib.bgc_render_review_response.restype = C.c_long
+lib.bgc_handle_reviews.restype = C.c_int
+lib.bgc_handle_reviews.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_size_t, C.c_char_p, C.c_size_t,
+                                   C.POINTER(C.c_size_t), C.POINTER(C.c_uint64)]
 lib.bgc_render_review_response.argtypes = [C.c_char_p, C.POINTER(_CResponse), C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]
 lib.bgc_render_patch.argtypes = [C.POINTER(_CConfig), C.POINTER(_CRequest), C.c_uint8, C.c_char_p, C.c_size_t]
 
@@ -101,10 +104,39 @@ def _invalid(message: str) -> str:
     return _render("", _CResponse(0, 3, 0, 0, None), message, None)
 
 
-def handle_reviews(engine: Engine, config: AdmissionConfig, bodies: Sequence[bytes | str]) -> list:
-    """Batched `mutate_handler`: one response JSON string per request body.  Reviews without a
-    `request` are answered `invalid` like src/admission.rs:189-197; everything else is flattened,
-    decided in one K0 launch, and rendered."""
+def handle_reviews(engine: Engine, config: AdmissionConfig, bodies: Sequence[bytes | str], stage_ms: dict | None = None) -> list:
+    """Batched `mutate_handler` (src/admission.rs:184-204): one response JSON string per request body, through
+    ONE C call (bgc_handle_reviews: parse, flatten, one K0 launch, render).  Reviews without a `request` and
+    bodies that do not parse are answered `invalid` on their own like :189-197.  `stage_ms`, when given, is
+    filled with the host time of the five stages."""
+    raw = [b.encode() if isinstance(b, str) else b for b in bodies]
+    n = len(raw)
+    if n == 0:
+        return []
+    blob = b"".join(raw)                                   # one buffer, pointers computed from the lengths
+    lens = np.fromiter(map(len, raw), np.uint64, n)
+    base = C.cast(C.c_char_p(blob), C.c_void_p).value or 0
+    ptrs = base + np.concatenate([np.zeros(1, np.uint64), np.cumsum(lens[:-1], dtype=np.uint64)])
+    cap = len(blob) // 2 + 768 * n + 64
+    off = np.zeros(n + 1, np.uint64)
+    stages = (C.c_uint64 * 5)()
+    cc, keep = config._c()
+    for _ in range(2):
+        buf = np.empty(cap, np.uint8)
+        rc = lib.bgc_handle_reviews(engine._h, C.byref(cc), ptrs.ctypes.data_as(C.POINTER(C.c_char_p)), lens.ctypes.data_as(C.POINTER(C.c_size_t)),
+                                    C.c_size_t(n), buf.ctypes.data_as(C.c_char_p), C.c_size_t(cap), off.ctypes.data_as(C.POINTER(C.c_size_t)), stages)
+        if rc == 0 or int(off[n]) <= cap:
+            break
+        cap = int(off[n])      # the call reported the size it needs
+    engine._ck(rc)
+    if stage_ms is not None:
+        stage_ms.update(zip(("parse", "flatten_decide", "patch", "render", "release_copy"), (s / 1e6 for s in stages)))
+    return buf[:int(off[n]) - 1].tobytes().decode().split("\0")   # responses are JSON text: no NUL inside one
+
+
+def handle_reviews_stepwise(engine: Engine, config: AdmissionConfig, bodies: Sequence[bytes | str]) -> list:
+    """The same handler spelled out call by call (bgc_review_parse → bgc_review_request → bgc_mutate_batch →
+    bgc_render_patch → bgc_render_review_response); kept for the tests that compare the two."""
     reviews = _parse_all(bodies)
     live = [i for i, r in enumerate(reviews) if r is not None and r.has_request]
     creqs = (_CRequest * max(1, len(live)))()

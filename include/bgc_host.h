@@ -187,6 +187,18 @@ int bgc_review_request(const bgc_review *r, bgc_admission_request *out);
  * object.metadata.namespace); pointers valid until bgc_review_destroy */
 int bgc_review_pod(const bgc_review *r, bgc_pod_spec *out);
 
+/* The batched mutate_handler (src/admission.rs:184-204) in ONE call, wire bytes to wire bytes: every body is parsed
+ * (OpenMP over the batch), the requests are flattened, decided in one K0 launch (bgc_mutate_batch) and rendered.
+ * A body that is not a well-formed AdmissionReview, or carries no `request`, is answered `invalid` on its own,
+ * as the reference's handler rejects only the offending request (:189-197).  The responses are written back to
+ * back into `out` (NUL-terminated each); out_off[i] = offset of response i, out_off[n] = bytes used.  Returns
+ * BGC_E_BADARG when `out` is too small (out_off[n] then holds the size needed).  stage_ns (optional, 5 values):
+ * host time of parse, flatten + decide, patch rendering, response rendering, and releasing the parsed trees +
+ * copying the responses out. */
+int bgc_handle_reviews(bgc_ctx *ctx, const bgc_admission_config *cfg, const char *const *bodies,
+                       const size_t *body_len, size_t n, char *out, size_t out_cap, size_t *out_off,
+                       uint64_t *stage_ns);
+
 /* AdmissionReview response text for one decision.  patch_json = bgc_render_patch output or NULL.
  * allow   → {"uid","allowed":true,"status":{}} (+ "patch": base64, "patchType":"JSONPatch")
  * deny    → allowed:false, status.message = the reference's literal

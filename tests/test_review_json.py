@@ -93,6 +93,36 @@ def test_wire_bytes_to_response_json(bgc, engine):
     assert last["allowed"] is False and last["status"]["reason"] == "InvalidRequest"
 
 
+@pytest.mark.gpu
+def test_one_call_handler_equals_the_stepwise_handler(bgc, engine):
+    """bgc_handle_reviews (one C call per batch) against the same handler spelled out call by call: byte-equal
+    responses, bad bodies answered on their own, an `out` that is too small reports the size it needs."""
+    import ctypes as C
+    cfg = bgc.admission.AdmissionConfig()
+    reviews = _reviews()
+    rng = np.random.default_rng(7)
+    bodies = [json.dumps(reviews[int(i)]) for i in rng.integers(0, len(reviews), 3000)]
+    long_name = "n" * 5000                      # a patch and a response longer than the first render buffers
+    big = json.loads(bodies[0]); big["request"]["object"] = {"metadata": {"name": long_name}, "spec": {"kube_username": None, "quota": None}}
+    big["request"]["operation"] = "CREATE"; big["request"]["userInfo"] = {"username": "oidc:" + long_name, "groups": []}
+    bodies[17] = json.dumps(big)
+    bodies[5] = "{"; bodies[6] = '{"kind":"AdmissionReview"}'; bodies[7] = ""; bodies[2999] = b'{"a":"\xff"}'
+    stages = {}
+    got = bgc.review.handle_reviews(engine, cfg, bodies, stage_ms=stages)
+    want = bgc.review.handle_reviews_stepwise(engine, cfg, bodies)
+    assert got == want
+    assert set(stages) == {"parse", "flatten_decide", "patch", "render", "release_copy"} and all(v >= 0 for v in stages.values())
+    assert bgc.review.handle_reviews(engine, cfg, []) == []
+    assert bgc.review.handle_reviews(engine, cfg, bodies[:3]) == want[:3]       # below the OpenMP threshold
+    raw = [b.encode() if isinstance(b, str) else b for b in bodies[:10]]
+    arr = (C.c_char_p * 10)(*raw); lens = (C.c_size_t * 10)(*[len(b) for b in raw]); off = (C.c_size_t * 11)()
+    cc, keep = cfg._c()
+    small = C.create_string_buffer(16)
+    assert bgc.lib.bgc_handle_reviews(engine._h, C.byref(cc), arr, lens, 10, small, 16, off, None) == bgc.E_BADARG
+    assert off[10] == sum(len(w.encode()) + 1 for w in want[:10])
+    assert bgc.lib.bgc_handle_reviews(None, C.byref(cc), arr, lens, 10, small, 16, off, None) == bgc.E_BADARG
+
+
 def test_pod_reviews_wire_to_wire_with_a_stand_in_engine(bgc, oracle):
     """`review.handle_pod_reviews` composes parse -> flatten -> K2 -> render.  K2 itself is covered by the
     GPU tests; here a stand-in engine whose quota_eval is the oracle lets the composition run on CPU."""

@@ -75,13 +75,18 @@ def main():
     code, pm = eng.policy_eval(op, flags)
     rc, rp = oracle.policy_bits(op, flags)
     same = bool(np.array_equal(code, rc) and np.array_equal(pm, rp))
-    t_e2e_gpu = med(lambda: bgc.review.handle_reviews(eng, cfg, bodies), 5)
+    t_e2e_gpu = med(lambda: bgc.review.handle_reviews(eng, cfg, bodies), 9)
+    t_e2e_step = med(lambda: bgc.review.handle_reviews_stepwise(eng, cfg, bodies), 5)
+    one_call = {}
+    bgc.review.handle_reviews(eng, cfg, bodies, stage_ms=one_call)
     out["userbootstrap_reviews"] = {
         "wire_bytes": wire_bytes, "gpu_equals_cpu": same,
         "stage_ms": {"parse (C++ parser, one ctypes call per body)": t_parse * 1e3, "flatten strings -> predicate bits (C++, one call)": t_flatten * 1e3,
                      "decide GPU: bgc_policy_eval from host memory (copies, K0 launch, sync)": t_gpu * 1e3,
                      "decide CPU: policy_ref_bits_batch, 1 thread": t_cpu1 * 1e3, f"decide CPU: policy_ref_bits_batch, {cores} threads": t_cpuN * 1e3},
-        "wire_to_wire_ms_gpu_arm (review.handle_reviews: parse + flatten + K0 + patch + render, Python glue included)": t_e2e_gpu * 1e3,
+        "wire_to_wire_ms_gpu_arm (review.handle_reviews = ONE C call, bgc_handle_reviews: parse + flatten + K0 + patch + render; ctypes marshalling of the bodies included)": t_e2e_gpu * 1e3,
+        "one_call_stage_ms (host clock inside bgc_handle_reviews)": one_call,
+        "wire_to_wire_ms_call_by_call (review.handle_reviews_stepwise: the same five C calls made from Python per body)": t_e2e_step * 1e3,
         "reviews_per_s_wire_to_wire_gpu_arm": n / t_e2e_gpu,
         "decide_stage_reviews_per_s": {"gpu": n / t_gpu, "cpu_1_thread": n / t_cpu1, "cpu_all": n / t_cpuN},
         "who_wins_the_decide_stage": "CPU" if min(t_cpu1, t_cpuN) < t_gpu else "GPU",
