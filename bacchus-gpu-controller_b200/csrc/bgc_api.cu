@@ -87,6 +87,12 @@ struct bgc_ctx {
   size_t gh_cap = 0;
   int gh_R = 0;
   size_t g_cap = 0, g_hist_cap = 0, g_seg_cap = 0;
+  // long segments of the greedy walk, cut into chained tiles (bgc_k3.cuh): tile table and descriptors
+  uint32_t *g_tile_base = nullptr, *g_tile_li = nullptr, *g_ticket_tile = nullptr, *g_long = nullptr, *g_chain_status = nullptr;
+  long long *g_chain_agg = nullptr, *g_chain_agg2 = nullptr, *g_chain_exact = nullptr;
+  size_t g_tile_base_cap = 0, g_chain_cap = 0;
+  int g_chain_R = 0;
+  int k3_long = -1;  // -1: read BGC_K3_LONG once (chain | team); 0 chain, 1 team
   // latency path: small host batches are read by the kernel straight over PCIe (zero-copy) from
   // the caller's pinned buffers, or from this pinned, device-mapped staging area
   uint8_t* zc_host = nullptr;
@@ -694,6 +700,7 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   cudaFreeHost(ctx->bounce[0]); cudaFreeHost(ctx->bounce[1]);
   cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order);
   cudaFree(ctx->g_seg); cudaFree(ctx->g_hist); cudaFree(ctx->g_mask); cudaFree(ctx->g_mask2);
+  cudaFree(ctx->g_tile_base); cudaFree(ctx->g_tile_li); cudaFree(ctx->g_ticket_tile); cudaFree(ctx->g_long); cudaFree(ctx->g_chain_status); cudaFree(ctx->g_chain_agg); cudaFree(ctx->g_chain_agg2); cudaFree(ctx->g_chain_exact);
   for (auto q : ctx->g_req) cudaFree(q);
   for (auto q : ctx->g_req2) cudaFree(q);
   cudaFree(ctx->gh_ns); cudaFree(ctx->gh_mask); cudaFree(ctx->gh_v);
@@ -1155,8 +1162,11 @@ int bgc_quota_eval16(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
 // ---------------------------------------------------------------- K3 (row N1): greedy in-batch admission
 namespace {
 
+// tiles of 1024 pods over the segments of kGreedyTeamMin pods or more: each has at most len / 1024 + 1
+inline size_t chain_tile_bound(size_t n) { return n / kGreedyTeam + n / kGreedyTeamMin + 2; }
+
 template <int R, typename VT>
-int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const uint8_t* mask_in, VT* verdict) {
+int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, size_t n, const uint8_t* mask_in, VT* verdict) {
   // the grouping sort already left the request columns (and masks) in grouped order in the context's buffers
   ReqCols<R> cols;
   for (int r = 0; r < R; ++r) cols.p[r] = ctx->g_req[r];
@@ -1168,18 +1178,54 @@ int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, const uint8_t* mask_in, VT* verdi
   int team_grid = ctx->sm_count;
   if ((uint32_t)team_grid > ctx->NS) team_grid = (int)ctx->NS;
   const size_t ring = greedy_team_smem(R);
-  auto go = [&](auto warp_kern, auto team_kern) -> int {
-    CU(cudaFuncSetAttribute(team_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
+  if (ctx->k3_long < 0) {
+    const char* e = std::getenv("BGC_K3_LONG");
+    ctx->k3_long = e && !std::strcmp(e, "team") ? 1 : 0;
+  }
+  auto go = [&](auto warp_kern, auto team_kern, auto chain_kern) -> int {
     warp_kern<<<grid, 256, 0, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask, ctx->NS,
                                     ctx->compute_mask, verdict, kGreedyTeamMin);
-    team_kern<<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
-                                                    ctx->NS, ctx->compute_mask, verdict);
-    ctx->tm.launches += 2;
+    ctx->tm.launches++;
     CU(cudaGetLastError());
+    if (n < kGreedyTeamMin) return BGC_OK;  // no segment can be long
+    if (ctx->k3_long == 1) {  // one CTA per long segment (the round-2 form before the chained tiles; kept for comparison)
+      CU(cudaFuncSetAttribute(team_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring));
+      team_kern<<<team_grid, kGreedyTeam, ring, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
+                                                      ctx->NS, ctx->compute_mask, verdict);
+      ctx->tm.launches++;
+      CU(cudaGetLastError());
+      return BGC_OK;
+    }
+    // long segments as chained tiles over all SMs
+    const size_t cnt = (size_t)ctx->NS + 1;
+    const unsigned blocks = (unsigned)((cnt + kScanBlock - 1) / kScanBlock);
+    uint32_t* totals = ctx->g_tile_base + cnt;
+    const size_t bound = chain_tile_bound(n);
+    ChainBufs C{ctx->g_tile_base, ctx->g_long, ctx->g_long + bound, ctx->g_tile_li, ctx->g_ticket_tile, ctx->g_chain_status,
+                ctx->g_chain_agg, ctx->g_chain_agg2, ctx->g_chain_exact, ctx->g_chain_status + bound};
+    CU(cudaMemsetAsync(ctx->g_chain_status, 0, (bound + 8) * 4, st));
+    k_chain_count<<<grid_for(cnt, 256, ctx->sm_count * 4), 256, 0, st>>>(ctx->g_seg, ctx->NS, kGreedyTeamMin, C);
+    k_scan_blocks<<<blocks, 1024, 0, st>>>(ctx->g_tile_base, cnt, totals);
+    k_scan_u32<<<1, 1024, 0, st>>>(totals, blocks);
+    k_scan_add<<<blocks, 1024, 0, st>>>(ctx->g_tile_base, cnt, totals);
+    k_chain_fill<<<ctx->sm_count, 256, 0, st>>>(C);
+    k_chain_order<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->NS, C);
+    const size_t smem = (size_t)R * kGreedyTeam * 8;
+    CU(cudaFuncSetAttribute(chain_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    chain_kern<<<ctx->sm_count, kGreedyTeam, smem, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
+                                                         ctx->NS, ctx->compute_mask, verdict, C);
+    ctx->tm.launches += 7;
+    CU(cudaGetLastError());
+    if (std::getenv("BGC_K3_STATS")) {  // debugging aid: synchronises
+      uint32_t h[8];
+      CU(cudaStreamSynchronize(st));
+      CU(cudaMemcpy(h, ctx->g_chain_status + bound, sizeof h, cudaMemcpyDeviceToHost));
+      std::fprintf(stderr, "[bgc k3 chain] tickets %u: first-of-segment %u, IDENT %u, AGG2 fitted %u, AGG fitted %u, walked %u; long segments %u\n", h[0], h[1], h[2], h[3], h[4], h[5], h[6]);
+    }
     return BGC_OK;
   };
-  return mask ? go(k3_admit_greedy<R, true, VT>, k3_admit_greedy_team<R, true, VT>)
-              : go(k3_admit_greedy<R, false, VT>, k3_admit_greedy_team<R, false, VT>);
+  return mask ? go(k3_admit_greedy<R, true, VT>, k3_admit_greedy_team<R, true, VT>, k3_admit_greedy_chain<R, true, VT>)
+              : go(k3_admit_greedy<R, false, VT>, k3_admit_greedy_team<R, false, VT>, k3_admit_greedy_chain<R, false, VT>);
 }
 
 int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
@@ -1210,6 +1256,32 @@ int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
     cudaFree(ctx->g_seg); ctx->g_seg = nullptr; ctx->g_seg_cap = 0;
     CU(cudaMalloc(&ctx->g_seg, ((size_t)ctx->NS + 2) * 4));
     ctx->g_seg_cap = (size_t)ctx->NS + 2;
+  }
+  {
+    const size_t base_need = (size_t)ctx->NS + 1 + ((size_t)ctx->NS + 1 + kScanBlock - 1) / kScanBlock + 1;  // + the scan's block totals
+    if (base_need > ctx->g_tile_base_cap) {
+      CU(cudaDeviceSynchronize());
+      cudaFree(ctx->g_tile_base); ctx->g_tile_base = nullptr; ctx->g_tile_base_cap = 0;
+      CU(cudaMalloc(&ctx->g_tile_base, base_need * 4));
+      ctx->g_tile_base_cap = base_need;
+    }
+    const size_t tiles = chain_tile_bound(n);
+    if (tiles > ctx->g_chain_cap || ctx->R > ctx->g_chain_R) {
+      CU(cudaDeviceSynchronize());
+      cudaFree(ctx->g_tile_li); cudaFree(ctx->g_ticket_tile); cudaFree(ctx->g_long); cudaFree(ctx->g_chain_status); cudaFree(ctx->g_chain_agg); cudaFree(ctx->g_chain_agg2); cudaFree(ctx->g_chain_exact);
+      ctx->g_tile_li = ctx->g_ticket_tile = ctx->g_long = ctx->g_chain_status = nullptr; ctx->g_chain_agg = ctx->g_chain_agg2 = ctx->g_chain_exact = nullptr;
+      const size_t cap = tiles > ctx->g_chain_cap ? tiles : ctx->g_chain_cap;
+      const int RR = ctx->R > ctx->g_chain_R ? ctx->R : ctx->g_chain_R;
+      ctx->g_chain_cap = 0; ctx->g_chain_R = 0;
+      CU(cudaMalloc(&ctx->g_tile_li, cap * 4));
+      CU(cudaMalloc(&ctx->g_ticket_tile, cap * 4));
+      CU(cudaMalloc(&ctx->g_long, cap * 2 * 4));  // namespaces and tile counts of the long segments (fewer than tiles)
+      CU(cudaMalloc(&ctx->g_chain_status, (cap + 8) * 4));  // + the ticket counter and the statistics
+      CU(cudaMalloc(&ctx->g_chain_agg, cap * RR * 8));
+      CU(cudaMalloc(&ctx->g_chain_agg2, cap * RR * 8));
+      CU(cudaMalloc(&ctx->g_chain_exact, cap * RR * 8));
+      ctx->g_chain_cap = cap; ctx->g_chain_R = RR;
+    }
   }
   size_t hist_need = (size_t)256 * ((n + kSortTile - 1) / kSortTile);
   hist_need += (hist_need + kScanBlock - 1) / kScanBlock + 1;  // + the block totals of the scan
@@ -1293,18 +1365,18 @@ int admit_greedy_dev_impl(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* 
   CU(cudaGetLastError());
   ctx->head_stale = true;
   switch (ctx->R) {
-    case 1: return launch_k3_r<1, VT>(ctx, st, d_req_mask, d_verdict);
-    case 2: return launch_k3_r<2, VT>(ctx, st, d_req_mask, d_verdict);
-    case 3: return launch_k3_r<3, VT>(ctx, st, d_req_mask, d_verdict);
-    case 4: return launch_k3_r<4, VT>(ctx, st, d_req_mask, d_verdict);
+    case 1: return launch_k3_r<1, VT>(ctx, st, n, d_req_mask, d_verdict);
+    case 2: return launch_k3_r<2, VT>(ctx, st, n, d_req_mask, d_verdict);
+    case 3: return launch_k3_r<3, VT>(ctx, st, n, d_req_mask, d_verdict);
+    case 4: return launch_k3_r<4, VT>(ctx, st, n, d_req_mask, d_verdict);
     default: break;
   }
   if constexpr (sizeof(VT) == 2) {
     switch (ctx->R) {
-      case 5: return launch_k3_r<5, VT>(ctx, st, d_req_mask, d_verdict);
-      case 6: return launch_k3_r<6, VT>(ctx, st, d_req_mask, d_verdict);
-      case 7: return launch_k3_r<7, VT>(ctx, st, d_req_mask, d_verdict);
-      default: return launch_k3_r<8, VT>(ctx, st, d_req_mask, d_verdict);
+      case 5: return launch_k3_r<5, VT>(ctx, st, n, d_req_mask, d_verdict);
+      case 6: return launch_k3_r<6, VT>(ctx, st, n, d_req_mask, d_verdict);
+      case 7: return launch_k3_r<7, VT>(ctx, st, n, d_req_mask, d_verdict);
+      default: return launch_k3_r<8, VT>(ctx, st, n, d_req_mask, d_verdict);
     }
   }
   return fail(ctx, BGC_E_BADARG, "R out of range");

@@ -706,4 +706,497 @@ k3_admit_greedy_team(const uint32_t* __restrict__ order, const uint32_t* __restr
   }
 }
 
+// ------------------------------------------------------------------ long segments on MANY CTAs: chained tiles
+// k3_admit_greedy_team gives a long segment to ONE CTA, so a Zipf head of 10^7 pods is 10^4 tiles walked one after
+// the other (4 us each: 40-70 ms, the whole greedy call waits for it).  Here the long segments are cut into tiles
+// of 1024 pods that ANY CTA may take (a ticket counter hands them out in order, so a tile only ever waits for
+// tiles held by CTAs that are already running), and the only thing a tile needs from its predecessors — the usage
+// S_in it starts from — travels through per-tile descriptors, decoupled look-back style:
+//   AGG(X)   "if S_in + X fits the quota, all my eligible pods are admitted and S_out = S_in + X" — published as
+//            soon as the tile's own requests are summed, before S_in is known;
+//   IDENT    "S_out = S_in" — published as soon as ANY exact usage of an earlier tile shows that no pod with a
+//            non-zero request fits on its own: requests are >= 0 in these tiles, so usage only grows and a pod that
+//            does not fit against a lower bound of S_in does not fit against S_in;
+//   AGG2(X') the same lower bound strikes out the pods that can never fit; X' sums the ones left: "if S_in + X' fits,
+//            exactly those are admitted and S_out = S_in + X'" (one resource full, the others still filling);
+//   EXACT(S) the tile's S_out, final;
+//   OPAQUE   a tile with a request outside [0, 2^40]: nothing can be said before S_in is known.
+// A tile resolves S_in by walking back to the nearest EXACT and adding the AGGs in between (valid when the sum
+// still fits: every intermediate prefix is smaller), IDENTs adding nothing.  While everything fits, and again once
+// the namespace is saturated, no tile waits for its predecessor's walk: the chain is only sequential where pods
+// are still slipping into the last of the headroom.  Verdict bits need the exact S_in, so an IDENT tile still
+// waits for it, but nobody waits for that tile.
+constexpr uint32_t kChainPending = 0, kChainAgg = 1, kChainOpaque = 2, kChainIdent = 3, kChainExact = 4, kChainAgg2 = 5;
+constexpr uint32_t kChainMaxBack = 2048;  // tiles: 2^62 + 2048 * 1024 * 2^40 < 2^63, so a walked-over stretch cannot wrap
+
+struct ChainBufs {
+  uint32_t* tile_base;    // [NS + 1] exclusive prefix of the tile counts (0 tiles for a short segment); [NS] = all tiles
+  uint32_t* long_ns;      // [long segments] their namespaces, in no particular order
+  uint32_t* long_nt;      // [long segments] their tile counts
+  uint32_t* tile_li;      // [tiles] index into long_ns of the tile's segment
+  uint32_t* ticket_tile;  // [tiles] the tile a ticket stands for: tile 0 of every long segment, then tile 1 of every ...
+  uint32_t* status;       // [tiles] kChain*
+  long long* agg;         // [tiles][R]
+  long long* agg2;        // [tiles][R]
+  long long* exact;       // [tiles][R]
+  uint32_t* ticket;       // [0] next ticket, [1..5] statistics, [6] number of long segments
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// tiles per namespace: ceil(len / 1024) for a segment the warp kernel leaves alone, else 0; the long ones are listed
+static __global__ void k_chain_count(const uint32_t* __restrict__ seg, uint32_t NS, uint32_t team_min, ChainBufs C) {
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k <= (size_t)NS; k += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t len = k < NS ? seg[k + 1] - seg[k] : 0u;
+    const uint32_t nt = len >= team_min ? (len + 1023u) / 1024u : 0u;
+    C.tile_base[k] = nt;
+    if (nt) {
+      const uint32_t li = atomicAdd(C.ticket + 6, 1u);
+      C.long_ns[li] = (uint32_t)k;
+      C.long_nt[li] = nt;
+    }
+  }
+}
+
+// tile_li[]: one warp per long segment
+static __global__ void k_chain_fill(ChainBufs C) {
+  const uint32_t lane = threadIdx.x & 31u, L = C.ticket[6];
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t li = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; li < L; li += warps) {
+    const uint32_t ns = C.long_ns[li];
+    const uint32_t b = C.tile_base[ns], e = C.tile_base[ns + 1];
+    for (uint32_t t = b + lane; t < e; t += 32) C.tile_li[t] = li;
+  }
+}
+
+// Ticket order: tile t of EVERY long segment before tile t + 1 of any, so that the CTAs in flight work on as many
+// segments as there are (a tile only ever waits for lower tiles of its own segment: the fewer of those are in
+// flight, the fresher the usage it looks back to, and the sequential stretches of different segments overlap).
+// Position of tile (segment li, t) = sum over segments of min(tiles, t) + the number of segments before li that
+// have a tile t.
+static __global__ void k_chain_order(uint32_t NS, ChainBufs C) {
+  const uint32_t L = C.ticket[6], tiles = C.tile_base[NS];
+  for (uint32_t d = blockIdx.x * blockDim.x + threadIdx.x; d < tiles; d += gridDim.x * blockDim.x) {
+    const uint32_t li = C.tile_li[d];
+    const uint32_t t = d - C.tile_base[C.long_ns[li]];
+    uint32_t pos = 0;
+    for (uint32_t j = 0; j < L; ++j) {
+      const uint32_t nt = __ldg(C.long_nt + j);
+      pos += (nt < t ? nt : t) + ((j < li && nt > t) ? 1u : 0u);
+    }
+    C.ticket_tile[pos] = d;
+  }
+}
+
+// shared memory of one 1024-pod tile step (the admit-run / reject-run alternation of the team kernel)
+template <int R>
+struct TileSmem {
+  long long (*E)[kGreedyTeam];  // [R][1024] exclusive prefixes (dynamic shared memory)
+  long long (*wtot)[32];        // [R][32]
+  long long* total;             // [R]
+  uint32_t* first;              // [2]
+  uint32_t* fit;                // [2]
+};
+
+// block-wide exclusive prefix sum of x[] (0 for threads that do not take part); leaves the per-thread prefixes in
+// M.E and the block total in M.total.  Two barriers.
+template <int R>
+__device__ __forceinline__ void tile_exclusive(const TileSmem<R>& M, const long long (&x)[R], long long (&E)[R]) {
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  long long incl[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) incl[r] = x[r];
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
+      if (lane >= (uint32_t)d) incl[r] = (long long)((unsigned long long)incl[r] + (unsigned long long)o);
+    }
+  }
+  if (lane == 31) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) M.wtot[r][warp] = incl[r];
+  }
+  __syncthreads();
+  if (warp == 0) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const long long mine = M.wtot[r][lane];
+      long long y = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const long long o = __shfl_up_sync(0xFFFFFFFFu, y, d);
+        if (lane >= (uint32_t)d) y = (long long)((unsigned long long)y + (unsigned long long)o);
+      }
+      M.wtot[r][lane] = (long long)((unsigned long long)y - (unsigned long long)mine);
+      if (lane == 31) M.total[r] = y;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    E[r] = (long long)((unsigned long long)M.wtot[r][warp] + (unsigned long long)incl[r] - (unsigned long long)x[r]);
+    M.E[r][tid] = E[r];
+  }
+}
+
+// One tile of 1024 consecutive pods of one namespace, usage S on entry: returns this thread's verdict and leaves the
+// usage after the tile in S (the same in every thread).  Ends on a barrier: the shared state may be reused at once.
+// `done(S)` is called by every thread as soon as the usage after the tile is final (before the reason bits of the
+// rejected pods are worked out).
+template <int R, int SHIFT, typename Done>
+__device__ __forceinline__ uint32_t greedy_tile(const TileSmem<R>& M, const GreedyPod<R>& p, bool valid, long long (&S)[R],
+                                               const long long (&H)[R], uint32_t hm, uint32_t compute_mask, uint32_t& iter,
+                                               Done done) {
+  const uint32_t tid = threadIdx.x, lane = tid & 31u;
+  constexpr uint32_t BIG = 0xFFFFFFFFu;
+  uint32_t my_verdict = 0, pos = 0;
+  bool tame = true;  // monotone fast path: requests in [0, 2^40], usage in [0, 2^62] (see the warp kernel)
+#pragma unroll
+  for (int r = 0; r < R; ++r) tame = tame && p.q[r] >= 0 && p.q[r] <= (1ll << 40) && S[r] >= 0 && S[r] <= (1ll << 62);
+  if (__syncthreads_and(tame)) {
+    long long S0[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) S0[r] = S[r];
+    bool live = valid, adm = false;
+    while (true) {
+      if (live && greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask) != 0) live = false;  // can never fit again
+      if (!__syncthreads_or(live)) break;
+      const uint32_t par = iter & 1u;
+      ++iter;
+      if (tid == 0) M.first[par] = BIG;
+      long long x[R], E[R], T[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) x[r] = live ? p.q[r] : 0;
+      tile_exclusive<R>(M, x, E);  // its barriers also publish the reset of first[par]
+#pragma unroll
+      for (int r = 0; r < R; ++r) T[r] = S[r] + E[r];
+      const uint32_t fail = __ballot_sync(0xFFFFFFFFu, live && greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask) != 0);
+      if (fail && lane == (uint32_t)(__ffs(fail) - 1)) atomicMin(&M.first[par], tid);
+      __syncthreads();
+      const uint32_t v = M.first[par];
+      if (v == BIG) {
+        adm = adm || live;
+#pragma unroll
+        for (int r = 0; r < R; ++r) S[r] += M.total[r];
+        break;
+      }
+      if (live && tid < v) adm = true;
+#pragma unroll
+      for (int r = 0; r < R; ++r) S[r] += M.E[r][v];
+      if (tid <= v) live = false;
+    }
+    done(S);
+    if (__syncthreads_or(adm)) {  // reason bits against the usage each rejected pod actually met
+      long long x[R], E[R], T[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) x[r] = adm ? p.q[r] : 0;
+      tile_exclusive<R>(M, x, E);
+#pragma unroll
+      for (int r = 0; r < R; ++r) T[r] = S0[r] + E[r];
+      my_verdict = adm ? 0u : greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
+    } else {                      // nothing admitted in this tile: usage never moved
+      my_verdict = valid ? greedy_verdict<R, SHIFT>(p, S0, H, hm, compute_mask) : 0u;
+    }
+    __syncthreads();
+    return my_verdict;
+  }
+  while (pos < (uint32_t)kGreedyTeam) {
+    const uint32_t par = iter & 1u;
+    ++iter;
+    // ---- admit-run: block-wide exclusive prefix of the adds of threads >= pos
+    if (tid == 0) { M.first[par] = BIG; M.fit[par] = BIG; }
+    long long a[R], E[R], T[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) a[r] = (valid && tid >= pos) ? p.q[r] : 0;
+    tile_exclusive<R>(M, a, E);
+#pragma unroll
+    for (int r = 0; r < R; ++r) T[r] = (long long)((unsigned long long)S[r] + (unsigned long long)E[r]);
+    const uint32_t v_run = greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
+    const uint32_t fail = __ballot_sync(0xFFFFFFFFu, valid && tid >= pos && v_run != 0);
+    if (fail && lane == (uint32_t)(__ffs(fail) - 1)) atomicMin(&M.first[par], tid);
+    __syncthreads();
+    const uint32_t v = M.first[par];
+    if (v == BIG) {  // everyone left in the tile is admitted
+#pragma unroll
+      for (int r = 0; r < R; ++r) S[r] = (long long)((unsigned long long)S[r] + (unsigned long long)M.total[r]);
+      break;
+    }
+    if (tid == v) my_verdict = v_run;
+#pragma unroll
+    for (int r = 0; r < R; ++r) S[r] = (long long)((unsigned long long)S[r] + (unsigned long long)M.E[r][v]);
+    pos = v + 1;
+    if (pos >= (uint32_t)kGreedyTeam) break;
+    // ---- reject-run: usage stands still at S until somebody fits on their own
+    const uint32_t v_alone = greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask);
+    const uint32_t fits = __ballot_sync(0xFFFFFFFFu, valid && tid >= pos && v_alone == 0);
+    if (fits && lane == (uint32_t)(__ffs(fits) - 1)) atomicMin(&M.fit[par], tid);
+    __syncthreads();
+    const uint32_t stop = M.fit[par] == BIG ? (uint32_t)kGreedyTeam : M.fit[par];
+    if (tid >= pos && tid < stop && valid) my_verdict = v_alone;
+    pos = stop;
+  }
+  done(S);
+  __syncthreads();
+  return my_verdict;
+}
+
+// block-wide sum of x[] into out[] (shared); one barrier inside, the caller adds the one that publishes out[]
+template <int R>
+__device__ __forceinline__ void tile_sum(long long (&x)[R], long long (*wtot)[32], long long* out) {
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) x[r] += __shfl_xor_sync(0xFFFFFFFFu, x[r], d);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) wtot[r][warp] = x[r];
+  }
+  __syncthreads();
+  if (warp == 0) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      long long y = wtot[r][lane];
+#pragma unroll
+      for (int d = 16; d >= 1; d >>= 1) y += __shfl_xor_sync(0xFFFFFFFFu, y, d);
+      if (lane == 0) out[r] = y;  // <= 1024 * 2^40
+    }
+  }
+}
+
+// does usage S + X still fit?  (only resources somebody asks for can be exceeded; sums stay below 2^63)
+template <int R>
+__device__ __forceinline__ bool chain_fits(const long long (&S)[R], const long long (&X)[R], const long long (&H)[R], uint32_t hm) {
+  bool ok = true;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const long long sum = S[r] + X[r];  // S in [0, 2^62], X in [0, 2^61]
+    ok = ok && sum <= (1ll << 62) && !(((hm >> r) & 1u) && X[r] > 0 && sum > H[r]);
+  }
+  return ok;
+}
+
+// Warp 0 of the CTA that holds tile c walks back over the descriptors of tiles first..c-1 of the same namespace.
+// Returns 0 with S = S_in when it is known, 1 with S = a lower bound of S_in (the nearest exact usage) when the
+// aggregates in between do not fit, 2 when nothing can be said yet.
+template <int R>
+__device__ __forceinline__ int chain_lookback(const ChainBufs& C, uint32_t c, uint32_t first, const long long (&H)[R], uint32_t hm,
+                                              long long (&S)[R]) {
+  const uint32_t lane = threadIdx.x & 31u;
+  long long A[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) A[r] = 0;
+  uint32_t pos = c;  // tiles pos..c-1 are summed in A
+  for (uint32_t hop = 0; hop < kChainMaxBack / 32; ++hop) {
+    const bool in = pos >= first + lane + 1;
+    const uint32_t j = pos - 1u - lane;
+    const uint32_t st = in ? ld_acquire_u32(C.status + j) : kChainPending;
+    const uint32_t m_exact = __ballot_sync(0xFFFFFFFFu, st == kChainExact);
+    const uint32_t m_block = __ballot_sync(0xFFFFFFFFu, st == kChainPending || st == kChainOpaque);
+    const uint32_t e = m_exact ? (uint32_t)__ffs(m_exact) - 1u : 32u;
+    const uint32_t nearer = e == 32u ? 0xFFFFFFFFu : ((1u << e) - 1u);
+    if (m_block & nearer) return 2;
+    const bool take = lane < e && (st == kChainAgg || st == kChainAgg2);
+    const long long* from = st == kChainAgg2 ? C.agg2 : C.agg;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      long long a = take ? __ldcg(from + (size_t)j * R + r) : 0;
+#pragma unroll
+      for (int d = 16; d >= 1; d >>= 1) a += __shfl_xor_sync(0xFFFFFFFFu, a, d);
+      A[r] += a;                                 // <= 2^61 + 32 * 2^50
+      if (A[r] > (1ll << 61)) A[r] = 1ll << 61;  // too much to fit anyway
+    }
+    if (e < 32u) {
+      bool sane = true, zero = true;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        long long b = lane == e ? __ldcg(C.exact + (size_t)j * R + r) : 0;
+        S[r] = __shfl_sync(0xFFFFFFFFu, b, e);
+        sane = sane && S[r] >= 0 && S[r] <= (1ll << 62);
+        zero = zero && A[r] == 0;
+      }
+      if (zero) return 0;  // nothing but IDENT tiles (and tiles of all-zero requests) in between
+      if (!sane) return 2;
+      if (chain_fits<R>(S, A, H, hm)) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) S[r] += A[r];
+        return 0;
+      }
+      return 1;
+    }
+    pos -= 32u;
+  }
+  return 2;
+}
+
+template <int R, bool HAS_MASK, typename VT>
+__global__ void __launch_bounds__(kGreedyTeam, 1)
+k3_admit_greedy_chain(const uint32_t* __restrict__ order, const uint32_t* __restrict__ seg, ReqCols<R> req,
+                      const uint8_t* __restrict__ req_mask, long long* used, const long long* __restrict__ hard,
+                      const uint8_t* __restrict__ hard_mask, uint32_t NS, uint32_t compute_mask,
+                      VT* __restrict__ verdict, ChainBufs C) {
+  constexpr int SHIFT = sizeof(VT) == 1 ? 4 : 8;
+  extern __shared__ __align__(16) long long g_chain_E[];  // [R][kGreedyTeam]
+  __shared__ long long s_wtot[R][32];
+  __shared__ long long s_total[R];
+  __shared__ long long s_X[R], s_in[R];
+  __shared__ uint32_t s_first[2], s_fit[2], s_tile, s_res;
+  TileSmem<R> M;
+  M.E = reinterpret_cast<long long (*)[kGreedyTeam]>(g_chain_E);
+  M.wtot = s_wtot; M.total = s_total; M.first = s_first; M.fit = s_fit;
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const uint32_t tiles = C.tile_base[NS];
+  uint32_t iter = 0;
+  for (;;) {
+    if (tid == 0) s_tile = atomicAdd(C.ticket, 1u);
+    __syncthreads();
+    if (s_tile >= tiles) break;
+    const uint32_t c = C.ticket_tile[s_tile];
+    const uint32_t ns = C.long_ns[C.tile_li[c]];
+    const uint32_t first = C.tile_base[ns], last = C.tile_base[ns + 1] - 1u;
+    const uint32_t end = seg[ns + 1];
+    const uint32_t t = seg[ns] + (c - first) * (uint32_t)kGreedyTeam;
+    const bool valid = t + tid < end;
+    GreedyPod<R> p;
+#pragma unroll
+    for (int r = 0; r < R; ++r) p.q[r] = valid ? req.p[r][t + tid] : 0;
+    p.mask = (HAS_MASK && valid) ? req_mask[t + tid] : 0xFFu;
+    const uint32_t ord = valid ? order[t + tid] : 0u;
+    long long H[R], S[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) H[r] = hard[(size_t)r * NS + ns];
+    const uint32_t hm = hard_mask[ns];
+    // what can be said before S_in is known
+    bool tame_q = true;
+#pragma unroll
+    for (int r = 0; r < R; ++r) tame_q = tame_q && p.q[r] >= 0 && p.q[r] <= (1ll << 40);
+    const bool tile_tame = __syncthreads_and(tame_q);
+    uint32_t missing = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      if (((hm >> r) & 1u) && !((p.mask >> r) & 1u) && ((compute_mask >> r) & 1u)) missing |= 1u << r;
+    const bool eligible = valid && missing == 0;  // a pod that misses a required request is rejected whatever the usage
+    if (tile_tame) {
+      long long x[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) x[r] = eligible ? p.q[r] : 0;
+      tile_sum<R>(x, s_wtot, s_X);
+      if (tid == 0 && c != first) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) __stcg(C.agg + (size_t)c * R + r, s_X[r]);
+      }
+    }
+    if (tid == 0 && c != first) {
+      __threadfence();
+      st_release_u32(C.status + c, tile_tame ? kChainAgg : kChainOpaque);
+    }
+    __syncthreads();
+    // ---- S_in
+    bool ident = false, agg2 = false, live = eligible;  // live: not yet struck out by a lower bound of S_in
+    if (c == first) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) S[r] = used[(size_t)r * NS + ns];
+    } else {
+      bool tried_ident = !tile_tame;
+      unsigned long long t0 = 0;
+      for (uint32_t spin = 0;; ++spin) {
+        if (warp == 0) {
+          long long W[R];
+          const int res = chain_lookback<R>(C, c, first, H, hm, W);
+          if (lane == 0) {
+            s_res = (uint32_t)res;
+#pragma unroll
+            for (int r = 0; r < R; ++r) s_in[r] = W[r];
+          }
+        }
+        __syncthreads();
+        const uint32_t res = s_res;
+#pragma unroll
+        for (int r = 0; r < R; ++r) S[r] = s_in[r];
+        if (res == 0) break;
+        if (res == 1 && !tried_ident) {  // S is a lower bound of S_in: who does not fit against it never will
+          tried_ident = true;
+          live = eligible && greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask) == 0;
+          bool moves = false;  // an admitted pod of all-zero requests leaves the usage where it is
+#pragma unroll
+          for (int r = 0; r < R; ++r) moves = moves || p.q[r] != 0;
+          if (!__syncthreads_or(live && moves)) {
+            ident = true;
+            if (tid == 0) st_release_u32(C.status + c, kChainIdent);
+          } else {
+            agg2 = true;
+            long long x[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) x[r] = live ? p.q[r] : 0;
+            tile_sum<R>(x, s_wtot, s_X);  // replaces the sum over all eligible pods: the struck ones are out for good
+            if (tid == 0) {
+#pragma unroll
+              for (int r = 0; r < R; ++r) __stcg(C.agg2 + (size_t)c * R + r, s_X[r]);
+              __threadfence();
+              st_release_u32(C.status + c, kChainAgg2);
+            }
+          }
+        }
+        __syncthreads();  // s_res / s_in are rewritten by the next walk
+        if (warp == 0) {
+          if (spin > 64) __nanosleep(200);
+          if ((spin & 1023u) == 1023u) {  // a tile never waits for a tile that is not running: this is a bug trap, not a time limit
+            const unsigned long long now = global_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 30000000000ull) __trap();
+          }
+        }
+      }
+    }
+    // ---- S_out known without walking the tile?  Tell the successors now.
+    bool early = false;
+    if (tile_tame) {
+      long long X[R];
+      bool sane = true;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        X[r] = ident ? 0 : s_X[r];
+        sane = sane && S[r] >= 0 && S[r] <= (1ll << 62);
+      }
+      early = sane && (ident || chain_fits<R>(S, X, H, hm));
+      if (early && tid == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) __stcg(C.exact + (size_t)c * R + r, S[r] + X[r]);
+        __threadfence();
+        st_release_u32(C.status + c, kChainExact);
+      }
+    }
+    const uint32_t my_verdict = greedy_tile<R, SHIFT>(M, p, valid, S, H, hm, compute_mask, iter, [&](const long long (&So)[R]) {
+      if (!early && tid == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) __stcg(C.exact + (size_t)c * R + r, So[r]);
+        __threadfence();
+        st_release_u32(C.status + c, kChainExact);
+      }
+    });
+    if (valid) verdict[ord] = (VT)my_verdict;
+    if (tid == 0)  // how the tile got its S_out, for BGC_K3_STATS: [1] first of a segment, [2] IDENT, [3] AGG2 fitted, [4] AGG fitted, [5] walked
+      atomicAdd(C.ticket + (c == first ? 1 : ident ? 2 : early && agg2 ? 3 : early ? 4 : 5), 1u);
+    if (c == last && tid == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) used[(size_t)r * NS + ns] = S[r];
+    }
+  }
+}
+
 }  // namespace bgc

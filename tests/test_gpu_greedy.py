@@ -174,3 +174,55 @@ def test_greedy_long_segments_in_and_out_of_the_monotone_range(engine, oracle, R
     assert np.array_equal(got_v, want_v)
     assert np.array_equal(engine.usage_get(), want_u)
     assert 0.0 < np.mean(want_v[ns == 0] == 0) < 1.0 and np.all(want_v[ns == 3] == 0)
+
+
+@pytest.mark.parametrize("R,wide", [(1, False), (3, False), (4, False), (6, True)])
+@pytest.mark.parametrize("scenario", ["fill_then_slip", "saturated_from_start", "never_full", "negatives", "wrap"])
+def test_greedy_chained_tiles(engine, oracle, R, wide, scenario):
+    """Segments of hundreds to thousands of 1024-pod tiles, walked by many CTAs at once through the tile descriptors
+    (AGG / IDENT / EXACT / OPAQUE, csrc/bgc_k3.cuh): every regime of the chain against the literal loop.
+      fill_then_slip        quota reached a third of the way in, small pods keep slipping into what is left
+      saturated_from_start  usage starts at the quota: every tile is IDENT, verdict bits still need the exact usage
+      never_full            no tile ever rejects: pure prefix sums over AGG descriptors (one namespace without a quota object)
+      negatives             a negative request every ~3000 pods: OPAQUE tiles force the sequential hand-over
+      wrap                  an unconstrained column crosses 2^63 and wraps (more than 2048 tiles of 2^40-byte requests)"""
+    rng = np.random.default_rng(R * 31 + len(scenario))
+    NS = 3
+    n = 4_600_000 if scenario == "wrap" else 1_500_000
+    ns = rng.choice(np.array([0, 0, 0, 1, 2], np.uint32), n) if scenario != "wrap" else np.zeros(n, np.uint32)
+    sizes = np.array([0, 1, 1, 2, 3, 8, 64, 250, 1000, 4000], np.int64)
+    req = [rng.choice(sizes, n) for _ in range(R)]
+    mask = rng.integers(0, 256, n, dtype=np.uint8) | np.uint8(0b0110)
+    mask[::53] &= np.uint8(0xFD)                     # some pods omit a required request
+    used0 = np.zeros((R, NS), np.int64)
+    hm = np.full(NS, (1 << R) - 1, np.uint8)
+    total = np.stack([np.bincount(ns, weights=c.astype(np.float64), minlength=NS) for c in req]).astype(np.int64)
+    hard = total // 3
+    if scenario == "saturated_from_start":
+        used0[:] = hard - 1
+        used0[0, 1] = hard[0, 1] + 5                 # one namespace already over its quota
+    elif scenario == "never_full":
+        hard[:, 0] = total[:, 0] + 1                 # fits to the last pod
+        hm[1] = 0                                    # no quota object
+        hard[:, 2] = np.iinfo(np.int64).max
+    elif scenario == "negatives":
+        for r in range(R):
+            req[r][rng.integers(0, n, n // 3000)] = -rng.integers(1, 5000, n // 3000)
+    elif scenario == "wrap":
+        hm[:] = 1 if R > 1 else 0                    # the last column is unconstrained (R = 1: no quota at all)
+        req[R - 1][:] = 1 << 40
+        used0[R - 1, 0] = (1 << 62) - 12345
+        hard = np.full((R, NS), np.iinfo(np.int64).max, np.int64)
+        if R > 1:
+            hard[0, 0] = total[0, 0] - total[0, 0] // 40    # the constrained column fills up near the end
+    engine.quota_table_set(hard, hm, UNITS[R])
+    engine.usage_set(used0)
+    f = oracle.admit_greedy16 if wide else oracle.admit_greedy
+    want_v, want_u = f(ns, req, mask, NS, used0, hard, hm, _cm(UNITS[R]))
+    got_v = engine.admit_greedy(ns, req, mask, wide=wide)
+    assert np.array_equal(got_v, want_v)
+    assert np.array_equal(engine.usage_get(), want_u)
+    if scenario == "fill_then_slip":
+        assert 0.2 < np.mean(want_v == 0) < 0.9
+    if scenario == "wrap":
+        assert want_u[R - 1, 0] < 0                  # it did wrap

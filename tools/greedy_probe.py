@@ -10,7 +10,9 @@ from oracle import quota_ref as Q
 from workloads import KINDS, UNITS, make_hard
 bgc = importlib.import_module("bacchus-gpu-controller_b200")
 
-ap = argparse.ArgumentParser(); ap.add_argument("--pods", type=int, default=100_000_000); args = ap.parse_args()
+ap = argparse.ArgumentParser(); ap.add_argument("--pods", type=int, default=100_000_000)
+ap.add_argument("--verify", action="store_true", help="check EVERY verdict and the final usage table against the literal loop (about 10 s per case)")
+args = ap.parse_args()
 n = args.pods
 eng = bgc.Engine(0); eng.use_torch_stream()
 R = 3
@@ -42,7 +44,12 @@ for NS, dist, s in [(10_000, 0, 0.0), (10_000, 1, 1.1), (1_000_000, 0, 0.0), (1_
     c = oracle.gen_fill(oracle.gen_params(0xB2000003, 1, NS, dist, 0, n, a, b, cdf, KINDS[R]), 0, m, threads=8)
     t0 = time.perf_counter(); wv, wu = oracle.admit_greedy(c[0], c[1], None, NS, used0, hard, hm, 6); cpu_s = time.perf_counter() - t0
     same = bool(np.array_equal(wv[: 1 << 16], v[: 1 << 16].cpu().numpy())) if m == n else None
+    full = None
+    if args.verify:     # the device's own columns, every pod, through the literal loop
+        fv, fu = oracle.admit_greedy(ns.cpu().numpy().view(np.uint32), [c.cpu().numpy() for c in req], None, NS, used0, hard, hm, 6)
+        full = bool(np.array_equal(fv, v.cpu().numpy()) and np.array_equal(fu, eng.usage_get()))
     print(json.dumps({"kernel": "k3_admit_greedy", "n": n, "NS": NS, "dist": "zipf%.1f" % s if dist else "uniform", "ms": round(ms, 3),
                       "Mpods_s": round(n / ms / 1e3, 1), "admitted_frac": round(adm, 3), "cpu_literal_loop_Mpods_s": round(m / cpu_s / 1e6, 1),
-                      "prefix_matches_oracle": same}), flush=True)
+                      "prefix_matches_oracle": same, "every_verdict_and_usage_match_the_literal_loop": full,
+                      "long_segments": os.environ.get("BGC_K3_LONG", "chain")}), flush=True)
     del ns, req, v
