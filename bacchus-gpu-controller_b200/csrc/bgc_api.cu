@@ -88,7 +88,7 @@ struct bgc_ctx {
   int gh_R = 0;
   size_t g_cap = 0, g_hist_cap = 0, g_seg_cap = 0;
   // long segments of the greedy walk, cut into chained tiles (bgc_k3.cuh): tile table and descriptors
-  uint32_t *g_tile_base = nullptr, *g_tile_li = nullptr, *g_ticket_tile = nullptr, *g_long = nullptr, *g_chain_status = nullptr;
+  uint32_t *g_tile_base = nullptr, *g_tile_li = nullptr, *g_ticket_rec = nullptr, *g_long = nullptr, *g_chain_status = nullptr;
   long long *g_chain_agg = nullptr, *g_chain_agg2 = nullptr, *g_chain_exact = nullptr;
   size_t g_tile_base_cap = 0, g_chain_cap = 0;
   int g_chain_R = 0;
@@ -700,7 +700,7 @@ int bgc_ctx_destroy(bgc_ctx* ctx) {
   cudaFreeHost(ctx->bounce[0]); cudaFreeHost(ctx->bounce[1]);
   cudaFree(ctx->g_keys); cudaFree(ctx->g_keys_sorted); cudaFree(ctx->g_idx); cudaFree(ctx->g_order);
   cudaFree(ctx->g_seg); cudaFree(ctx->g_hist); cudaFree(ctx->g_mask); cudaFree(ctx->g_mask2);
-  cudaFree(ctx->g_tile_base); cudaFree(ctx->g_tile_li); cudaFree(ctx->g_ticket_tile); cudaFree(ctx->g_long); cudaFree(ctx->g_chain_status); cudaFree(ctx->g_chain_agg); cudaFree(ctx->g_chain_agg2); cudaFree(ctx->g_chain_exact);
+  cudaFree(ctx->g_tile_base); cudaFree(ctx->g_tile_li); cudaFree(ctx->g_ticket_rec); cudaFree(ctx->g_long); cudaFree(ctx->g_chain_status); cudaFree(ctx->g_chain_agg); cudaFree(ctx->g_chain_agg2); cudaFree(ctx->g_chain_exact);
   for (auto q : ctx->g_req) cudaFree(q);
   for (auto q : ctx->g_req2) cudaFree(q);
   cudaFree(ctx->gh_ns); cudaFree(ctx->gh_mask); cudaFree(ctx->gh_v);
@@ -1163,7 +1163,7 @@ int bgc_quota_eval16(bgc_ctx* ctx, const uint32_t* ns_id, const int64_t* const* 
 namespace {
 
 // tiles of 1024 pods over the segments of kGreedyTeamMin pods or more: each has at most len / 1024 + 1
-inline size_t chain_tile_bound(size_t n) { return n / kGreedyTeam + n / kGreedyTeamMin + 2; }
+inline size_t chain_tile_bound(size_t n) { return (n / kGreedyTeam + n / kGreedyTeamMin + 3) & ~size_t(1); }  // even: 8-byte aligned counters behind it
 
 template <int R, typename VT>
 int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, size_t n, const uint8_t* mask_in, VT* verdict) {
@@ -1201,15 +1201,15 @@ int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, size_t n, const uint8_t* mask_in,
     const unsigned blocks = (unsigned)((cnt + kScanBlock - 1) / kScanBlock);
     uint32_t* totals = ctx->g_tile_base + cnt;
     const size_t bound = chain_tile_bound(n);
-    ChainBufs C{ctx->g_tile_base, ctx->g_long, ctx->g_long + bound, ctx->g_tile_li, ctx->g_ticket_tile, ctx->g_chain_status,
+    ChainBufs C{ctx->g_tile_base, ctx->g_long, ctx->g_long + bound, ctx->g_tile_li, reinterpret_cast<uint4*>(ctx->g_ticket_rec), ctx->g_chain_status,
                 ctx->g_chain_agg, ctx->g_chain_agg2, ctx->g_chain_exact, ctx->g_chain_status + bound};
-    CU(cudaMemsetAsync(ctx->g_chain_status, 0, (bound + 8) * 4, st));
+    CU(cudaMemsetAsync(ctx->g_chain_status, 0, (bound + 16) * 4, st));
     k_chain_count<<<grid_for(cnt, 256, ctx->sm_count * 4), 256, 0, st>>>(ctx->g_seg, ctx->NS, kGreedyTeamMin, C);
     k_scan_blocks<<<blocks, 1024, 0, st>>>(ctx->g_tile_base, cnt, totals);
     k_scan_u32<<<1, 1024, 0, st>>>(totals, blocks);
     k_scan_add<<<blocks, 1024, 0, st>>>(ctx->g_tile_base, cnt, totals);
     k_chain_fill<<<ctx->sm_count, 256, 0, st>>>(C);
-    k_chain_order<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->NS, C);
+    k_chain_order<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->g_seg, ctx->NS, C);
     const size_t smem = (size_t)R * kGreedyTeam * 8;
     CU(cudaFuncSetAttribute(chain_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     chain_kern<<<ctx->sm_count, kGreedyTeam, smem, st>>>(ctx->g_order, ctx->g_seg, cols, mask, ctx->d_used, ctx->d_hard, ctx->d_hard_mask,
@@ -1217,9 +1217,17 @@ int launch_k3_r(bgc_ctx* ctx, cudaStream_t st, size_t n, const uint8_t* mask_in,
     ctx->tm.launches += 7;
     CU(cudaGetLastError());
     if (std::getenv("BGC_K3_STATS")) {  // debugging aid: synchronises
-      uint32_t h[8];
+      uint32_t h[16];
       CU(cudaStreamSynchronize(st));
       CU(cudaMemcpy(h, ctx->g_chain_status + bound, sizeof h, cudaMemcpyDeviceToHost));
+#ifdef BGC_K3_CLOCKS
+      {
+        unsigned long long ck[3];
+        std::memcpy(ck, h + 8, sizeof ck);
+        std::fprintf(stderr, "[bgc k3 chain] cycles per tile: load+sum %.0f, wait for S_in %.0f, walk %.0f\n", (double)ck[0] / (h[0] ? h[0] : 1),
+                     (double)ck[1] / (h[0] ? h[0] : 1), (double)ck[2] / (h[0] ? h[0] : 1));
+      }
+#endif
       std::fprintf(stderr, "[bgc k3 chain] tickets %u: first-of-segment %u, IDENT %u, AGG2 fitted %u, AGG fitted %u, walked %u; long segments %u\n", h[0], h[1], h[2], h[3], h[4], h[5], h[6]);
     }
     return BGC_OK;
@@ -1268,15 +1276,15 @@ int ensure_greedy_buffers(bgc_ctx* ctx, size_t n) {
     const size_t tiles = chain_tile_bound(n);
     if (tiles > ctx->g_chain_cap || ctx->R > ctx->g_chain_R) {
       CU(cudaDeviceSynchronize());
-      cudaFree(ctx->g_tile_li); cudaFree(ctx->g_ticket_tile); cudaFree(ctx->g_long); cudaFree(ctx->g_chain_status); cudaFree(ctx->g_chain_agg); cudaFree(ctx->g_chain_agg2); cudaFree(ctx->g_chain_exact);
-      ctx->g_tile_li = ctx->g_ticket_tile = ctx->g_long = ctx->g_chain_status = nullptr; ctx->g_chain_agg = ctx->g_chain_agg2 = ctx->g_chain_exact = nullptr;
+      cudaFree(ctx->g_tile_li); cudaFree(ctx->g_ticket_rec); cudaFree(ctx->g_long); cudaFree(ctx->g_chain_status); cudaFree(ctx->g_chain_agg); cudaFree(ctx->g_chain_agg2); cudaFree(ctx->g_chain_exact);
+      ctx->g_tile_li = ctx->g_ticket_rec = ctx->g_long = ctx->g_chain_status = nullptr; ctx->g_chain_agg = ctx->g_chain_agg2 = ctx->g_chain_exact = nullptr;
       const size_t cap = tiles > ctx->g_chain_cap ? tiles : ctx->g_chain_cap;
       const int RR = ctx->R > ctx->g_chain_R ? ctx->R : ctx->g_chain_R;
       ctx->g_chain_cap = 0; ctx->g_chain_R = 0;
       CU(cudaMalloc(&ctx->g_tile_li, cap * 4));
-      CU(cudaMalloc(&ctx->g_ticket_tile, cap * 4));
+      CU(cudaMalloc(&ctx->g_ticket_rec, cap * 16));
       CU(cudaMalloc(&ctx->g_long, cap * 2 * 4));  // namespaces and tile counts of the long segments (fewer than tiles)
-      CU(cudaMalloc(&ctx->g_chain_status, (cap + 8) * 4));  // + the ticket counter and the statistics
+      CU(cudaMalloc(&ctx->g_chain_status, (cap + 16) * 4));  // + the ticket counter and the statistics
       CU(cudaMalloc(&ctx->g_chain_agg, cap * RR * 8));
       CU(cudaMalloc(&ctx->g_chain_agg2, cap * RR * 8));
       CU(cudaMalloc(&ctx->g_chain_exact, cap * RR * 8));

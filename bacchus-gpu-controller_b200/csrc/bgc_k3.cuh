@@ -136,6 +136,10 @@ struct SortPayload {
 // (Tried and measured slower, round 2: warp-owned contiguous chunks ranked with two passes of __match_any_sync and
 // only four block barriers per tile — 12.5 ms per 10^8-pod greedy call against 9.8 ms for the rounds below: the
 // second match per element costs more than the 124 barriers it saves.)
+// (Also tried, round 2: keeping only (digit, place in the tile) per element while the tile is ranked — 32 KB of shared
+// memory and 64 registers instead of 80 KB and 123, four CTAs per SM instead of two — and fetching key and index
+// again at write-out like the payload columns: 9.8 ms per 10^8-pod greedy call against 8.2 ms, the scattered 4-byte
+// re-reads cost a whole L2 sector each.)
 // One tile per trip: the tile is sorted by digit INSIDE shared memory first (in-order ranks as described
 // above), then written out — every digit's elements of the tile are consecutive in shared memory and go to
 // consecutive global positions, so the writes are whole 32-byte sectors instead of one 4-byte element per
@@ -734,7 +738,8 @@ struct ChainBufs {
   uint32_t* long_ns;      // [long segments] their namespaces, in no particular order
   uint32_t* long_nt;      // [long segments] their tile counts
   uint32_t* tile_li;      // [tiles] index into long_ns of the tile's segment
-  uint32_t* ticket_tile;  // [tiles] the tile a ticket stands for: tile 0 of every long segment, then tile 1 of every ...
+  uint4* ticket_rec;      // [tiles] what a ticket stands for — tile 0 of every long segment, then tile 1 of every ... —
+                          // as one 16-byte record: tile, namespace, first tile of the namespace, first pod of the tile
   uint32_t* status;       // [tiles] kChain*
   long long* agg;         // [tiles][R]
   long long* agg2;        // [tiles][R]
@@ -786,17 +791,18 @@ static __global__ void k_chain_fill(ChainBufs C) {
 // flight, the fresher the usage it looks back to, and the sequential stretches of different segments overlap).
 // Position of tile (segment li, t) = sum over segments of min(tiles, t) + the number of segments before li that
 // have a tile t.
-static __global__ void k_chain_order(uint32_t NS, ChainBufs C) {
+static __global__ void k_chain_order(const uint32_t* __restrict__ seg, uint32_t NS, ChainBufs C) {
   const uint32_t L = C.ticket[6], tiles = C.tile_base[NS];
   for (uint32_t d = blockIdx.x * blockDim.x + threadIdx.x; d < tiles; d += gridDim.x * blockDim.x) {
     const uint32_t li = C.tile_li[d];
-    const uint32_t t = d - C.tile_base[C.long_ns[li]];
+    const uint32_t ns = C.long_ns[li], first = C.tile_base[ns];
+    const uint32_t t = d - first;
     uint32_t pos = 0;
     for (uint32_t j = 0; j < L; ++j) {
       const uint32_t nt = __ldg(C.long_nt + j);
       pos += (nt < t ? nt : t) + ((j < li && nt > t) ? 1u : 0u);
     }
-    C.ticket_tile[pos] = d;
+    C.ticket_rec[pos] = make_uint4(d, ns, first, seg[ns] + t * (uint32_t)kGreedyTeam);
   }
 }
 
@@ -1066,12 +1072,14 @@ k3_admit_greedy_chain(const uint32_t* __restrict__ order, const uint32_t* __rest
     if (tid == 0) s_tile = atomicAdd(C.ticket, 1u);
     __syncthreads();
     if (s_tile >= tiles) break;
-    const uint32_t c = C.ticket_tile[s_tile];
-    const uint32_t ns = C.long_ns[C.tile_li[c]];
-    const uint32_t first = C.tile_base[ns], last = C.tile_base[ns + 1] - 1u;
+#ifdef BGC_K3_CLOCKS
+    const long long ck0 = clock64();
+#endif
+    const uint4 rec = C.ticket_rec[s_tile];  // one load instead of a chain of five dependent ones
+    const uint32_t c = rec.x, ns = rec.y, first = rec.z, t = rec.w;
     const uint32_t end = seg[ns + 1];
-    const uint32_t t = seg[ns] + (c - first) * (uint32_t)kGreedyTeam;
     const bool valid = t + tid < end;
+    const bool is_last = t + (uint32_t)kGreedyTeam >= end;
     GreedyPod<R> p;
 #pragma unroll
     for (int r = 0; r < R; ++r) p.q[r] = valid ? req.p[r][t + tid] : 0;
@@ -1106,6 +1114,9 @@ k3_admit_greedy_chain(const uint32_t* __restrict__ order, const uint32_t* __rest
       st_release_u32(C.status + c, tile_tame ? kChainAgg : kChainOpaque);
     }
     __syncthreads();
+#ifdef BGC_K3_CLOCKS
+    const long long ck1 = clock64();
+#endif
     // ---- S_in
     bool ident = false, agg2 = false, live = eligible;  // live: not yet struck out by a lower bound of S_in
     if (c == first) {
@@ -1163,6 +1174,9 @@ k3_admit_greedy_chain(const uint32_t* __restrict__ order, const uint32_t* __rest
         }
       }
     }
+#ifdef BGC_K3_CLOCKS
+    const long long ck2 = clock64();
+#endif
     // ---- S_out known without walking the tile?  Tell the successors now.
     bool early = false;
     if (tile_tame) {
@@ -1181,18 +1195,42 @@ k3_admit_greedy_chain(const uint32_t* __restrict__ order, const uint32_t* __rest
         st_release_u32(C.status + c, kChainExact);
       }
     }
-    const uint32_t my_verdict = greedy_tile<R, SHIFT>(M, p, valid, S, H, hm, compute_mask, iter, [&](const long long (&So)[R]) {
-      if (!early && tid == 0) {
+    uint32_t my_verdict;
+    if (early && ident) {  // nobody moves the usage: every pod met S_in
+      my_verdict = valid ? greedy_verdict<R, SHIFT>(p, S, H, hm, compute_mask) : 0u;
+    } else if (early) {    // the pods still live are admitted one and all; the others met S_in + what was admitted before them
+      long long x[R], E[R], T[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) __stcg(C.exact + (size_t)c * R + r, So[r]);
-        __threadfence();
-        st_release_u32(C.status + c, kChainExact);
-      }
-    });
+      for (int r = 0; r < R; ++r) x[r] = live ? p.q[r] : 0;
+      tile_exclusive<R>(M, x, E);
+#pragma unroll
+      for (int r = 0; r < R; ++r) T[r] = S[r] + E[r];
+      my_verdict = (live || !valid) ? 0u : greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
+#pragma unroll
+      for (int r = 0; r < R; ++r) S[r] += M.total[r];
+      __syncthreads();  // M is reused by the next tile
+    } else {
+      my_verdict = greedy_tile<R, SHIFT>(M, p, valid, S, H, hm, compute_mask, iter, [&](const long long (&So)[R]) {
+        if (tid == 0) {
+#pragma unroll
+          for (int r = 0; r < R; ++r) __stcg(C.exact + (size_t)c * R + r, So[r]);
+          __threadfence();
+          st_release_u32(C.status + c, kChainExact);
+        }
+      });
+    }
     if (valid) verdict[ord] = (VT)my_verdict;
+#ifdef BGC_K3_CLOCKS
+    if (tid == 0) {  // cycles: ticket -> AGG published, waiting for S_in, walking the tile
+      unsigned long long* ck = reinterpret_cast<unsigned long long*>(C.ticket + 8);
+      atomicAdd(ck + 0, (unsigned long long)(ck1 - ck0));
+      atomicAdd(ck + 1, (unsigned long long)(ck2 - ck1));
+      atomicAdd(ck + 2, (unsigned long long)(clock64() - ck2));
+    }
+#endif
     if (tid == 0)  // how the tile got its S_out, for BGC_K3_STATS: [1] first of a segment, [2] IDENT, [3] AGG2 fitted, [4] AGG fitted, [5] walked
       atomicAdd(C.ticket + (c == first ? 1 : ident ? 2 : early && agg2 ? 3 : early ? 4 : 5), 1u);
-    if (c == last && tid == 0) {
+    if (is_last && tid == 0) {
 #pragma unroll
       for (int r = 0; r < R; ++r) used[(size_t)r * NS + ns] = S[r];
     }
