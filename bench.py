@@ -419,7 +419,8 @@ def k3_record(torch, bgc, eng, oracle, Q, wl, seed, peak):
                      "admitted_fraction": float((v[::101] == 0).float().mean())}
         del ns, req, v
     return {"kernel": "k3_admit_greedy", "algorithmic_bytes_per_pod": 4 + 8 * R + 1, **out,
-            "parity": "bit-exact vs the literal loop in tests/test_gpu_greedy.py (not re-checked at this size)"}
+            "long_segments": os.environ.get("BGC_K3_LONG", "chain"),
+            "parity": "bit-exact vs the literal loop in tests/test_gpu_greedy.py; at this size by tools/greedy_probe.py --verify (profiles/r02_greedy_n1_chain.jsonl), not re-checked in this run"}
 
 
 def crossover_record(torch, bgc, eng, oracle, Q, seed, cores):
