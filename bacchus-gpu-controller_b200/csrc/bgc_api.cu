@@ -636,7 +636,7 @@ int bounced(bgc_ctx* ctx, const BounceCol* cols, int ncols, const BounceOut* out
 // =============================================================================== C ABI
 extern "C" {
 
-const char* bgc_version(void) { return "bgc 0.4 (sm_100a)"; }
+const char* bgc_version(void) { return "bgc 0.5 (sm_100a)"; }
 
 int bgc_ctx_create(int device, bgc_ctx** out) {
   if (!out) return BGC_E_BADARG;

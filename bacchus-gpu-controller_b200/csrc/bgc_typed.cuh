@@ -86,6 +86,21 @@ __device__ __forceinline__ void ld_col_typed(const TCol& c, size_t base, long lo
     if (c.type == T_U16) ld_u16xN<PODS>(c.p, base, t);
     else if (c.type == T_U8) ld_u8xN<PODS>(c.p, base, t);
     else ldg_ns<PODS>(static_cast<const uint32_t*>(c.p) + base, t);
+    // element << shift as ONE wide multiply by 2^shift (a 64-bit shift by a run-time amount is five instructions:
+    // ncu counted 105 thread instructions per pod in the typed K2 against 66 in the int64 one, SHF / SEL / ISETP on top).
+    // The branches are uniform over the grid.
+    if (c.type != T_I32 && c.shift < 32u) {
+      const uint32_t m = 1u << c.shift;
+#pragma unroll
+      for (int k = 0; k < PODS; ++k) v[k] = (long long)((unsigned long long)t[k] * m);
+      return;
+    }
+    if (c.type == T_I32 && c.shift < 31u) {
+      const int m = 1 << c.shift;
+#pragma unroll
+      for (int k = 0; k < PODS; ++k) v[k] = (long long)(int)t[k] * m;
+      return;
+    }
 #pragma unroll
     for (int k = 0; k < PODS; ++k) v[k] = c.type == T_I32 ? (long long)(int)t[k] : (long long)t[k];
   }

@@ -133,6 +133,27 @@ while time.time() < t_end:
             assert np.array_equal(d_ns.cpu().numpy().view(np.uint32), local_of[src[0][keep]]) and np.array_equal(d_sx.cpu().numpy(), keep + first)
             assert all(np.array_equal(d_rq[r].cpu().numpy(), src[1][r][keep]) for r in range(Rg)) and np.array_equal(d_mk.cpu().numpy(), src[2][keep])
         stats["shard_gen"] = stats.get("shard_gen", 0) + 1
+    if it % 11 == 0:       # long segments: the chained-tile walker (hundreds of 1024-pod tiles per namespace)
+        Rl = int(rng.integers(1, 5)); NSl = int(rng.integers(1, 6)); nl = int(rng.integers(40_000, 1_500_000))
+        nsl = rng.integers(0, NSl, nl, dtype=np.uint32) if rng.random() < 0.7 else np.sort(rng.integers(0, NSl, nl, dtype=np.uint32))
+        sizes = rng.choice(np.array([0, 0, 1, 2, 3, 7, 50, 250, 1000, 4000, 1 << 20, 1 << 33, 1 << 40], np.int64), int(rng.integers(2, 9)))
+        reql = [rng.choice(sizes, nl) for _ in range(Rl)]
+        if rng.random() < 0.3:      # a few requests outside the monotone range
+            for c in reql:
+                c[rng.integers(0, nl, int(rng.integers(1, 40)))] = rng.choice(np.array([-1, -5000, (1 << 40) + 1, -(1 << 50)], np.int64))
+        maskl = rng.integers(0, 256, nl, dtype=np.uint8) | np.uint8(rng.integers(0, 16)) if rng.random() < 0.6 else None
+        tot = oracle.usage_reduce(nsl, reql, NSl, threads=4)
+        frac = float(rng.choice([0.0, 0.01, 0.3, 0.9, 1.0, 3.0]))
+        hardl = (np.abs(tot).astype(np.float64) * frac).astype(np.int64) + int(rng.integers(0, 3))
+        hml = rng.integers(0, 1 << Rl, NSl, dtype=np.uint8) if rng.random() < 0.5 else np.full(NSl, (1 << Rl) - 1, np.uint8)
+        used0 = (hardl * float(rng.choice([0.0, 0.5, 0.999, 1.2]))).astype(np.int64)
+        unitsl = [int(x) for x in rng.integers(0, 3, Rl)]
+        eng.quota_table_set(hardl, hml, unitsl); eng.usage_set(used0)
+        cml = sum(1 << r for r, u in enumerate(unitsl) if u)
+        gv, gu = oracle.admit_greedy(nsl, reql, maskl, NSl, used0, hardl, hml, cml)
+        assert np.array_equal(eng.admit_greedy(nsl, reql, maskl), gv), f"K3 long-segment verdict mismatch seed={seed} R={Rl} NS={NSl} n={nl}"
+        assert np.array_equal(eng.usage_get(), gu), f"K3 long-segment usage mismatch seed={seed}"
+        stats["k3_long"] = stats.get("k3_long", 0) + 1
     if it % 5 == 0:
         m = int(rng.integers(1, 200_000))
         op = rng.integers(0, 256, m, dtype=np.uint8); fl = rng.integers(0, 65536, m, dtype=np.uint16)
