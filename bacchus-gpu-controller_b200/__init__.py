@@ -53,7 +53,7 @@ EXPORTS = [
     "bgc_sheet_infer_header", "bgc_sheet_parse_csv", "bgc_sheet_destroy", "bgc_sheet_row_count", "bgc_sheet_skipped_rows",
     "bgc_sheet_get_row", "bgc_sheet_match", "bgc_sheet_row_quota",
     "bgc_review_parse", "bgc_review_destroy", "bgc_review_has_request", "bgc_review_uid", "bgc_review_kind",
-    "bgc_review_request", "bgc_review_pod", "bgc_render_review_response", "bgc_handle_reviews",
+    "bgc_review_request", "bgc_review_pod", "bgc_render_review_response", "bgc_handle_reviews", "bgc_handle_pod_reviews",
     "bgc_format_quantity", "bgc_render_quota_denial",
     "bgc_reconcile_plan", "bgc_plan_destroy", "bgc_plan_count", "bgc_plan_item", "bgc_plan_requeue_seconds",
 ]

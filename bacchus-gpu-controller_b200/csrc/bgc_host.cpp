@@ -5,6 +5,7 @@
 // (ns_id, req[r], req_mask) columns K1/K2 consume.  Plain C++17, no CUDA in this file; the only
 // device work is reached through the C ABI (bgc_policy_eval).
 #include <chrono>
+#include <deque>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -982,7 +983,7 @@ struct bgc_review {
   const JVal* request = nullptr;
   std::vector<const char*> groups;
   // pod view
-  std::vector<std::vector<const char*>> name_store, quant_store;
+  std::deque<std::vector<const char*>> name_store, quant_store;  // a deque never moves its elements: lists handed out stay put
   std::vector<bgc_container_spec> containers, init_containers;
   bgc_resource_list overhead{};
   bool has_overhead = false;
@@ -1107,8 +1108,6 @@ int bgc_review_pod(const bgc_review* rc, bgc_pod_spec* out) {
   const JVal* obj = r->request->get_obj("object");
   if (!obj) return BGC_E_BADARG;
   r->name_store.clear(); r->quant_store.clear();
-  // the stores must not reallocate while pointers into them are handed out
-  r->name_store.reserve(4096); r->quant_store.reserve(4096);
   const JVal* spec = obj->get_obj("spec");
   const JVal* meta = obj->get_obj("metadata");
   const char* ns = r->request->get_str("namespace");
@@ -1292,77 +1291,243 @@ extern "C" int bgc_handle_reviews(bgc_ctx* ctx, const bgc_admission_config* cfg,
   using clk = std::chrono::steady_clock;
   auto ns_since = [](clk::time_point t0) { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - t0).count(); };
   auto t0 = clk::now();
-  std::vector<bgc_review*> rv(n, nullptr);
+  // One pass per body, all in the thread that parsed it: parse, the fields mutate() reads, their predicate bits
+  // (row A2), copies of the three strings a response can need, release of the tree.  (Freeing 10k trees after the
+  // batch cost more than parsing them, even spread over the cores.)
+  struct Kept {
+    std::string uid, username, spec_user;
+    bool has_username = false, has_spec_user = false;
+  };
+  std::vector<uint8_t> state(n, 0);  // 0 malformed, 1 no request, 2 decided below
+  std::vector<Kept> kept(n);
+  std::vector<uint8_t> op_all(n ? n : 1);
+  std::vector<uint16_t> flags_all(n ? n : 1);
+  int rc = BGC_OK;
 #pragma omp parallel for schedule(dynamic, 64) if (n >= 256)
-  for (long long i = 0; i < (long long)n; ++i) rv[i] = bodies[i] ? bgc_review_parse(bodies[i], body_len[i], nullptr, 0) : nullptr;
+  for (long long i = 0; i < (long long)n; ++i) {
+    bgc_review* r = bodies[i] ? bgc_review_parse(bodies[i], body_len[i], nullptr, 0) : nullptr;
+    if (!r) continue;
+    state[i] = 1;
+    bgc_admission_request q;
+    if (bgc_review_has_request(r) && bgc_review_request(r, &q) == BGC_OK) {
+      const int e = bgc_flatten_requests(cfg, &q, 1, &op_all[i], &flags_all[i]);
+      if (e != BGC_OK) {
+#pragma omp atomic write
+        rc = e;
+      } else {
+        state[i] = 2;
+        Kept& k = kept[i];
+        k.uid = bgc_review_uid(r);
+        if (q.username) { k.username = q.username; k.has_username = true; }
+        if (q.spec_kube_username) { k.spec_user = q.spec_kube_username; k.has_spec_user = true; }
+      }
+    }
+    bgc_review_destroy(r);
+  }
+  if (rc) return rc;
   const uint64_t t_parse = ns_since(t0);
   t0 = clk::now();
   std::vector<size_t> live;
   live.reserve(n);
   for (size_t i = 0; i < n; ++i)
-    if (rv[i] && bgc_review_has_request(rv[i])) live.push_back(i);
-  std::vector<bgc_admission_request> reqs(live.size());
-  std::vector<bgc_admission_response> resp(live.size());
-#pragma omp parallel for schedule(static) if (live.size() >= 256)
-  for (long long k = 0; k < (long long)live.size(); ++k) bgc_review_request(rv[live[k]], &reqs[k]);
-  int rc = live.empty() ? BGC_OK : bgc_mutate_batch(ctx, cfg, reqs.data(), live.size(), resp.data());
-  const uint64_t t_decide = ns_since(t0);
-  uint64_t t_patch = 0, t_render = 0;
-  int bad_render = 0;
-  std::vector<std::string> text(n);
-  if (rc == BGC_OK) {
-    t0 = clk::now();
-    std::vector<std::string> patch(live.size());
-#pragma omp parallel for schedule(static) if (live.size() >= 256)
-    for (long long k = 0; k < (long long)live.size(); ++k)
-      if (resp[k].patch_mask) {
-        std::string buf(1024, '\0');
-        long m;
-        while ((m = bgc_render_patch(cfg, &reqs[k], resp[k].patch_mask, &buf[0], buf.size())) == BGC_E_BADARG && buf.size() < (1u << 24))
-          buf.resize(buf.size() * 4);
-        if (m > 0) patch[k].assign(buf.data(), (size_t)m);
-        else
-#pragma omp atomic write
-          bad_render = 1;  // a patch that was asked for and did not come out fails the call, never a response without it
-      }
-    t_patch = ns_since(t0);
-    t0 = clk::now();
-    std::vector<long long> slot(n, -1);
-    for (size_t k = 0; k < live.size(); ++k) slot[live[k]] = (long long)k;
-#pragma omp parallel for schedule(static) if (n >= 256)
-    for (long long i = 0; i < (long long)n; ++i) {
-      std::string buf(1024, '\0');
-      long m;
-      for (;;) {
-        if (slot[i] >= 0) {
-          const size_t k = (size_t)slot[i];
-          m = bgc_render_review_response(bgc_review_uid(rv[i]), &resp[k], nullptr, patch[k].empty() ? nullptr : patch[k].c_str(), &buf[0], buf.size());
-        } else {
-          const bgc_admission_response bad = {0, BGC_INVALID, 0, 0, nullptr};
-          m = bgc_render_review_response("", &bad, rv[i] ? "invalid request: AdmissionReview carries no request" : "malformed AdmissionReview",
-                                         nullptr, &buf[0], buf.size());
-        }
-        if (m != BGC_E_BADARG || buf.size() >= (1u << 24)) break;
-        buf.resize(buf.size() * 4);
-      }
-      if (m > 0) text[i].assign(buf.data(), (size_t)m);
-    }
-    t_render = ns_since(t0);
-  }
-  t0 = clk::now();
-#pragma omp parallel for schedule(dynamic, 64) if (n >= 256)
-  for (long long i = 0; i < (long long)n; ++i) bgc_review_destroy(rv[i]);  // the parsed trees: as many frees as the parse made allocations
+    if (state[i] == 2) live.push_back(i);
+  const size_t m = live.size();
+  std::vector<uint8_t> op(m ? m : 1), code(m ? m : 1), pm(m ? m : 1);
+  std::vector<uint16_t> flags(m ? m : 1);
+  for (size_t k = 0; k < m; ++k) { op[k] = op_all[live[k]]; flags[k] = flags_all[live[k]]; }
+  if (m) rc = bgc_policy_eval(ctx, op.data(), flags.data(), m, code.data(), pm.data());  // one K0 launch
   if (rc) return rc;
+  const uint64_t t_decide = ns_since(t0);
+  t0 = clk::now();
+  std::vector<long long> slot(n, -1);
+  for (size_t k = 0; k < m; ++k) slot[live[k]] = (long long)k;
+  std::vector<std::string> text(n);
+  int bad_render = 0;
+#pragma omp parallel for schedule(static) if (n >= 256)
+  for (long long i = 0; i < (long long)n; ++i) {
+    bgc_admission_response resp = {0, BGC_INVALID, 0, 0, nullptr};
+    const char* uid = "";
+    const char* msg = nullptr;
+    std::string patch;
+    bool fail = false;
+    if (slot[i] < 0) {
+      msg = state[i] ? "invalid request: AdmissionReview carries no request" : "malformed AdmissionReview";
+    } else {
+      const size_t k = (size_t)slot[i];
+      resp.klass = code[k] >> 4;
+      resp.reason = code[k] & 15;
+      resp.patch_mask = pm[k];
+      resp.allowed = resp.klass <= BGC_ALLOW_PATCH;
+      resp.message = bgc_reason_message(resp.reason);
+      uid = kept[i].uid.c_str();
+      if (resp.patch_mask) {  // the patch reads two strings of the request only (src/admission.rs:354-357,387-416)
+        bgc_admission_request q;
+        std::memset(&q, 0, sizeof q);
+        q.username = kept[i].has_username ? kept[i].username.c_str() : nullptr;
+        q.spec_kube_username = kept[i].has_spec_user ? kept[i].spec_user.c_str() : nullptr;
+        std::string buf(1024, '\0');
+        long len;
+        while ((len = bgc_render_patch(cfg, &q, resp.patch_mask, &buf[0], buf.size())) == BGC_E_BADARG && q.username && buf.size() < (1u << 24))
+          buf.resize(buf.size() * 4);
+        if (len > 0) patch.assign(buf.data(), (size_t)len);
+        else fail = true;  // a patch that was asked for and did not come out fails the call, never a response without it
+      }
+    }
+    std::string buf(1024, '\0');
+    long len = -1;
+    while (!fail && (len = bgc_render_review_response(uid, &resp, msg, patch.empty() ? nullptr : patch.c_str(), &buf[0], buf.size())) == BGC_E_BADARG &&
+           buf.size() < (1u << 24))
+      buf.resize(buf.size() * 4);
+    if (len > 0) text[i].assign(buf.data(), (size_t)len);
+    else
+#pragma omp atomic write
+      bad_render = 1;
+  }
   if (bad_render) return BGC_E_BADARG;
+  const uint64_t t_render = ns_since(t0);
+  t0 = clk::now();
   size_t need = 0;
   for (size_t i = 0; i < n; ++i) {
-    if (text[i].empty()) return BGC_E_BADARG;  // a response did not fit the render buffer
     out_off[i] = need;
     need += text[i].size() + 1;
   }
   out_off[n] = need;
   if (need > out_cap) return BGC_E_BADARG;
   for (size_t i = 0; i < n; ++i) std::memcpy(out + out_off[i], text[i].c_str(), text[i].size() + 1);
-  if (stage_ns) { stage_ns[0] = t_parse; stage_ns[1] = t_decide; stage_ns[2] = t_patch; stage_ns[3] = t_render; stage_ns[4] = ns_since(t0); }
+  if (stage_ns) { stage_ns[0] = t_parse; stage_ns[1] = t_decide; stage_ns[2] = t_render; stage_ns[3] = ns_since(t0); }
+  return BGC_OK;
+}
+
+// ---- Pod-create reviews, wire bytes to wire bytes (no reference counterpart; same seam as above) ------------------
+extern "C" int bgc_handle_pod_reviews(bgc_ctx* ctx, const char* const* bodies, const size_t* body_len, size_t n,
+                                      const char* const* quota_keys, const uint8_t* unit, uint32_t R, bgc_nsmap* map, int wide,
+                                      const int64_t* used, const int64_t* hard, uint32_t ns_count, char* out, size_t out_cap,
+                                      size_t* out_off, uint64_t* stage_ns) {
+  if (!ctx || (n && (!bodies || !body_len)) || !quota_keys || !unit || !map || R < 1 || R > BGC_MAX_R || !out_off || (!out && out_cap))
+    return BGC_E_BADARG;
+  if (!wide && R > 4) return BGC_E_BADARG;
+  using clk = std::chrono::steady_clock;
+  auto ns_since = [](clk::time_point t0) { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - t0).count(); };
+  auto t0 = clk::now();
+  // one pass per body, all in the thread that parsed it: parse, pod spec, flatten (row A5) into row i, keep the uid,
+  // release the tree (10k trees freed after the batch, even in parallel, cost more than parsing them)
+  std::vector<uint8_t> state(n, 0);  // 0 malformed, 1 no pod object, 2 has a row
+  std::vector<std::string> uid_of(n);
+  std::vector<uint32_t> ns_all(n ? n : 1);
+  std::vector<std::vector<int64_t>> req_all(R, std::vector<int64_t>(n ? n : 1));
+  std::vector<uint8_t> mask_all(n ? n : 1);
+  int rc = BGC_OK;
+#pragma omp parallel for schedule(dynamic, 64) if (n >= 256)
+  for (long long i = 0; i < (long long)n; ++i) {
+    bgc_review* r = bodies[i] ? bgc_review_parse(bodies[i], body_len[i], nullptr, 0) : nullptr;
+    if (!r) continue;
+    bgc_pod_spec spec;
+    state[i] = 1;
+    if (bgc_review_pod(r, &spec) == BGC_OK) {
+      int64_t* row[BGC_MAX_R];
+      for (uint32_t q = 0; q < R; ++q) row[q] = req_all[q].data() + i;
+      size_t wrote = 0;
+      int e = bgc_flatten_pods(&spec, 1, quota_keys, unit, R, map, 0, ns_all.data() + i, row, mask_all.data() + i, &wrote);
+      if (e == BGC_OK && wrote != 1) e = BGC_E_BADARG;  // terminal pods cannot appear in create reviews
+      if (e != BGC_OK) {
+#pragma omp atomic write
+        rc = e;
+      } else {
+        state[i] = 2;
+        uid_of[i] = bgc_review_uid(r);
+      }
+    }
+    bgc_review_destroy(r);
+  }
+  const uint64_t t_parse = ns_since(t0);
+  t0 = clk::now();
+  std::vector<size_t> live;
+  live.reserve(n);
+  for (size_t i = 0; i < n; ++i)
+    if (state[i] == 2) live.push_back(i);
+  const size_t m = live.size();
+  std::vector<uint32_t> ns_id(m ? m : 1);
+  std::vector<std::vector<int64_t>> req(R, std::vector<int64_t>(m ? m : 1));
+  std::vector<const int64_t*> reqc(R);
+  std::vector<uint8_t> mask(m ? m : 1);
+  for (size_t k = 0; k < m; ++k) {
+    ns_id[k] = ns_all[live[k]];
+    mask[k] = mask_all[live[k]];
+    for (uint32_t q = 0; q < R; ++q) req[q][k] = req_all[q][live[k]];
+  }
+  for (uint32_t q = 0; q < R; ++q) reqc[q] = req[q].data();
+  const uint64_t t_flat = ns_since(t0);
+  t0 = clk::now();
+  std::vector<uint16_t> v16(wide && m ? m : 1);
+  std::vector<uint8_t> v8(!wide && m ? m : 1);
+  if (rc == BGC_OK && m)
+    rc = wide ? bgc_quota_eval16(ctx, ns_id.data(), reqc.data(), mask.data(), m, v16.data())
+              : bgc_quota_eval(ctx, ns_id.data(), reqc.data(), mask.data(), m, v8.data());
+  const uint64_t t_eval = ns_since(t0);
+  t0 = clk::now();
+  std::vector<std::string> text(n);
+  int bad_render = 0;
+  if (rc == BGC_OK) {
+    std::vector<long long> slot(n, -1);
+    for (size_t k = 0; k < m; ++k) slot[live[k]] = (long long)k;
+    const unsigned unknown = wide ? 0xFFFFu : 0xFFu;
+#pragma omp parallel for schedule(static) if (n >= 256)
+    for (long long i = 0; i < (long long)n; ++i) {
+      bgc_admission_response resp = {0, BGC_DENY, 0, 0, nullptr};
+      std::string msg;
+      const char* uid = "";
+      if (slot[i] < 0) {
+        resp.klass = BGC_INVALID;
+        msg = state[i] ? "invalid request: AdmissionReview carries no pod object" : "malformed AdmissionReview";
+      } else {
+        const size_t k = (size_t)slot[i];
+        const unsigned v = wide ? v16[k] : v8[k];
+        uid = uid_of[i].c_str();
+        if (v == 0) {
+          resp.allowed = 1; resp.klass = BGC_ALLOW;
+        } else if (v == unknown) {
+          msg = "namespace is not known to the quota engine";
+        } else if (!used || !hard || ns_id[k] >= ns_count) {
+          msg = "exceeded quota";
+        } else {
+          int64_t q[BGC_MAX_R], u[BGC_MAX_R], h[BGC_MAX_R];
+          for (uint32_t r = 0; r < R; ++r) {
+            q[r] = req[r][k];
+            u[r] = used[(size_t)r * ns_count + ns_id[k]];
+            h[r] = hard[(size_t)r * ns_count + ns_id[k]];
+          }
+          std::string buf(1024, '\0');
+          long len;
+          while ((len = bgc_render_quota_denial(v, wide, bgc_nsmap_name(map, ns_id[k]), quota_keys, unit, R, q, u, h, &buf[0], buf.size())) == BGC_E_BADARG &&
+                 buf.size() < (1u << 20))
+            buf.resize(buf.size() * 4);
+          if (len > 0) msg.assign(buf.data(), (size_t)len);
+          else msg = "exceeded quota";
+        }
+      }
+      std::string buf(1024, '\0');
+      long len;
+      while ((len = bgc_render_review_response(uid, &resp, resp.allowed ? nullptr : msg.c_str(), nullptr, &buf[0], buf.size())) == BGC_E_BADARG &&
+             buf.size() < (1u << 24))
+        buf.resize(buf.size() * 4);
+      if (len > 0) text[i].assign(buf.data(), (size_t)len);
+      else
+#pragma omp atomic write
+        bad_render = 1;
+    }
+  }
+  const uint64_t t_render = ns_since(t0);
+  t0 = clk::now();
+  if (rc) return rc;
+  if (bad_render) return BGC_E_BADARG;
+  size_t need = 0;
+  for (size_t i = 0; i < n; ++i) {
+    out_off[i] = need;
+    need += text[i].size() + 1;
+  }
+  out_off[n] = need;
+  if (need > out_cap) return BGC_E_BADARG;
+  for (size_t i = 0; i < n; ++i) std::memcpy(out + out_off[i], text[i].c_str(), text[i].size() + 1);
+  if (stage_ns) { stage_ns[0] = t_parse; stage_ns[1] = t_flat; stage_ns[2] = t_eval; stage_ns[3] = t_render; stage_ns[4] = ns_since(t0); }
   return BGC_OK;
 }

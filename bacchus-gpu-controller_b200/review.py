@@ -24,6 +24,10 @@ lib.bgc_review_kind.argtypes = [C.c_void_p]
 lib.bgc_review_request.argtypes = [C.c_void_p, C.POINTER(_CRequest)]
 lib.bgc_review_pod.argtypes = [C.c_void_p, C.POINTER(_Pod)]
 lib.bgc_render_review_response.restype = C.c_long
+lib.bgc_handle_pod_reviews.restype = C.c_int
+lib.bgc_handle_pod_reviews.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_size_t, C.POINTER(C.c_char_p), C.c_void_p, C.c_uint32,
+                                       C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                       C.POINTER(C.c_uint64)]
 lib.bgc_handle_reviews.restype = C.c_int
 lib.bgc_handle_reviews.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_size_t, C.c_char_p, C.c_size_t,
                                    C.POINTER(C.c_size_t), C.POINTER(C.c_uint64)]
@@ -108,18 +112,14 @@ def handle_reviews(engine: Engine, config: AdmissionConfig, bodies: Sequence[byt
     """Batched `mutate_handler` (src/admission.rs:184-204): one response JSON string per request body, through
     ONE C call (bgc_handle_reviews: parse, flatten, one K0 launch, render).  Reviews without a `request` and
     bodies that do not parse are answered `invalid` on their own like :189-197.  `stage_ms`, when given, is
-    filled with the host time of the five stages."""
-    raw = [b.encode() if isinstance(b, str) else b for b in bodies]
-    n = len(raw)
+    filled with the host time of the four stages."""
+    n = len(bodies)
     if n == 0:
         return []
-    blob = b"".join(raw)                                   # one buffer, pointers computed from the lengths
-    lens = np.fromiter(map(len, raw), np.uint64, n)
-    base = C.cast(C.c_char_p(blob), C.c_void_p).value or 0
-    ptrs = base + np.concatenate([np.zeros(1, np.uint64), np.cumsum(lens[:-1], dtype=np.uint64)])
+    blob, ptrs, lens = _marshal_bodies(bodies)
     cap = len(blob) // 2 + 768 * n + 64
     off = np.zeros(n + 1, np.uint64)
-    stages = (C.c_uint64 * 5)()
+    stages = (C.c_uint64 * 4)()
     cc, keep = config._c()
     for _ in range(2):
         buf = np.empty(cap, np.uint8)
@@ -130,7 +130,7 @@ def handle_reviews(engine: Engine, config: AdmissionConfig, bodies: Sequence[byt
         cap = int(off[n])      # the call reported the size it needs
     engine._ck(rc)
     if stage_ms is not None:
-        stage_ms.update(zip(("parse", "flatten_decide", "patch", "render", "release_copy"), (s / 1e6 for s in stages)))
+        stage_ms.update(zip(("parse_flatten_release", "decide", "render", "copy"), (s / 1e6 for s in stages)))
     return buf[:int(off[n]) - 1].tobytes().decode().split("\0")   # responses are JSON text: no NUL inside one
 
 
@@ -187,12 +187,68 @@ def flatten_pod_reviews(bodies: Sequence[bytes | str], quota_keys: Sequence[str]
     return ns_id[:m].copy(), [c[:m].copy() for c in req], mask[:m].copy(), unit
 
 
-def handle_pod_reviews(engine, bodies: Sequence[bytes | str], quota_keys: Sequence[str], nsmap, used=None, hard=None, wide: bool | None = None) -> list:
-    """Pod-create AdmissionReviews, wire bytes to wire bytes: parse -> flatten (row A5) -> snapshot
-    verdicts on the GPU (K2) -> AdmissionReview responses, denied pods carrying the message
-    kube-apiserver's ResourceQuota plugin would give (`pods.quota_denial_message`).  `used` / `hard`
-    ([R][NS] arrays) are only needed for the denial text; pass None to get bare allow/deny.
-    Not a reference path: the reference's webhook never sees pods."""
+def _marshal_bodies(bodies):
+    """bodies -> (blob kept alive, pointer array, length array) for the one-call handlers"""
+    raw = [b.encode() if isinstance(b, str) else b for b in bodies]
+    n = len(raw)
+    blob = b"".join(raw)                                   # one buffer, pointers computed from the lengths
+    lens = np.fromiter(map(len, raw), np.uint64, n)
+    base = C.cast(C.c_char_p(blob), C.c_void_p).value or 0
+    ptrs = base + np.concatenate([np.zeros(1, np.uint64), np.cumsum(lens[:-1], dtype=np.uint64)])
+    return blob, ptrs, lens
+
+
+def handle_pod_reviews(engine, bodies: Sequence[bytes | str], quota_keys: Sequence[str], nsmap, used=None, hard=None, wide: bool | None = None,
+                       stage_ms: dict | None = None) -> list:
+    """Pod-create AdmissionReviews, wire bytes to wire bytes, through ONE C call (bgc_handle_pod_reviews): parse ->
+    flatten (row A5) -> snapshot verdicts on the GPU (K2) -> AdmissionReview responses, denied pods carrying the
+    message kube-apiserver's ResourceQuota plugin would give.  `used` / `hard` ([R][NS] arrays) are only needed for
+    the denial text; pass None to get bare allow/deny.  An `engine` that is not a real Engine (the CPU tests' stand-in)
+    takes the call-by-call form.  Not a reference path: the reference's webhook never sees pods."""
+    from .pods import QUOTA_KEYS
+    if not isinstance(engine, Engine):
+        return handle_pod_reviews_stepwise(engine, bodies, quota_keys, nsmap, used, hard, wide)
+    R = len(quota_keys)
+    if wide is None:
+        wide = R > 4
+    n = len(bodies)
+    if n == 0:
+        return []
+    blob, ptrs, lens = _marshal_bodies(bodies)
+    keys = (C.c_char_p * R)(*[k.encode() for k in quota_keys])
+    unit = np.array([QUOTA_KEYS[k] for k in quota_keys], np.uint8)
+    u = h = None
+    ns_count = 0
+    if used is not None and hard is not None:
+        u, h = np.ascontiguousarray(used, dtype=np.int64), np.ascontiguousarray(hard, dtype=np.int64)
+        if u.shape != h.shape or u.ndim != 2 or u.shape[0] != R:
+            raise ValueError("used / hard must be [R][NS] arrays")
+        ns_count = u.shape[1]
+    cap = len(blob) // 4 + 1024 * n + 64
+    off = np.zeros(n + 1, np.uint64)
+    stages = (C.c_uint64 * 5)()
+    for _ in range(2):
+        buf = np.empty(cap, np.uint8)
+        rc = lib.bgc_handle_pod_reviews(engine._h, ptrs.ctypes.data_as(C.POINTER(C.c_char_p)), lens.ctypes.data_as(C.POINTER(C.c_size_t)), C.c_size_t(n),
+                                        keys, C.c_void_p(unit.ctypes.data), C.c_uint32(R), nsmap._h, C.c_int(int(bool(wide))),
+                                        C.c_void_p(u.ctypes.data if u is not None else 0), C.c_void_p(h.ctypes.data if h is not None else 0),
+                                        C.c_uint32(ns_count), buf.ctypes.data_as(C.c_char_p), C.c_size_t(cap),
+                                        off.ctypes.data_as(C.POINTER(C.c_size_t)), stages)
+        if rc == 0 or int(off[n]) <= cap:
+            break
+        cap = int(off[n])
+    if rc == -1 and int(off[n]) == 0:
+        raise ValueError("bgc_handle_pod_reviews: bad argument (a terminal pod in a create review, or R / wide do not match)")
+    engine._ck(rc)
+    if stage_ms is not None:
+        stage_ms.update(zip(("parse_flatten_release", "gather", "verdicts", "render", "copy"), (s / 1e6 for s in stages)))
+    return buf[:int(off[n]) - 1].tobytes().decode().split("\0")
+
+
+def handle_pod_reviews_stepwise(engine, bodies: Sequence[bytes | str], quota_keys: Sequence[str], nsmap, used=None, hard=None, wide: bool | None = None) -> list:
+    """The same handler call by call (bgc_review_parse / bgc_review_pod / bgc_flatten_pods / engine.quota_eval /
+    bgc_render_quota_denial / bgc_render_review_response): the cross-check of the one-call form, and the form the CPU
+    tests drive with a stand-in engine."""
     from .pods import quota_denial_message
     R = len(quota_keys)
     if wide is None:

@@ -187,17 +187,32 @@ int bgc_review_request(const bgc_review *r, bgc_admission_request *out);
  * object.metadata.namespace); pointers valid until bgc_review_destroy */
 int bgc_review_pod(const bgc_review *r, bgc_pod_spec *out);
 
-/* The batched mutate_handler (src/admission.rs:184-204) in ONE call, wire bytes to wire bytes: every body is parsed
- * (OpenMP over the batch), the requests are flattened, decided in one K0 launch (bgc_mutate_batch) and rendered.
- * A body that is not a well-formed AdmissionReview, or carries no `request`, is answered `invalid` on its own,
- * as the reference's handler rejects only the offending request (:189-197).  The responses are written back to
- * back into `out` (NUL-terminated each); out_off[i] = offset of response i, out_off[n] = bytes used.  Returns
- * BGC_E_BADARG when `out` is too small (out_off[n] then holds the size needed).  stage_ns (optional, 5 values):
- * host time of parse, flatten + decide, patch rendering, response rendering, and releasing the parsed trees +
- * copying the responses out. */
+/* The batched mutate_handler (src/admission.rs:184-204) in ONE call, wire bytes to wire bytes.  One pass per body
+ * (OpenMP over the batch, everything in the thread that parsed it): parse, the fields mutate() reads, their predicate
+ * bits (row A2), release of the parsed tree; then one K0 launch (bgc_policy_eval) over the batch; then the responses,
+ * patches included.  A body that is not a well-formed AdmissionReview, or carries no `request`, is answered `invalid`
+ * on its own, as the reference's handler rejects only the offending request (:189-197).  The responses are written
+ * back to back into `out` (NUL-terminated each); out_off[i] = offset of response i, out_off[n] = bytes used.
+ * Returns BGC_E_BADARG when `out` is too small (out_off[n] then holds the size needed).  stage_ns (optional, 4
+ * values): host time of the per-body pass, the decision (gather + K0), rendering, copy-out. */
 int bgc_handle_reviews(bgc_ctx *ctx, const bgc_admission_config *cfg, const char *const *bodies,
                        const size_t *body_len, size_t n, char *out, size_t out_cap, size_t *out_off,
                        uint64_t *stage_ns);
+
+/* Pod-create AdmissionReviews wire to wire in ONE call: parse (OpenMP) -> bgc_review_pod -> bgc_flatten_pods (row A5)
+ * -> snapshot verdicts on the GPU (bgc_quota_eval, or bgc_quota_eval16 when wide != 0) -> responses, a denied pod
+ * carrying bgc_render_quota_denial's message when used / hard ([R][ns_count], as given to bgc_quota_table_set /
+ * read by bgc_usage_get) are passed, else "exceeded quota".  Not a reference path: the reference's webhook never sees
+ * pods; the seam is the same handler, src/admission.rs:184-204.  A body that does not parse, or
+ * carries no pod object, is answered `invalid` on its own; a pod of a namespace the map does not know is denied.
+ * Output layout as bgc_handle_reviews; stage_ns (optional, 5 values): the per-body pass (parse, pod spec, flatten into
+ * the body's row, release of the parsed tree — all in the thread that parsed it), gathering the rows, verdicts,
+ * rendering, copy-out.
+ * The quota table of `ctx` must be set for `quota_keys`' columns.  A terminal pod in a create review -> BGC_E_BADARG. */
+int bgc_handle_pod_reviews(bgc_ctx *ctx, const char *const *bodies, const size_t *body_len, size_t n,
+                           const char *const *quota_keys, const uint8_t *unit, uint32_t R, bgc_nsmap *map, int wide,
+                           const int64_t *used, const int64_t *hard, uint32_t ns_count, char *out, size_t out_cap,
+                           size_t *out_off, uint64_t *stage_ns);
 
 /* AdmissionReview response text for one decision.  patch_json = bgc_render_patch output or NULL.
  * allow   → {"uid","allowed":true,"status":{}} (+ "patch": base64, "patchType":"JSONPatch")

@@ -157,6 +157,19 @@ def test_pod_reviews_wire_to_wire_on_the_device(bgc, engine, oracle, wide):
         resp = json.loads(outs[i])["response"]
         assert resp["allowed"] is False and resp["status"]["reason"] == "InvalidRequest" and resp["uid"] == ""
     assert 0.02 < float(np.mean(want != 0)) < 0.999
+    # the one-call form (bgc_handle_pod_reviews) answers byte for byte like the call-by-call form
+    stages = {}
+    assert bgc.review.handle_pod_reviews(engine, bodies, keys, m, used, hard, wide=wide, stage_ms=stages) == \
+        bgc.review.handle_pod_reviews_stepwise(engine, bodies, keys, m, used, hard, wide=wide)
+    assert set(stages) == {"parse_flatten_release", "gather", "verdicts", "render", "copy"}
+    few = bodies[:7] + bodies[98:102]                              # below the OpenMP threshold, no denial text
+    assert bgc.review.handle_pod_reviews(engine, few, keys, m, wide=wide) == bgc.review.handle_pod_reviews_stepwise(engine, few, keys, m, wide=wide)
+    assert bgc.review.handle_pod_reviews(engine, [], keys, m, used, hard, wide=wide) == []
+    done = dict(pods[3]); done["status"] = {"phase": "Succeeded"}
+    gone = json.dumps({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview",
+                       "request": {"uid": "t", "operation": "CREATE", "kind": {"kind": "Pod"}, "namespace": done["metadata"]["namespace"], "object": done}})
+    with pytest.raises(ValueError):
+        bgc.review.handle_pod_reviews(engine, [gone], keys, m, used, hard, wide=wide)   # a terminal pod is not a create review
 
 
 def test_c1_pods_through_compact_columns(bgc, engine, oracle):

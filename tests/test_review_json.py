@@ -111,7 +111,7 @@ def test_one_call_handler_equals_the_stepwise_handler(bgc, engine):
     got = bgc.review.handle_reviews(engine, cfg, bodies, stage_ms=stages)
     want = bgc.review.handle_reviews_stepwise(engine, cfg, bodies)
     assert got == want
-    assert set(stages) == {"parse", "flatten_decide", "patch", "render", "release_copy"} and all(v >= 0 for v in stages.values())
+    assert set(stages) == {"parse_flatten_release", "decide", "render", "copy"} and all(v >= 0 for v in stages.values())
     assert bgc.review.handle_reviews(engine, cfg, []) == []
     assert bgc.review.handle_reviews(engine, cfg, bodies[:3]) == want[:3]       # below the OpenMP threshold
     raw = [b.encode() if isinstance(b, str) else b for b in bodies[:10]]

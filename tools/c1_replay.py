@@ -125,14 +125,19 @@ def main():
     t_c2N = med(lambda: oracle.quota_eval(c_ns, c_req, c_mask, len(nss), used, hard, hm, cm, threads=cores))
     same = bool(np.array_equal(used, oracle.usage_reduce(r_ns, r_req, len(nss))) and
                 np.array_equal(eng.quota_eval(c_ns, c_req, c_mask), oracle.quota_eval(c_ns, c_req, c_mask, len(nss), used, hard, hm, cm)))
-    t_pe2e = med(lambda: bgc.review.handle_pod_reviews(eng, pbodies, C1_KEYS, m, used, hard), 5)
+    t_pe2e = med(lambda: bgc.review.handle_pod_reviews(eng, pbodies, C1_KEYS, m, used, hard), 9)
+    t_pstep = med(lambda: bgc.review.handle_pod_reviews_stepwise(eng, pbodies, C1_KEYS, m, used, hard), 3)
+    p_one = {}
+    bgc.review.handle_pod_reviews(eng, pbodies, C1_KEYS, m, used, hard, stage_ms=p_one)
     out["pod_reviews"] = {
         "wire_bytes": sum(len(b) for b in pbodies), "namespaces": len(nss), "running_pods": int(r_ns.shape[0]), "gpu_equals_cpu": same,
         "stage_ms": {"parse (C++ parser, one ctypes call per body)": t_pparse * 1e3, "flatten pod specs -> columns (C++, row A5)": t_pflat * 1e3,
                      "usage GPU: bgc_usage_reduce from host memory": t_k1 * 1e3, "usage CPU: quota_ref_usage_reduce, 1 thread": t_c1 * 1e3,
                      "verdicts GPU: bgc_quota_eval from host memory": t_k2 * 1e3, "verdicts CPU: quota_ref_quota_eval, 1 thread": t_c2 * 1e3,
                      f"verdicts CPU: quota_ref_quota_eval, {cores} threads": t_c2N * 1e3},
-        "wire_to_wire_ms_gpu_arm (review.handle_pod_reviews, Python glue included)": t_pe2e * 1e3,
+        "wire_to_wire_ms_gpu_arm (review.handle_pod_reviews = ONE C call, bgc_handle_pod_reviews; ctypes marshalling of the bodies included)": t_pe2e * 1e3,
+        "one_call_stage_ms (host clock inside bgc_handle_pod_reviews)": p_one,
+        "wire_to_wire_ms_call_by_call (review.handle_pod_reviews_stepwise, Python glue per body)": t_pstep * 1e3,
         "reviews_per_s_wire_to_wire_gpu_arm": n / t_pe2e,
         "verdict_stage_pods_per_s": {"gpu": n / t_k2, "cpu_1_thread": n / t_c2, "cpu_all": n / t_c2N},
         "who_wins_the_verdict_stage": "CPU" if min(t_c2, t_c2N) < t_k2 else "GPU",
