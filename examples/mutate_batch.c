@@ -1,6 +1,6 @@
 /* examples/mutate_batch.c — the C ABI from plain C: a batch of UserBootstrap admission requests is
  * flattened on the host, decided on the GPU and printed; then a handful of pods are checked against a
- * quota table.  Build (after `make -C bacchus-gpu-controller_b200/csrc`):
+ * quota table, and three raw AdmissionReview bodies go through the one-call handler.  Build (after `make -C bacchus-gpu-controller_b200/csrc`):
  *   gcc -std=c99 -Iinclude examples/mutate_batch.c -Lbacchus-gpu-controller_b200 -lbgc \
  *       -Wl,-rpath,$PWD/bacchus-gpu-controller_b200 -o /tmp/mutate_batch && /tmp/mutate_batch
  * Needs a CUDA device: there is no CPU fallback (bgc_ctx_create fails with BGC_E_CUDA otherwise). */
@@ -77,6 +77,25 @@ int main(void) {
   }
   printf("narrow columns: used gpu=[%lld,%lld] cpu=[%lld,%lld]; verdicts = %u %u %u\n", (long long)used_t[0], (long long)used_t[1],
          (long long)used_t[2], (long long)used_t[3], verdict_t[0], verdict_t[1], verdict_t[2]);
+  /* The handler itself, wire bytes to wire bytes (src/admission.rs:184-204): two review bodies and a broken one. */
+  const char *bodies[3] = {
+      "{\"apiVersion\":\"admission.k8s.io/v1\",\"kind\":\"AdmissionReview\",\"request\":{\"uid\":\"u-1\",\"operation\":\"CREATE\","
+      "\"userInfo\":{\"username\":\"oidc:alice\",\"groups\":[\"gpu\"]},\"object\":{\"metadata\":{\"name\":\"alice\"},\"spec\":{}}}}",
+      "{\"apiVersion\":\"admission.k8s.io/v1\",\"kind\":\"AdmissionReview\",\"request\":{\"uid\":\"u-2\",\"operation\":\"CREATE\","
+      "\"userInfo\":{\"username\":\"oidc:bob\",\"groups\":[]},\"object\":{\"metadata\":{\"name\":\"bob\"},\"spec\":{}}}}",
+      "{\"apiVersion\":"};
+  size_t lens[3], off[4];
+  char text[4096];
+  for (int i = 0; i < 3; ++i) {
+    lens[i] = 0;
+    while (bodies[i][lens[i]]) ++lens[i];
+  }
+  rc = bgc_handle_reviews(ctx, &cfg, bodies, lens, 3, text, sizeof text, off, NULL);
+  if (rc != BGC_OK) {
+    fprintf(stderr, "bgc_handle_reviews: %s\n", bgc_last_error(ctx));
+    return 1;
+  }
+  for (int i = 0; i < 3; ++i) printf("review %d -> %s\n", i, text + off[i]);
   bgc_ctx_destroy(ctx);
   return 0;
 }

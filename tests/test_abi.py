@@ -100,3 +100,7 @@ def test_c_example_runs_on_the_device(tmp_path):
     assert "request 2: allowed=1 class=0 reason=12" in out.stdout
     assert "used gpu=[1,1] cpu=[6000,1000]; verdicts = 0 1 1" in out.stdout
     assert "narrow columns: used gpu=[1,1] cpu=[6000,1000]; verdicts = 0 1 1" in out.stdout
+    import json
+    answers = [json.loads(line.split(" -> ", 1)[1])["response"] for line in out.stdout.splitlines() if line.startswith("review ")]
+    assert [a["allowed"] for a in answers] == [True, False, False] and answers[0]["uid"] == "u-1" and "patch" in answers[0]
+    assert answers[1]["status"]["message"] == "user is not in authorized group" and answers[2]["status"]["reason"] == "InvalidRequest"
