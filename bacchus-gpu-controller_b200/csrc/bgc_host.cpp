@@ -1285,7 +1285,7 @@ int bgc_plan_requeue_seconds(int failed) { return failed ? 3 : 30; }  // src/con
 }  // extern "C"
 
 // ---- the batched mutate_handler, wire bytes to wire bytes (reference src/admission.rs:184-204) ----------------
-extern "C" int bgc_handle_reviews(bgc_ctx* ctx, const bgc_admission_config* cfg, const char* const* bodies, const size_t* body_len,
+static int handle_reviews_impl(bgc_ctx* ctx, const bgc_admission_config* cfg, const char* const* bodies, const size_t* body_len,
                        size_t n, char* out, size_t out_cap, size_t* out_off, uint64_t* stage_ns) {
   if (!ctx || !cfg || (n && (!bodies || !body_len)) || !out_off || (!out && out_cap)) return BGC_E_BADARG;
   using clk = std::chrono::steady_clock;
@@ -1399,7 +1399,7 @@ extern "C" int bgc_handle_reviews(bgc_ctx* ctx, const bgc_admission_config* cfg,
 }
 
 // ---- Pod-create reviews, wire bytes to wire bytes (no reference counterpart; same seam as above) ------------------
-extern "C" int bgc_handle_pod_reviews(bgc_ctx* ctx, const char* const* bodies, const size_t* body_len, size_t n,
+static int handle_pod_reviews_impl(bgc_ctx* ctx, const char* const* bodies, const size_t* body_len, size_t n,
                                       const char* const* quota_keys, const uint8_t* unit, uint32_t R, bgc_nsmap* map, int wide,
                                       const int64_t* used, const int64_t* hard, uint32_t ns_count, char* out, size_t out_cap,
                                       size_t* out_off, uint64_t* stage_ns) {
@@ -1530,4 +1530,28 @@ extern "C" int bgc_handle_pod_reviews(bgc_ctx* ctx, const char* const* bodies, c
   for (size_t i = 0; i < n; ++i) std::memcpy(out + out_off[i], text[i].c_str(), text[i].size() + 1);
   if (stage_ns) { stage_ns[0] = t_parse; stage_ns[1] = t_flat; stage_ns[2] = t_eval; stage_ns[3] = t_render; stage_ns[4] = ns_since(t0); }
   return BGC_OK;
+}
+
+// the C boundary: nothing is thrown across it (the batch handlers allocate in proportion to the batch)
+extern "C" int bgc_handle_reviews(bgc_ctx* ctx, const bgc_admission_config* cfg, const char* const* bodies, const size_t* body_len,
+                                  size_t n, char* out, size_t out_cap, size_t* out_off, uint64_t* stage_ns) {
+  try {
+    return handle_reviews_impl(ctx, cfg, bodies, body_len, n, out, out_cap, out_off, stage_ns);
+  } catch (const std::bad_alloc&) {
+    return BGC_E_OOM;
+  } catch (...) {
+    return BGC_E_STATE;
+  }
+}
+extern "C" int bgc_handle_pod_reviews(bgc_ctx* ctx, const char* const* bodies, const size_t* body_len, size_t n,
+                                      const char* const* quota_keys, const uint8_t* unit, uint32_t R, bgc_nsmap* map, int wide,
+                                      const int64_t* used, const int64_t* hard, uint32_t ns_count, char* out, size_t out_cap,
+                                      size_t* out_off, uint64_t* stage_ns) {
+  try {
+    return handle_pod_reviews_impl(ctx, bodies, body_len, n, quota_keys, unit, R, map, wide, used, hard, ns_count, out, out_cap, out_off, stage_ns);
+  } catch (const std::bad_alloc&) {
+    return BGC_E_OOM;
+  } catch (...) {
+    return BGC_E_STATE;
+  }
 }
