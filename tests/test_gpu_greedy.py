@@ -226,3 +226,27 @@ def test_greedy_chained_tiles(engine, oracle, R, wide, scenario):
         assert 0.2 < np.mean(want_v == 0) < 0.9
     if scenario == "wrap":
         assert want_u[R - 1, 0] < 0                  # it did wrap
+
+
+def test_greedy_one_cta_per_long_segment_form(bgc, oracle, monkeypatch):
+    """BGC_K3_LONG=team: the round-2 walker that gives a long segment to ONE CTA is kept for comparison; it must stay
+    bit-exact too (a fresh context reads the knob at its first greedy call)."""
+    monkeypatch.setenv("BGC_K3_LONG", "team")
+    eng = bgc.Engine(0)
+    try:
+        rng = np.random.default_rng(77)
+        R, NS, n = 3, 3, 400_000
+        ns = rng.choice(np.array([0, 0, 0, 1, 2], np.uint32), n)
+        req = [rng.choice(np.array([0, 1, 2, 8, 250, 4000], np.int64), n) for _ in range(R)]
+        req[1][rng.integers(0, n, 50)] = -7
+        mask = rng.integers(0, 256, n, dtype=np.uint8) | np.uint8(0b0110)
+        total = np.stack([np.bincount(ns, weights=c.astype(np.float64), minlength=NS) for c in req]).astype(np.int64)
+        hard, hm = total // 3, np.full(NS, 7, np.uint8)
+        used0 = np.zeros((R, NS), np.int64)
+        eng.quota_table_set(hard, hm, UNITS[R])
+        eng.usage_set(used0)
+        want_v, want_u = oracle.admit_greedy(ns, req, mask, NS, used0, hard, hm, _cm(UNITS[R]))
+        assert np.array_equal(eng.admit_greedy(ns, req, mask), want_v)
+        assert np.array_equal(eng.usage_get(), want_u)
+    finally:
+        eng.close()
