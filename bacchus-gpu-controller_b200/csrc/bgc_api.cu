@@ -1357,18 +1357,12 @@ int admit_greedy_dev_impl(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* 
         P.mask_in = p == 0 ? d_req_mask : (to_final ? ctx->g_mask2 : ctx->g_mask);
         P.mask_out = to_final ? ctx->g_mask : ctx->g_mask2;
       }
-      static const int sort_form = [] { const char* e = std::getenv("BGC_K3_SORT"); return e ? std::atoi(e) : 4; }();
-      if (sort_form == 4) {
-        CU(cudaFuncSetAttribute(k_rsort_scatter4, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 11));
-        k_rsort_scatter4<<<grid, kSort2Threads, (size_t)kSortTile * 11, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
-      } else if (sort_form == 3) {
-        CU(cudaFuncSetAttribute(k_rsort_scatter3, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 11));
-        k_rsort_scatter3<<<grid, kSortThreads, (size_t)kSortTile * 11, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
-      } else if (sort_form == 2) {
-        CU(cudaFuncSetAttribute(k_rsort_scatter2, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 10));
-        k_rsort_scatter2<<<grid, kSort2Threads, (size_t)kSortTile * 10, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
-      } else {
+      static const int sort_form = [] { const char* e = std::getenv("BGC_K3_SORT"); return e ? std::atoi(e) : 0; }();
+      if (sort_form == 1) {  // the round-2 form before warp-private ranking and the staged payload (kept for comparison)
         k_rsort_scatter<<<grid, kSortThreads, (size_t)kSortTile * 10, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
+      } else {
+        CU(cudaFuncSetAttribute(k_rsort_scatter_wp, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 11));
+        k_rsort_scatter_wp<<<grid, kSort2Threads, (size_t)kSortTile * 11, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
       }
       ctx->tm.launches += 3;
       CU(cudaGetLastError());

@@ -266,306 +266,25 @@ k_rsort_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
   }
 }
 
-// The shipped form: as above, but the payload goes THROUGH shared memory at write-out (see there).
-static __global__ void __launch_bounds__(kSortThreads)
-k_rsort_scatter3(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ ns_id,
-                uint32_t NS, size_t n, int shift, const uint32_t* __restrict__ offs, uint32_t ntile,
-                uint32_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out, SortPayload P) {
-  extern __shared__ __align__(16) uint32_t rs_smem[];
-  uint32_t* s_key = rs_smem;                    // [kSortTile] the tile, grouped by digit
-  uint32_t* s_idx = rs_smem + kSortTile;        // [kSortTile]
-  unsigned short* s_src = reinterpret_cast<unsigned short*>(rs_smem + 2 * kSortTile);  // [kSortTile] where in the tile it came from
-  uint8_t* s_dig = reinterpret_cast<uint8_t*>(s_src + kSortTile);                      // [kSortTile] digit of the element placed at j
-  long long* stage = reinterpret_cast<long long*>(rs_smem);  // [kSortTile] one payload column of the tile, over s_key + s_idx once they are out
-  __shared__ uint32_t s_warp[kSortThreads / 32][256];  // per-warp digit counts of the current round, then bases
-  __shared__ uint32_t s_run[256];                      // cursor of each digit inside the tile
-  __shared__ uint32_t s_lbase[256];                    // first tile position of each digit
-  __shared__ uint32_t s_goff[256];                     // first global position of each digit's run of this tile
-  __shared__ uint32_t s_scan[kSortThreads / 32];
-  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  for (uint32_t t = blockIdx.x; t < ntile; t += gridDim.x) {
-    const size_t base = (size_t)t * kSortTile;
-    const uint32_t live_n = (uint32_t)(n - base < (size_t)kSortTile ? n - base : (size_t)kSortTile);
-    {  // this tile's digit counts = differences of the scanned digit-major histogram; exclusive scan over the 256 digits
-      const size_t at = (size_t)threadIdx.x * ntile + t;
-      const uint32_t off = offs[at];
-      // count of (digit d, tile t) = next entry in scan order - this one; the very last entry ends at n
-      const uint32_t nxt = (threadIdx.x == 255 && t + 1 == ntile) ? (uint32_t)n : offs[at + 1];
-      const uint32_t cnt = nxt - off;
-      uint32_t incl = cnt;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if (lane >= (uint32_t)d) incl += o;
-      }
-      if (lane == 31) s_scan[warp] = incl;
-      __syncthreads();
-      uint32_t before = incl - cnt;
-      for (uint32_t w = 0; w < warp; ++w) before += s_scan[w];
-      s_lbase[threadIdx.x] = before;
-      s_run[threadIdx.x] = before;
-      s_goff[threadIdx.x] = off;
-    }
-    // every load of the tile is issued before the first round (ncu: with one load per thread per round the kernel
-    // sat in long-scoreboard stalls at 13 % issue utilisation, a tile taking ~100 us of exposed latency)
-    uint32_t keys[kSortRounds], idxs[kSortRounds];
-#pragma unroll
-    for (int r = 0; r < kSortRounds; ++r) {
-      const size_t i = base + (size_t)r * kSortThreads + threadIdx.x;
-      keys[r] = i < n ? sort_key_at(keys_in, ns_id, NS, i) : 0u;
-      idxs[r] = i < n ? (idx_in ? idx_in[i] : (uint32_t)i) : 0u;
-    }
-#pragma unroll
-    for (int r = 0; r < kSortRounds; ++r) {
-#pragma unroll
-      for (int w = 0; w < kSortThreads / 32; ++w) s_warp[w][threadIdx.x] = 0;
-      __syncthreads();
-      const size_t i = base + (size_t)r * kSortThreads + threadIdx.x;
-      const bool live = i < n;
-      const uint32_t key = keys[r];
-      uint32_t digit = 0x100u + lane;  // dead lanes get digits nobody else has
-      if (live) digit = (key >> shift) & 0xFFu;
-      const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit);
-      const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
-      if (live && rank == 0) s_warp[warp][digit] = __popc(peers);  // the first lane of each group publishes its size
-      __syncthreads();
-      {  // thread d: turn the 8 per-warp counts of digit d into exclusive bases, advance the digit's cursor
-        uint32_t run = s_run[threadIdx.x];
-#pragma unroll
-        for (int w = 0; w < kSortThreads / 32; ++w) {
-          const uint32_t c = s_warp[w][threadIdx.x];
-          s_warp[w][threadIdx.x] = run;
-          run += c;
-        }
-        s_run[threadIdx.x] = run;
-      }
-      __syncthreads();
-      if (live) {
-        const uint32_t pos = s_warp[warp][digit] + rank;
-        s_key[pos] = key;
-        s_idx[pos] = idxs[r];
-        s_src[pos] = (unsigned short)(r * kSortThreads + threadIdx.x);
-      }
-      __syncthreads();
-    }
-    // write-out.  Keys and indices first, straight from shared memory; then the payload, one column at a time THROUGH
-    // shared memory: the tile's slice of the column is read coalesced into the space keys and indices have left, and
-    // gathered from there.  (Gathering it from global memory by source index costs a 32-byte L2 sector per 8-byte value,
-    // and L1 cannot hold a 64 KB window per column next to 160 KB of shared memory.)
-    constexpr int kWB = 8;
-    for (uint32_t j0 = threadIdx.x; j0 < live_n; j0 += kSortThreads * kWB) {
-#pragma unroll
-      for (int u = 0; u < kWB; ++u) {
-        const uint32_t j = j0 + (uint32_t)u * kSortThreads;
-        if (j < live_n) {
-          const uint32_t key = s_key[j];
-          const uint32_t d = (key >> shift) & 0xFFu;
-          const uint32_t gp = s_goff[d] + (j - s_lbase[d]);
-          keys_out[gp] = key;
-          idx_out[gp] = s_idx[j];
-          s_dig[j] = (uint8_t)d;
-        }
-      }
-    }
-    __syncthreads();
-    for (int q = 0; q < P.R; ++q) {
-      const long long* __restrict__ col = P.in[q] + base;
-      for (uint32_t i0 = threadIdx.x; i0 < live_n; i0 += kSortThreads * kWB) {
-        long long v[kWB];
-#pragma unroll
-        for (int u = 0; u < kWB; ++u) {
-          const uint32_t i = i0 + (uint32_t)u * kSortThreads;
-          v[u] = i < live_n ? col[i] : 0;
-        }
-#pragma unroll
-        for (int u = 0; u < kWB; ++u) {
-          const uint32_t i = i0 + (uint32_t)u * kSortThreads;
-          if (i < live_n) stage[i] = v[u];
-        }
-      }
-      __syncthreads();
-      long long* __restrict__ dst = P.out[q];
-      for (uint32_t j0 = threadIdx.x; j0 < live_n; j0 += kSortThreads * kWB) {
-#pragma unroll
-        for (int u = 0; u < kWB; ++u) {
-          const uint32_t j = j0 + (uint32_t)u * kSortThreads;
-          if (j < live_n) {
-            const uint32_t d = s_dig[j];
-            dst[s_goff[d] + (j - s_lbase[d])] = stage[s_src[j]];
-          }
-        }
-      }
-      __syncthreads();
-    }
-    if (P.mask_in) {
-      uint8_t* stage8 = reinterpret_cast<uint8_t*>(stage);
-      for (uint32_t i = threadIdx.x; i < live_n; i += kSortThreads) stage8[i] = P.mask_in[base + i];
-      __syncthreads();
-      for (uint32_t j = threadIdx.x; j < live_n; j += kSortThreads) {
-        const uint32_t d = s_dig[j];
-        P.mask_out[s_goff[d] + (j - s_lbase[d])] = stage8[s_src[j]];
-      }
-    }
-    __syncthreads();
-  }
-}
-
-// The same pass with WARP-PRIVATE ranking: every warp owns a contiguous chunk of the tile and ranks it round by round
-// against its own row of digit counters, with two __syncwarp per round and no block barrier; one block-wide step then
-// turns the per-warp counts into bases.  3 barriers per tile instead of 128, and only (digit, rank) live in registers
-// while ranking — 24 registers instead of 64 — so that 512 threads fit twice on an SM (32 warps instead of 16 to hide
-// the loads and the write-out behind).  Keys and indices are read a second time when the tile is placed in shared
-// memory: coalesced (the chunk in memory order), and L2 hits.
+// The shipped form of the pass.  Two things changed against k_rsort_scatter above (kept behind BGC_K3_SORT=1 for
+// comparison), each measured on the 10^8-pod greedy call:
+//  * WARP-PRIVATE ranking: every warp owns a contiguous chunk of the tile and ranks it round by round against its own
+//    row of digit counters, with two __syncwarp per round and no block barrier; one block-wide step then turns the
+//    per-warp counts into bases.  3 barriers per tile instead of 128, and only (digit, rank) live in registers while
+//    ranking — 24 registers instead of 64 — so that 512 threads fit twice on an SM (32 warps instead of 16).  Keys and
+//    indices are read a second time when the tile is placed in shared memory: coalesced, and L2 hits.
+//  * the payload columns go THROUGH shared memory at write-out: the tile's slice of a column is read coalesced into
+//    the space keys and indices have left, and gathered from there.  Gathering it from global memory by source index
+//    cost a 32-byte L2 sector per 8-byte value (L1 cannot hold a 64 KB window per column next to the shared memory).
+// Alone, the first made the call slower (9.7 against 8.1 ms: twice the threads thrashing L1 with those gathers) and
+// the second took 8.1 to 7.4 ms; together 5.9 ms (scatter passes 3.46 + 2.50 -> 2.03 + 1.79 ms).  Staging keys and
+// indices the same way as the payload changed nothing (5.97 ms).
 constexpr int kSort2Threads = 512;
 constexpr int kSort2Warps = kSort2Threads / 32;
 constexpr int kSort2Chunk = kSortTile / kSort2Warps;  // 512 consecutive elements per warp
 constexpr int kSort2Rounds = kSort2Chunk / 32;        // 16
 static __global__ void __launch_bounds__(kSort2Threads, 2)
-k_rsort_scatter2(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ ns_id,
-                 uint32_t NS, size_t n, int shift, const uint32_t* __restrict__ offs, uint32_t ntile,
-                 uint32_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out, SortPayload P) {
-  extern __shared__ __align__(16) uint32_t rs_smem[];
-  uint32_t* s_key = rs_smem;
-  uint32_t* s_idx = rs_smem + kSortTile;
-  unsigned short* s_src = reinterpret_cast<unsigned short*>(rs_smem + 2 * kSortTile);
-  __shared__ uint32_t s_warp[kSort2Warps][256];  // per-warp digit counts, then the warp's base for each digit
-  __shared__ uint32_t s_lbase[256];
-  __shared__ uint32_t s_goff[256];
-  __shared__ uint32_t s_scan[8];
-  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-  for (uint32_t t = blockIdx.x; t < ntile; t += gridDim.x) {
-    const size_t base = (size_t)t * kSortTile;
-    const uint32_t live_n = (uint32_t)(n - base < (size_t)kSortTile ? n - base : (size_t)kSortTile);
-    uint32_t cnt = 0, off = 0, incl = 0;
-    if (tid < 256) {  // this tile's digit counts = differences of the scanned digit-major histogram
-      const size_t at = (size_t)tid * ntile + t;
-      off = offs[at];
-      const uint32_t nxt = (tid == 255 && t + 1 == ntile) ? (uint32_t)n : offs[at + 1];
-      cnt = nxt - off;
-      incl = cnt;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if (lane >= (uint32_t)d) incl += o;
-      }
-      if (lane == 31) s_scan[warp] = incl;
-    }
-#pragma unroll
-    for (int d = 0; d < 256 / 32; ++d) s_warp[warp][d * 32 + lane] = 0;
-    __syncthreads();
-    if (tid < 256) {
-      uint32_t before = incl - cnt;
-      for (uint32_t w = 0; w < warp; ++w) before += s_scan[w];
-      s_lbase[tid] = before;
-      s_goff[tid] = off;
-    }
-    // ---- phase A: the warp ranks its own chunk (element e = warp * 512 + k * 32 + lane: memory order)
-    const uint32_t e0 = warp * kSort2Chunk + lane;
-    uint32_t dig[kSort2Rounds / 4], rk[kSort2Rounds / 2];
-#pragma unroll
-    for (int k4 = 0; k4 < kSort2Rounds / 4; ++k4) {
-      uint32_t kk[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const uint32_t e = e0 + (uint32_t)(k4 * 4 + u) * 32u;
-        kk[u] = e < live_n ? sort_key_at(keys_in, ns_id, NS, base + e) : 0u;
-      }
-      dig[k4] = ((kk[0] >> shift) & 0xFFu) | (((kk[1] >> shift) & 0xFFu) << 8) | (((kk[2] >> shift) & 0xFFu) << 16) | (((kk[3] >> shift) & 0xFFu) << 24);
-    }
-#pragma unroll
-    for (int k = 0; k < kSort2Rounds; ++k) {
-      const bool live = e0 + (uint32_t)k * 32u < live_n;
-      const uint32_t d = (dig[k >> 2] >> (8 * (k & 3))) & 0xFFu;
-      const uint32_t digit = live ? d : 0x100u + lane;  // dead lanes get digits nobody else has
-      const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit);
-      const uint32_t ahead = __popc(peers & ((1u << lane) - 1u));
-      const uint32_t seen = live ? s_warp[warp][d] : 0u;  // same-digit elements of the earlier rounds of this chunk
-      __syncwarp();
-      if (live && ahead == 0) s_warp[warp][d] = seen + __popc(peers);
-      __syncwarp();
-      const uint32_t r = seen + ahead;  // < 512
-      if (k & 1) rk[k >> 1] |= r << 16; else rk[k >> 1] = r;
-    }
-    __syncthreads();
-    // ---- phase B: digit d's counts of the 16 warps become the warps' first positions inside the tile
-    if (tid < 256) {
-      uint32_t run = s_lbase[tid];
-#pragma unroll
-      for (int w = 0; w < kSort2Warps; ++w) {
-        const uint32_t c = s_warp[w][tid];
-        s_warp[w][tid] = run;
-        run += c;
-      }
-    }
-    __syncthreads();
-    // ---- phase C: place the chunk (keys and indices read again, coalesced)
-#pragma unroll
-    for (int k8 = 0; k8 < kSort2Rounds / 8; ++k8) {
-      uint32_t kk[8], ii[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const uint32_t e = e0 + (uint32_t)(k8 * 8 + u) * 32u;
-        const bool live = e < live_n;
-        kk[u] = live ? sort_key_at(keys_in, ns_id, NS, base + e) : 0u;
-        ii[u] = (live && idx_in) ? idx_in[base + e] : (uint32_t)(base + e);
-      }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int k = k8 * 8 + u;
-        const uint32_t e = e0 + (uint32_t)k * 32u;
-        if (e < live_n) {
-          const uint32_t d = (dig[k >> 2] >> (8 * (k & 3))) & 0xFFu;
-          const uint32_t pos = s_warp[warp][d] + ((rk[k >> 1] >> (16 * (k & 1))) & 0xFFFFu);
-          s_key[pos] = kk[u];
-          s_idx[pos] = ii[u];
-          s_src[pos] = (unsigned short)e;
-        }
-      }
-    }
-    __syncthreads();
-    // ---- write-out, as in k_rsort_scatter
-    constexpr int kWB = 8;
-    for (uint32_t j0 = tid; j0 < live_n; j0 += kSort2Threads * kWB) {
-      uint32_t gpos[kWB];
-      size_t src[kWB];
-      bool on[kWB];
-#pragma unroll
-      for (int u = 0; u < kWB; ++u) {
-        const uint32_t j = j0 + (uint32_t)u * kSort2Threads;
-        on[u] = j < live_n;
-        const uint32_t key = on[u] ? s_key[j] : 0u;
-        const uint32_t d = (key >> shift) & 0xFFu;
-        gpos[u] = on[u] ? s_goff[d] + (j - s_lbase[d]) : 0u;
-        src[u] = base + (on[u] ? s_src[j] : 0u);
-        if (on[u]) {
-          keys_out[gpos[u]] = key;
-          idx_out[gpos[u]] = s_idx[j];
-        }
-      }
-      for (int q = 0; q < P.R; ++q) {
-        long long v[kWB];
-#pragma unroll
-        for (int u = 0; u < kWB; ++u) v[u] = on[u] ? P.in[q][src[u]] : 0;
-#pragma unroll
-        for (int u = 0; u < kWB; ++u)
-          if (on[u]) P.out[q][gpos[u]] = v[u];
-      }
-      if (P.mask_in) {
-        uint8_t m[kWB];
-#pragma unroll
-        for (int u = 0; u < kWB; ++u) m[u] = on[u] ? P.mask_in[src[u]] : (uint8_t)0;
-#pragma unroll
-        for (int u = 0; u < kWB; ++u)
-          if (on[u]) P.mask_out[gpos[u]] = m[u];
-      }
-    }
-    __syncthreads();
-  }
-}
-
-// Warp-private ranking (k_rsort_scatter2) with the payload staged through shared memory (k_rsort_scatter3).
-static __global__ void __launch_bounds__(kSort2Threads, 2)
-k_rsort_scatter4(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ ns_id,
+k_rsort_scatter_wp(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ idx_in, const uint32_t* __restrict__ ns_id,
                  uint32_t NS, size_t n, int shift, const uint32_t* __restrict__ offs, uint32_t ntile,
                  uint32_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out, SortPayload P) {
   extern __shared__ __align__(16) uint32_t rs_smem[];
