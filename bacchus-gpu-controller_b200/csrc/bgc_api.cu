@@ -1361,8 +1361,8 @@ int admit_greedy_dev_impl(bgc_ctx* ctx, const uint32_t* d_ns_id, const int64_t* 
       if (sort_form == 1) {  // the round-2 form before warp-private ranking and the staged payload (kept for comparison)
         k_rsort_scatter<<<grid, kSortThreads, (size_t)kSortTile * 10, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
       } else {
-        CU(cudaFuncSetAttribute(k_rsort_scatter_wp, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 11));
-        k_rsort_scatter_wp<<<grid, kSort2Threads, (size_t)kSortTile * 11, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
+        CU(cudaFuncSetAttribute(k_rsort_scatter_wp, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortTile * 10));
+        k_rsort_scatter_wp<<<grid, kSort2Threads, (size_t)kSortTile * 10, st>>>(kin, iin, d_ns_id, ctx->NS, n, 8 * p, ctx->g_hist, ntile, kout, iout, P);
       }
       ctx->tm.launches += 3;
       CU(cudaGetLastError());

@@ -291,7 +291,6 @@ k_rsort_scatter_wp(const uint32_t* __restrict__ keys_in, const uint32_t* __restr
   uint32_t* s_key = rs_smem;
   uint32_t* s_idx = rs_smem + kSortTile;
   unsigned short* s_src = reinterpret_cast<unsigned short*>(rs_smem + 2 * kSortTile);
-  uint8_t* s_dig = reinterpret_cast<uint8_t*>(s_src + kSortTile);
   long long* stage = reinterpret_cast<long long*>(rs_smem);  // one payload column of the tile, over s_key + s_idx once they are out
   __shared__ uint32_t s_warp[kSort2Warps][256];  // per-warp digit counts, then the warp's base for each digit
   __shared__ uint32_t s_lbase[256];
@@ -391,26 +390,30 @@ k_rsort_scatter_wp(const uint32_t* __restrict__ keys_in, const uint32_t* __restr
     // write-out.  Keys and indices first, straight from shared memory; then the payload, one column at a time THROUGH
     // shared memory: the tile's slice of the column is read coalesced into the space keys and indices have left, and
     // gathered from there.  (Gathering it from global memory by source index costs a 32-byte L2 sector per 8-byte value,
-    // and L1 cannot hold a 64 KB window per column next to 160 KB of shared memory.)
+    // and L1 cannot hold a 64 KB window per column next to 160 KB of shared memory.)  A thread places the same 16
+    // positions for every column: where they go and where they came from stay in registers.
     constexpr int kWB = 8;
-    for (uint32_t j0 = threadIdx.x; j0 < live_n; j0 += kSort2Threads * kWB) {
+    constexpr int kPer = kSortTile / kSort2Threads;  // 16
+    uint32_t gp[kPer], sr[kPer / 2];
 #pragma unroll
-      for (int u = 0; u < kWB; ++u) {
-        const uint32_t j = j0 + (uint32_t)u * kSort2Threads;
-        if (j < live_n) {
-          const uint32_t key = s_key[j];
-          const uint32_t d = (key >> shift) & 0xFFu;
-          const uint32_t gp = s_goff[d] + (j - s_lbase[d]);
-          keys_out[gp] = key;
-          idx_out[gp] = s_idx[j];
-          s_dig[j] = (uint8_t)d;
-        }
+    for (int m = 0; m < kPer; ++m) {
+      const uint32_t j = tid + (uint32_t)m * kSort2Threads;
+      uint32_t from = 0;
+      gp[m] = 0xFFFFFFFFu;
+      if (j < live_n) {
+        const uint32_t key = s_key[j];
+        const uint32_t d = (key >> shift) & 0xFFu;
+        gp[m] = s_goff[d] + (j - s_lbase[d]);
+        from = s_src[j];
+        keys_out[gp[m]] = key;
+        idx_out[gp[m]] = s_idx[j];
       }
+      if (m & 1) sr[m >> 1] |= from << 16; else sr[m >> 1] = from;
     }
     __syncthreads();
     for (int q = 0; q < P.R; ++q) {
       const long long* __restrict__ col = P.in[q] + base;
-      for (uint32_t i0 = threadIdx.x; i0 < live_n; i0 += kSort2Threads * kWB) {
+      for (uint32_t i0 = tid; i0 < live_n; i0 += kSort2Threads * kWB) {
         long long v[kWB];
 #pragma unroll
         for (int u = 0; u < kWB; ++u) {
@@ -425,26 +428,18 @@ k_rsort_scatter_wp(const uint32_t* __restrict__ keys_in, const uint32_t* __restr
       }
       __syncthreads();
       long long* __restrict__ dst = P.out[q];
-      for (uint32_t j0 = threadIdx.x; j0 < live_n; j0 += kSort2Threads * kWB) {
 #pragma unroll
-        for (int u = 0; u < kWB; ++u) {
-          const uint32_t j = j0 + (uint32_t)u * kSort2Threads;
-          if (j < live_n) {
-            const uint32_t d = s_dig[j];
-            dst[s_goff[d] + (j - s_lbase[d])] = stage[s_src[j]];
-          }
-        }
-      }
+      for (int m = 0; m < kPer; ++m)
+        if (gp[m] != 0xFFFFFFFFu) dst[gp[m]] = stage[(sr[m >> 1] >> (16 * (m & 1))) & 0xFFFFu];
       __syncthreads();
     }
     if (P.mask_in) {
       uint8_t* stage8 = reinterpret_cast<uint8_t*>(stage);
-      for (uint32_t i = threadIdx.x; i < live_n; i += kSort2Threads) stage8[i] = P.mask_in[base + i];
+      for (uint32_t i = tid; i < live_n; i += kSort2Threads) stage8[i] = P.mask_in[base + i];
       __syncthreads();
-      for (uint32_t j = threadIdx.x; j < live_n; j += kSort2Threads) {
-        const uint32_t d = s_dig[j];
-        P.mask_out[s_goff[d] + (j - s_lbase[d])] = stage8[s_src[j]];
-      }
+#pragma unroll
+      for (int m = 0; m < kPer; ++m)
+        if (gp[m] != 0xFFFFFFFFu) P.mask_out[gp[m]] = stage8[(sr[m >> 1] >> (16 * (m & 1))) & 0xFFFFu];
     }
     __syncthreads();
   }
