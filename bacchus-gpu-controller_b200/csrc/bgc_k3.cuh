@@ -574,22 +574,30 @@ k3_admit_greedy(const uint32_t* __restrict__ order, const uint32_t* __restrict__
           for (int r = 0; r < R; ++r) S[r] += __shfl_sync(0xFFFFFFFFu, E[r], v);
           live &= ~((2u << v) - 1u);
         }
-        // reason bits of the rejected pods are taken against the usage they actually met
-        long long incl[R], T[R];
+        // reason bits of the rejected pods are taken against the usage they actually met: a second scan, over the
+        // admitted pods only — not needed when the whole tile got in, nor when nobody did (usage never moved)
         const bool adm = (admitted >> lane) & 1u;
+        const uint32_t everyone = __ballot_sync(0xFFFFFFFFu, valid);
+        if (admitted == everyone) {
+          my_verdict = 0u;
+        } else if (admitted == 0u) {
+          my_verdict = valid ? greedy_verdict<R, SHIFT>(p, S0, H, hm, compute_mask) : 0u;
+        } else {
+          long long incl[R], T[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) incl[r] = adm ? p.q[r] : 0;
+          for (int r = 0; r < R; ++r) incl[r] = adm ? p.q[r] : 0;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
+          for (int d = 1; d < 32; d <<= 1) {
 #pragma unroll
-          for (int r = 0; r < R; ++r) {
-            const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
-            if (lane >= (uint32_t)d) incl[r] += o;
+            for (int r = 0; r < R; ++r) {
+              const long long o = __shfl_up_sync(0xFFFFFFFFu, incl[r], d);
+              if (lane >= (uint32_t)d) incl[r] += o;
+            }
           }
-        }
 #pragma unroll
-        for (int r = 0; r < R; ++r) T[r] = S0[r] + incl[r] - (adm ? p.q[r] : 0);
-        my_verdict = adm ? 0u : greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
+          for (int r = 0; r < R; ++r) T[r] = S0[r] + incl[r] - (adm ? p.q[r] : 0);
+          my_verdict = adm ? 0u : greedy_verdict<R, SHIFT>(p, T, H, hm, compute_mask);
+        }
         pos = 32;
       }
       while (pos < 32) {
