@@ -64,6 +64,26 @@ def test_pod_review_flattening_equals_dict_flattening(bgc):
         assert np.array_equal(x, y)
 
 
+def test_pod_review_with_thousands_of_containers(bgc):
+    """The per-review stores of resource lists hand out pointers while they grow (a deque: nothing moves): a pod with
+    3,000 containers and 500 init containers flattens to the same row through the review path and the dict path."""
+    from workloads import C1_KEYS
+    m = bgc.pods.NamespaceMap()
+    m.intern("big")
+    ctrs = [{"name": f"c{i}", "resources": {"requests": {"cpu": f"{1 + i % 7}m", "memory": f"{1 + i % 5}Mi", "nvidia.com/gpu": str(i % 2)},
+                                            "limits": {"nvidia.com/gpu": str(i % 2)}}} for i in range(3000)]
+    inits = [{"name": f"i{i}", "resources": {"requests": {"cpu": "9", "memory": "1Gi"}}} for i in range(500)]
+    pod = {"metadata": {"name": "p", "namespace": "big"}, "spec": {"containers": ctrs, "initContainers": inits}}
+    body = json.dumps({"apiVersion": "admission.k8s.io/v1", "kind": "AdmissionReview",
+                       "request": {"uid": "u", "operation": "CREATE", "kind": {"kind": "Pod"}, "namespace": "big", "object": pod}})
+    a = bgc.review.flatten_pod_reviews([body], C1_KEYS, m)
+    b = bgc.pods.flatten_pods([pod], C1_KEYS, m, intern=False)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
+    for x, y in zip(a[1], b[1]):
+        assert np.array_equal(x, y) and x.shape == (1,)
+    assert int(a[1][C1_KEYS.index("requests.cpu")][0]) == max(sum(1 + i % 7 for i in range(3000)), 9000)   # max(sum of containers, largest init container)
+
+
 @pytest.mark.gpu
 def test_wire_bytes_to_response_json(bgc, engine):
     cfg_py, cfg = P.Config(), bgc.admission.AdmissionConfig()
